@@ -1,0 +1,135 @@
+/*
+ * moss_splat.h -- C ABI of the B200-native differentiable Gaussian-splat rasterizer.
+ *
+ * Drop-in boundary for MOSS's vendored `diff_gaussian_rasterization` (DGR =
+ * /root/reference/submodules/diff-gaussian-rasterization).  Each entry point names the
+ * reference interface it replaces.  Plain pointers and sizes only: every pointer is a
+ * DEVICE pointer on the current CUDA device unless stated otherwise; the caller owns
+ * every buffer (outputs, gradients and the three workspaces).  No C++ exceptions cross
+ * this boundary: every call returns a MOSS_* status code.
+ *
+ * All launches go to the `stream` argument (a cudaStream_t passed as void*), never to
+ * the legacy default stream, so calls are CUDA-graph capturable when MOSS_FLAG_ASYNC
+ * is set (no host synchronisation at all in that mode).
+ */
+#ifndef MOSS_SPLAT_H_INCLUDED
+#define MOSS_SPLAT_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MOSS_ABI_VERSION 1
+
+/* status codes */
+#define MOSS_OK                  0
+#define MOSS_ERR_BINNING_OVERFLOW 1  /* num_rendered > binning capacity: outputs invalid; grow the
+                                        binning workspace to >= moss_binning_workspace_bytes(*num_rendered)
+                                        and call again with MOSS_FLAG_REBIN */
+#define MOSS_ERR_INVALID_ARGUMENT 2
+#define MOSS_ERR_WORKSPACE_TOO_SMALL 3
+#define MOSS_ERR_CUDA            4   /* a CUDA runtime error; see moss_last_cuda_error() */
+
+/* flags */
+#define MOSS_FLAG_ASYNC       1u  /* never block the host: *num_rendered is set to -1; the instance count and an
+                                     overflow flag stay on the device (moss_export_state which=MOSS_STATE_COUNTERS).
+                                     Required under CUDA-graph capture. */
+#define MOSS_FLAG_REBIN       2u  /* geometry + tile counts in the workspaces are valid (previous call returned
+                                     MOSS_ERR_BINNING_OVERFLOW): redo only scatter + sort + blend */
+#define MOSS_FLAG_EXPORT_KEYS 4u  /* also materialise the sorted 64-bit (tile<<32 | depth_bits) key list (parity
+                                     checks against DGR/cuda_rasterizer/rasterizer_impl.cu:305-310); needs the
+                                     larger binning workspace moss_binning_workspace_bytes_ex(R, 1) */
+#define MOSS_FLAG_DEBUG       8u  /* synchronise + check after every launch (DGR/cuda_rasterizer/auxiliary.h:166-173) */
+#define MOSS_FLAG_DETERMINISTIC 16u /* backward: fixed-order gradient reduction (bit-reproducible run to run) */
+
+/* Workspace sizes.  Replace the reference's `required<GeometryState|ImageState|BinningState>()`
+ * (DGR/cuda_rasterizer/rasterizer_impl.h:64-72) and its three grow-callbacks
+ * (DGR/cuda_rasterizer/rasterizer.h:33-35, DGR/rasterize_points.cu:27-33): the caller allocates. */
+size_t moss_geom_workspace_bytes(int P);
+size_t moss_image_workspace_bytes(int W, int H);
+size_t moss_binning_workspace_bytes(long long capacity);
+size_t moss_binning_workspace_bytes_ex(long long capacity, int export_keys);
+/* largest instance count a binning workspace of `bytes` can hold */
+long long moss_binning_capacity(size_t bytes, int export_keys);
+
+/* Per-view rasterization inputs (GaussianRasterizationSettings,
+ * DGR/diff_gaussian_rasterization/__init__.py:160-172, plus the tensors of
+ * GaussianRasterizer.forward :190-223).  Exactly one of shs / colors_precomp and exactly one of
+ * (scales, rotations) / cov3D_precomp must be non-NULL. */
+typedef struct MossScene {
+    int P;                       /* number of Gaussians */
+    int D;                       /* active SH degree 0..3 */
+    int M;                       /* SH coefficient stride (16 for degree-3 storage); 0 if shs == NULL */
+    int W, H;                    /* image size */
+    const float* bg;             /* [3] */
+    const float* means3D;        /* [P,3] */
+    const float* shs;            /* [P,M,3] or NULL */
+    const float* colors_precomp; /* [P,3] or NULL */
+    const float* opacities;      /* [P] */
+    const float* scales;         /* [P,3] or NULL */
+    const float* rotations;      /* [P,4] (r,x,y,z), used un-normalised as in DGR forward.cu:127, or NULL */
+    const float* cov3D_precomp;  /* [P,6] xx,xy,xz,yy,yz,zz or NULL */
+    const float* viewmatrix;     /* [16], W2C transposed (row-major tensor), DGR auxiliary.h:58-77 */
+    const float* projmatrix;     /* [16] */
+    const float* campos;         /* [3] */
+    float scale_modifier;
+    float tanfovx, tanfovy;
+    int prefiltered;
+    void* geom_ws;   size_t geom_bytes;    /* >= moss_geom_workspace_bytes(P) */
+    void* image_ws;  size_t image_bytes;   /* >= moss_image_workspace_bytes(W,H) */
+    void* binning_ws; size_t binning_bytes; /* capacity derived with moss_binning_capacity() */
+} MossScene;
+
+/* Forward.  Replaces CudaRasterizer::Rasterizer::forward (DGR/cuda_rasterizer/rasterizer.h:33-60,
+ * rasterizer_impl.cu:198-341) and the torch glue RasterizeGaussiansCUDA (DGR/rasterize_points.cu:35-119).
+ * out_color [3,H,W], out_depth [H,W], out_alpha [H,W], radii int32[P] are fully written.
+ * *num_rendered (HOST pointer, may be NULL) receives the instance count R. */
+int moss_rasterize_forward(void* stream, const MossScene* scene, unsigned flags,
+                           float* out_color, float* out_depth, float* out_alpha, int* radii,
+                           int* num_rendered);
+
+/* Backward.  Replaces CudaRasterizer::Rasterizer::backward (DGR/cuda_rasterizer/rasterizer.h:62-98,
+ * rasterizer_impl.cu:345-447) and RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:121-206).
+ * The workspaces must be the ones the forward call filled.
+ * dL_dmean2D [P,3], dL_dconic [P,4], dL_dopacity [P], dL_dcolor [P,3] are ACCUMULATED into and must be
+ * zero on entry (one packed, zero-filled buffer is the intended use); dL_dmean3D [P,3], dL_dcov3D [P,6],
+ * dL_dsh [P,M,3] (if shs), dL_dscale [P,3] and dL_drot [P,4] (if scales) are fully written. */
+int moss_rasterize_backward(void* stream, const MossScene* scene, unsigned flags, const int* radii,
+                            const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+                            float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                            float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot);
+
+/* markVisible.  Replaces CudaRasterizer::Rasterizer::markVisible (DGR/cuda_rasterizer/rasterizer.h:26-31,
+ * rasterizer_impl.cu:54-66,141-153).  present: uint8[P]. */
+int moss_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix,
+                      const float* projmatrix, uint8_t* present);
+
+/* Internal-state export for parity tests (the reference needs a C++ shim over fromChunk for this,
+ * DGR/cuda_rasterizer/rasterizer_impl.cu:155-194).  Copies one state array into `dst` (device) on
+ * `stream`; returns the byte count or a negative MOSS_ERR_*. */
+#define MOSS_STATE_DEPTHS        0  /* f32[P] */
+#define MOSS_STATE_CLAMPED       1  /* u8[3P] */
+#define MOSS_STATE_MEANS2D       2  /* f32[2P] */
+#define MOSS_STATE_COV3D         3  /* f32[6P] (only when built from scales/rotations) */
+#define MOSS_STATE_CONIC_OPACITY 4  /* f32[4P] */
+#define MOSS_STATE_RGB           5  /* f32[3P] */
+#define MOSS_STATE_TILES_TOUCHED 7  /* u32[P] */
+#define MOSS_STATE_KEYS_SORTED   9  /* u64[R] (needs MOSS_FLAG_EXPORT_KEYS) */
+#define MOSS_STATE_POINT_LIST    11 /* u32[R] */
+#define MOSS_STATE_RANGES        12 /* u32[2*tiles] */
+#define MOSS_STATE_N_CONTRIB     13 /* u32[W*H] */
+#define MOSS_STATE_FINAL_T       14 /* f32[W*H] */
+#define MOSS_STATE_COUNTERS      15 /* u32[4]: num_rendered, overflow flag, capacity, reserved */
+long long moss_export_state(void* stream, const MossScene* scene, int which, void* dst, long long max_bytes);
+
+int moss_abi_version(void);
+const char* moss_error_string(int status);
+int moss_last_cuda_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MOSS_SPLAT_H_INCLUDED */

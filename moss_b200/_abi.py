@@ -1,0 +1,102 @@
+"""ctypes binding of the C-ABI library (include/moss_splat.h).
+
+The product path has NO fallback: if ``libmoss_splat.so`` is missing or does not export the
+declared symbols, importing/using the rasterizer raises.  Build it with ``python -m moss_b200.build``
+(or ``__graft_entry__.build()``).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_lib", "libmoss_splat.so")
+
+MOSS_OK = 0
+MOSS_ERR_BINNING_OVERFLOW = 1
+MOSS_ERR_INVALID_ARGUMENT = 2
+MOSS_ERR_WORKSPACE_TOO_SMALL = 3
+MOSS_ERR_CUDA = 4
+
+FLAG_ASYNC = 1
+FLAG_REBIN = 2
+FLAG_EXPORT_KEYS = 4
+FLAG_DEBUG = 8
+FLAG_DETERMINISTIC = 16
+
+STATE = dict(depths=0, clamped=1, means2D=2, cov3D=3, conic_opacity=4, rgb=5, tiles_touched=7,
+             keys_sorted=9, point_list=11, ranges=12, n_contrib=13, final_T=14, counters=15)
+
+# every symbol include/moss_splat.h declares
+SYMBOLS = [
+    "moss_geom_workspace_bytes", "moss_image_workspace_bytes", "moss_binning_workspace_bytes",
+    "moss_binning_workspace_bytes_ex", "moss_binning_capacity", "moss_rasterize_forward",
+    "moss_rasterize_backward", "moss_mark_visible", "moss_export_state", "moss_abi_version",
+    "moss_error_string", "moss_last_cuda_error",
+]
+
+
+class MossScene(C.Structure):
+    _fields_ = [
+        ("P", C.c_int), ("D", C.c_int), ("M", C.c_int), ("W", C.c_int), ("H", C.c_int),
+        ("bg", C.c_void_p), ("means3D", C.c_void_p), ("shs", C.c_void_p), ("colors_precomp", C.c_void_p),
+        ("opacities", C.c_void_p), ("scales", C.c_void_p), ("rotations", C.c_void_p),
+        ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p),
+        ("campos", C.c_void_p),
+        ("scale_modifier", C.c_float), ("tanfovx", C.c_float), ("tanfovy", C.c_float),
+        ("prefiltered", C.c_int),
+        ("geom_ws", C.c_void_p), ("geom_bytes", C.c_size_t),
+        ("image_ws", C.c_void_p), ("image_bytes", C.c_size_t),
+        ("binning_ws", C.c_void_p), ("binning_bytes", C.c_size_t),
+    ]
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library once; raise loudly when it is absent (no CPU / eager fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"moss_b200: native library {LIB_PATH} not built. Run `python -m moss_b200.build` "
+            "(needs nvcc; cross-compiles for sm_100a without a GPU). There is no fallback path.")
+    lib = C.CDLL(LIB_PATH)
+    missing = [s for s in SYMBOLS if not hasattr(lib, s)]
+    if missing:
+        raise RuntimeError(f"moss_b200: {LIB_PATH} lacks symbols {missing}; rebuild it")
+    vp = C.c_void_p
+    lib.moss_geom_workspace_bytes.restype = C.c_size_t
+    lib.moss_geom_workspace_bytes.argtypes = [C.c_int]
+    lib.moss_image_workspace_bytes.restype = C.c_size_t
+    lib.moss_image_workspace_bytes.argtypes = [C.c_int, C.c_int]
+    lib.moss_binning_workspace_bytes.restype = C.c_size_t
+    lib.moss_binning_workspace_bytes.argtypes = [C.c_longlong]
+    lib.moss_binning_workspace_bytes_ex.restype = C.c_size_t
+    lib.moss_binning_workspace_bytes_ex.argtypes = [C.c_longlong, C.c_int]
+    lib.moss_binning_capacity.restype = C.c_longlong
+    lib.moss_binning_capacity.argtypes = [C.c_size_t, C.c_int]
+    lib.moss_rasterize_forward.restype = C.c_int
+    lib.moss_rasterize_forward.argtypes = [vp, C.POINTER(MossScene), C.c_uint, vp, vp, vp, vp, C.POINTER(C.c_int)]
+    lib.moss_rasterize_backward.restype = C.c_int
+    lib.moss_rasterize_backward.argtypes = [vp, C.POINTER(MossScene), C.c_uint, vp] + [vp] * 12
+    lib.moss_mark_visible.restype = C.c_int
+    lib.moss_mark_visible.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+    lib.moss_export_state.restype = C.c_longlong
+    lib.moss_export_state.argtypes = [vp, C.POINTER(MossScene), C.c_int, vp, C.c_longlong]
+    lib.moss_abi_version.restype = C.c_int
+    lib.moss_error_string.restype = C.c_char_p
+    lib.moss_error_string.argtypes = [C.c_int]
+    lib.moss_last_cuda_error.restype = C.c_int
+    _lib = lib
+    return lib
+
+
+def check(status, what="moss"):
+    if status == MOSS_OK:
+        return
+    lib = load()
+    msg = lib.moss_error_string(status).decode()
+    if status == MOSS_ERR_CUDA:
+        msg += f" (cudaError {lib.moss_last_cuda_error()})"
+    raise RuntimeError(f"{what}: {msg}")

@@ -1,0 +1,94 @@
+// K2: per-tile exclusive scan -> tile ranges (+ instance count);  K3: scatter (depth|id) keys into tile segments.
+//
+// Replaces the reference's per-Gaussian InclusiveSum + blocking D2H of num_rendered + duplicateWithKeys +
+// global 64-bit CUB radix sort + memset + identifyTileRanges (DGR/cuda_rasterizer/rasterizer_impl.cu:70-138,
+// 279-320).  Because K1 already counted the instances of every tile, the tile ranges are a scan over T tiles
+// (one block) and every instance can be scattered straight into its tile's segment; the remaining order
+// inside a segment -- (depth bits, Gaussian id), which is what a STABLE sort of (tile|depth) keys emitted in
+// ascending Gaussian order produces -- is a total order, so any per-segment sort of the 64-bit
+// (depth_bits<<32 | id) key reproduces the reference's sorted list bit for bit (K4, blend.cuh).
+// HBM traffic per instance: 8 B write here + 8 B read + 4 B write in K4, versus ~150 B for the 6-pass
+// global radix sort.
+#pragma once
+#include "common.cuh"
+
+namespace moss {
+
+constexpr int SCAN_THREADS = 1024;
+
+// One block.  ranges[t] = [first,last) (or (0,0) for an empty tile, as the reference's memset leaves it),
+// tile_count[t] <- 0 (re-used as the scatter cursor), counters = {R, R > capacity, capacity}.
+// host_R (mapped pinned host memory, may be null) also receives R so the host can read it without a
+// blocking copy.
+__global__ void __launch_bounds__(SCAN_THREADS)
+tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint2* __restrict__ ranges,
+	uint32_t* __restrict__ counters, uint32_t capacity, volatile int* host_R)
+{
+	__shared__ uint32_t warp_sums[32];
+	__shared__ uint32_t carry_s;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	if (threadIdx.x == 0) carry_s = 0;
+	__syncthreads();
+	for (int base = 0; base < T; base += SCAN_THREADS) {
+		const int t = base + threadIdx.x;
+		const uint32_t c = (t < T) ? tile_count[t] : 0u;
+		uint32_t v = c;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint32_t n = __shfl_up_sync(0xffffffffu, v, o);
+			if (lane >= o) v += n;
+		}
+		if (lane == 31) warp_sums[warp] = v;
+		__syncthreads();
+		if (warp == 0) {
+			uint32_t w = warp_sums[lane];
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const uint32_t n = __shfl_up_sync(0xffffffffu, w, o);
+				if (lane >= o) w += n;
+			}
+			warp_sums[lane] = w;
+		}
+		__syncthreads();
+		const uint32_t carry = carry_s;
+		const uint32_t incl = v + (warp > 0 ? warp_sums[warp - 1] : 0u) + carry;
+		if (t < T) {
+			ranges[t] = c ? make_uint2(incl - c, incl) : make_uint2(0u, 0u);
+			tile_count[t] = 0u;
+		}
+		__syncthreads();
+		if (threadIdx.x == SCAN_THREADS - 1) carry_s = incl;
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) {
+		const uint32_t R = carry_s;
+		counters[0] = R;
+		counters[1] = (R > capacity) ? 1u : 0u;
+		counters[2] = capacity;
+		if (host_R) { *host_R = (int)R; __threadfence_system(); }
+	}
+}
+
+// The exclusive start of tile t: ranges[t].x is only meaningful for non-empty tiles, which is all the
+// scatter ever asks for.
+__global__ void __launch_bounds__(256)
+scatter_keys_kernel(int P, int grid_x, const int* __restrict__ radii, GeomWS g,
+	const uint2* __restrict__ ranges, uint32_t* __restrict__ cursor, const uint32_t* __restrict__ counters,
+	unsigned long long* __restrict__ keys)
+{
+	const int idx = blockIdx.x * 256 + threadIdx.x;
+	if (idx >= P) return;
+	if (counters[1]) return;          // binning buffer too small: host re-runs with a larger one
+	if (!(radii[idx] > 0)) return;
+	const ushort4 r = g.rect[idx];
+	const unsigned long long key = ((unsigned long long)__float_as_uint(g.depths[idx]) << 32) | (uint32_t)idx;
+	for (uint32_t y = r.y; y < r.w; y++) {
+		for (uint32_t x = r.x; x < r.z; x++) {
+			const uint32_t t = y * grid_x + x;
+			const uint32_t slot = ranges[t].x + atomicAdd(&cursor[t], 1u);
+			keys[slot] = key;
+		}
+	}
+}
+
+} // namespace moss

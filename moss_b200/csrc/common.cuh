@@ -1,0 +1,126 @@
+// Shared definitions for the sm_100a splat rasterizer kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace moss {
+
+constexpr int TILE_X = 16;          // DGR/cuda_rasterizer/config.h:16-17 (tile = 16x16 px)
+constexpr int TILE_Y = 16;
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+constexpr int NCH = 3;              // DGR/cuda_rasterizer/config.h:15
+
+// ---------------------------------------------------------------------------------------------
+// Explicitly-rounded fp32 helpers.  The integer outputs (radii, tile rects, depth key bits) must be
+// bit-identical to the reference, which depends on WHERE nvcc fuses mul+add into fma in the
+// reference's expressions.  Intrinsics are never re-contracted, so the rounding sequence below is
+// pinned independent of compiler mood.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float ffma(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float frcp(float a) { return __frcp_rn(a); }
+__device__ __forceinline__ float fsqrt(float a) { return __fsqrt_rn(a); }
+
+// m[12+i] + (z*m[8+i] + (x*m[i] + y*m[4+i]))   -- rounding order of the reference's
+// transformPoint4x3/4x4 expressions (DGR/cuda_rasterizer/auxiliary.h:58-77) as nvcc contracts them.
+__device__ __forceinline__ float affine_row(float x, float y, float z, float m0, float m4, float m8, float m12)
+{
+	return fadd(m12, ffma(z, m8, ffma(x, m0, fmul(y, m4))));
+}
+// a2*b2 + (a0*b0 + a1*b1)   -- GLM mat3*mat3 element (glm/detail/type_mat3x3.inl:509-517) after contraction
+__device__ __forceinline__ float dot3_glm(float a0, float b0, float a1, float b1, float a2, float b2)
+{
+	return ffma(a2, b2, ffma(a0, b0, fmul(a1, b1)));
+}
+
+__host__ __device__ __forceinline__ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// ---------------------------------------------------------------------------------------------
+// Workspace carving (caller-owned memory; layout private to this library).
+// ---------------------------------------------------------------------------------------------
+struct GeomWS {
+	float*    depths;         // [P]   view-space z (sort key low bits)
+	float2*   means2D;        // [P]   pixel-space centre
+	float4*   conic_opacity;  // [P]   (conic.x, conic.y, conic.z, opacity)
+	float4*   feat;           // [P]   (r, g, b, depth): one 16 B gather per blended instance
+	float*    cov3D;          // [6P]  only written when built from scale/rotation
+	uint32_t* tiles_touched;  // [P]
+	ushort4*  rect;           // [P]   tile rect (xmin, ymin, xmax, ymax)
+	uint8_t*  clamped;        // [P]   bit c set <=> SH colour channel c was clamped at 0
+};
+struct ImageWS {
+	float*    final_T;        // [N]
+	uint32_t* n_contrib;      // [N]
+	uint32_t* tile_count;     // [T]  per-tile instance count, then scatter cursor
+	uint2*    ranges;         // [T]  [first, last) into the sorted list
+	uint32_t* counters;       // [4]  num_rendered, overflow, capacity, reserved
+};
+struct BinWS {
+	unsigned long long* keys; // [cap] (depth_bits << 32 | gaussian id), grouped per tile, sorted in place
+	uint32_t* point_list;     // [cap] sorted gaussian ids
+	unsigned long long* keys_sorted; // [cap] (tile << 32 | depth_bits), only with EXPORT_KEYS
+};
+
+template <typename T>
+__host__ __device__ inline T* carve(char*& p, size_t count)
+{
+	p = (char*)align_up((size_t)p, 256);
+	T* r = (T*)p;
+	p += count * sizeof(T);
+	return r;
+}
+__host__ __device__ inline GeomWS carve_geom(char* base, size_t P, size_t* bytes = nullptr)
+{
+	char* p = base;
+	GeomWS g;
+	g.depths = carve<float>(p, P);
+	g.means2D = carve<float2>(p, P);
+	g.conic_opacity = carve<float4>(p, P);
+	g.feat = carve<float4>(p, P);
+	g.cov3D = carve<float>(p, 6 * P);
+	g.tiles_touched = carve<uint32_t>(p, P);
+	g.rect = carve<ushort4>(p, P);
+	g.clamped = carve<uint8_t>(p, P);
+	if (bytes) *bytes = (size_t)(p - base) + 256;
+	return g;
+}
+__host__ __device__ inline ImageWS carve_image(char* base, size_t N, size_t T, size_t* bytes = nullptr)
+{
+	char* p = base;
+	ImageWS s;
+	s.final_T = carve<float>(p, N);
+	s.n_contrib = carve<uint32_t>(p, N);
+	s.tile_count = carve<uint32_t>(p, T);
+	s.ranges = carve<uint2>(p, T);
+	s.counters = carve<uint32_t>(p, 4);
+	if (bytes) *bytes = (size_t)(p - base) + 256;
+	return s;
+}
+__host__ __device__ inline BinWS carve_bin(char* base, size_t cap, bool export_keys, size_t* bytes = nullptr)
+{
+	char* p = base;
+	BinWS b;
+	b.keys = carve<unsigned long long>(p, cap);
+	b.point_list = carve<uint32_t>(p, cap);
+	b.keys_sorted = export_keys ? carve<unsigned long long>(p, cap) : nullptr;
+	if (bytes) *bytes = (size_t)(p - base) + 256;
+	return b;
+}
+
+// Per-view parameters.  The matrices live in device memory (they are torch tensors in the reference
+// API: DGR/diff_gaussian_rasterization/__init__.py:160-172); each block stages them in shared memory once.
+struct ViewParams {
+	const float* view;    // [16]
+	const float* proj;    // [16]
+	const float* campos;  // [3]
+	const float* bg;      // [3]
+	float tanfovx, tanfovy, focal_x, focal_y;
+	float scale_modifier;
+	int W, H, grid_x, grid_y;
+	int D, M;
+};
+
+} // namespace moss

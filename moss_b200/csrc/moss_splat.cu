@@ -1,0 +1,343 @@
+// C-ABI entry points (include/moss_splat.h) and launch orchestration for the sm_100a splat rasterizer.
+//
+// Forward launch sequence (5 launches, zero host synchronisation in ASYNC mode):
+//   memset(tile_count) -> K1 preprocess+count -> K2 tile scan -> K3 scatter -> K4 sort+blend
+// versus the reference's preprocess -> CUB scan -> blocking D2H -> duplicateWithKeys -> CUB radix sort
+// (~6 passes) -> memset -> identifyTileRanges -> render (DGR/cuda_rasterizer/rasterizer_impl.cu:198-341).
+// In synchronous mode the host waits only for an event recorded right after K2 (so K3/K4 are already queued
+// behind it and the GPU never idles) to learn num_rendered and detect binning-buffer overflow.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+#include <mutex>
+#include "../../include/moss_splat.h"
+#include "common.cuh"
+#include "preprocess.cuh"
+#include "preprocess_bwd.cuh"
+#include "binning.cuh"
+#include "blend.cuh"
+
+using namespace moss;
+
+namespace {
+
+thread_local int g_last_cuda_error = 0;
+
+#define MOSS_CUDA_TRY(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { g_last_cuda_error = (int)e__; return MOSS_ERR_CUDA; } } while (0)
+
+inline int check_launch(cudaStream_t s, unsigned flags)
+{
+	cudaError_t e = cudaGetLastError();
+	if (e == cudaSuccess && (flags & MOSS_FLAG_DEBUG)) e = cudaStreamSynchronize(s);
+	if (e != cudaSuccess) { g_last_cuda_error = (int)e; return MOSS_ERR_CUDA; }
+	return MOSS_OK;
+}
+#define MOSS_CHECK_LAUNCH(s, flags) do { int r__ = check_launch(s, flags); if (r__ != MOSS_OK) return r__; } while (0)
+
+// Pinned, device-mapped slots through which K2 hands num_rendered to the host without a blocking copy.
+struct HostSlots {
+	static constexpr int N = 64;
+	int* host = nullptr;       // cudaHostAlloc'ed, mapped
+	cudaEvent_t ev[N];
+	int next = 0;
+	bool ok = false;
+	std::mutex mu;
+	int acquire()
+	{
+		std::lock_guard<std::mutex> lk(mu);
+		if (!ok) {
+			if (cudaHostAlloc((void**)&host, N * sizeof(int), cudaHostAllocPortable | cudaHostAllocMapped) != cudaSuccess) return -1;
+			for (int i = 0; i < N; i++)
+				if (cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) != cudaSuccess) return -1;
+			ok = true;
+		}
+		const int s = next;
+		next = (next + 1) % N;
+		return s;
+	}
+};
+HostSlots g_slots;
+
+inline bool scene_valid(const MossScene* sc)
+{
+	if (!sc || sc->P < 0 || sc->W <= 0 || sc->H <= 0) return false;
+	if (sc->P == 0) return true;
+	if (!sc->means3D || !sc->opacities || !sc->viewmatrix || !sc->projmatrix || !sc->bg) return false;
+	if ((sc->shs != nullptr) == (sc->colors_precomp != nullptr)) return false;
+	const bool sr = (sc->scales != nullptr) && (sc->rotations != nullptr);
+	if (sr == (sc->cov3D_precomp != nullptr)) return false;
+	if (!sr && (sc->scales || sc->rotations)) return false;
+	if (sc->shs && (!sc->campos || sc->D < 0 || sc->D > 3 || sc->M < (sc->D + 1) * (sc->D + 1))) return false;
+	if (((sc->W + TILE_X - 1) / TILE_X) > 65535 || ((sc->H + TILE_Y - 1) / TILE_Y) > 65535) return false;
+	return true;
+}
+
+inline ViewParams make_view(const MossScene* sc)
+{
+	ViewParams vp;
+	vp.view = sc->viewmatrix; vp.proj = sc->projmatrix; vp.campos = sc->campos; vp.bg = sc->bg;
+	vp.tanfovx = sc->tanfovx; vp.tanfovy = sc->tanfovy;
+	vp.focal_y = sc->H / (2.0f * sc->tanfovy);   // DGR rasterizer_impl.cu:224-225
+	vp.focal_x = sc->W / (2.0f * sc->tanfovx);
+	vp.scale_modifier = sc->scale_modifier;
+	vp.W = sc->W; vp.H = sc->H;
+	vp.grid_x = (sc->W + TILE_X - 1) / TILE_X; vp.grid_y = (sc->H + TILE_Y - 1) / TILE_Y;
+	vp.D = sc->D; vp.M = sc->M;
+	return vp;
+}
+
+__global__ void reset_overflow_kernel(uint32_t* counters, uint32_t capacity)
+{
+	counters[1] = counters[0] > capacity ? 1u : 0u;
+	counters[2] = capacity;
+}
+
+__global__ void fill_background_kernel(int N, const float* __restrict__ bg, float* __restrict__ color,
+	float* __restrict__ depth, float* __restrict__ alpha)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= N) return;
+	color[i] = bg[0]; color[N + i] = bg[1]; color[2 * N + i] = bg[2];
+	depth[i] = 0.f; alpha[i] = 0.f;
+}
+
+} // namespace
+
+extern "C" {
+
+int moss_abi_version(void) { return MOSS_ABI_VERSION; }
+int moss_last_cuda_error(void) { return g_last_cuda_error; }
+
+const char* moss_error_string(int status)
+{
+	switch (status) {
+	case MOSS_OK: return "ok";
+	case MOSS_ERR_BINNING_OVERFLOW: return "binning workspace too small for num_rendered (re-run with MOSS_FLAG_REBIN)";
+	case MOSS_ERR_INVALID_ARGUMENT: return "invalid argument";
+	case MOSS_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
+	case MOSS_ERR_CUDA: return "CUDA runtime error";
+	default: return "unknown status";
+	}
+}
+
+size_t moss_geom_workspace_bytes(int P)
+{
+	size_t b = 0;
+	carve_geom(nullptr, (size_t)(P > 0 ? P : 0), &b);
+	return b;
+}
+size_t moss_image_workspace_bytes(int W, int H)
+{
+	size_t b = 0;
+	const size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+	carve_image(nullptr, (size_t)W * H, T, &b);
+	return b;
+}
+size_t moss_binning_workspace_bytes_ex(long long capacity, int export_keys)
+{
+	size_t b = 0;
+	carve_bin(nullptr, (size_t)(capacity > 0 ? capacity : 0), export_keys != 0, &b);
+	return b;
+}
+size_t moss_binning_workspace_bytes(long long capacity) { return moss_binning_workspace_bytes_ex(capacity, 0); }
+long long moss_binning_capacity(size_t bytes, int export_keys)
+{
+	const size_t per = export_keys ? 20 : 12;
+	long long lo = 0, hi = (long long)(bytes / per) + 1;   // largest cap with bytes_ex(cap) <= bytes
+	while (lo < hi) {
+		const long long mid = lo + (hi - lo + 1) / 2;
+		if (moss_binning_workspace_bytes_ex(mid, export_keys) <= bytes) lo = mid; else hi = mid - 1;
+	}
+	return lo;
+}
+
+int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
+	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!scene_valid(sc) || !out_color || !out_depth || !out_alpha) return MOSS_ERR_INVALID_ARGUMENT;
+	if (sc->P > 0 && !radii) return MOSS_ERR_INVALID_ARGUMENT;
+	if (num_rendered) *num_rendered = (flags & MOSS_FLAG_ASYNC) ? -1 : 0;
+	const int P = sc->P, W = sc->W, H = sc->H, N = W * H;
+	const ViewParams vp = make_view(sc);
+	const int T = vp.grid_x * vp.grid_y;
+	if (sc->image_bytes < moss_image_workspace_bytes(W, H) || !sc->image_ws) return MOSS_ERR_WORKSPACE_TOO_SMALL;
+	ImageWS im = carve_image((char*)sc->image_ws, (size_t)N, (size_t)T);
+	if (P == 0) {
+		// DGR/rasterize_points.cu:83: nothing rendered; outputs are background / zeros, state says "no contributors"
+		fill_background_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, sc->bg, out_color, out_depth, out_alpha);
+		MOSS_CUDA_TRY(cudaMemsetAsync(sc->image_ws, 0, moss_image_workspace_bytes(W, H) - 256, stream));
+		MOSS_CHECK_LAUNCH(stream, flags);
+		return MOSS_OK;
+	}
+	if (sc->geom_bytes < moss_geom_workspace_bytes(P) || !sc->geom_ws) return MOSS_ERR_WORKSPACE_TOO_SMALL;
+	const bool export_keys = (flags & MOSS_FLAG_EXPORT_KEYS) != 0;
+	const long long cap_ll = sc->binning_ws ? moss_binning_capacity(sc->binning_bytes, export_keys) : 0;
+	const uint32_t capacity = (uint32_t)(cap_ll > 0xfffffff0ll ? 0xfffffff0ll : cap_ll);
+	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P);
+	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
+
+	int slot = -1;
+	if (!(flags & MOSS_FLAG_ASYNC)) {
+		slot = g_slots.acquire();
+		if (slot < 0) { g_last_cuda_error = (int)cudaGetLastError(); return MOSS_ERR_CUDA; }
+	}
+
+	if (!(flags & MOSS_FLAG_REBIN)) {
+		MOSS_CUDA_TRY(cudaMemsetAsync(im.tile_count, 0, (size_t)T * sizeof(uint32_t), stream));
+		preprocess_forward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
+			P, vp, sc->means3D, sc->shs, sc->colors_precomp, sc->opacities, sc->scales, sc->rotations,
+			sc->cov3D_precomp, sc->prefiltered, g, im.tile_count, radii);
+		MOSS_CHECK_LAUNCH(stream, flags);
+		int* host_R = nullptr;
+		if (slot >= 0) MOSS_CUDA_TRY(cudaHostGetDevicePointer((void**)&host_R, g_slots.host + slot, 0));
+		tile_scan_kernel<<<1, SCAN_THREADS, 0, stream>>>(T, im.tile_count, im.ranges, im.counters, capacity, host_R);
+		MOSS_CHECK_LAUNCH(stream, flags);
+		if (slot >= 0) MOSS_CUDA_TRY(cudaEventRecord(g_slots.ev[slot], stream));
+	} else {
+		reset_overflow_kernel<<<1, 1, 0, stream>>>(im.counters, capacity);
+		MOSS_CHECK_LAUNCH(stream, flags);
+	}
+
+	scatter_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, vp.grid_x, radii, g, im.ranges, im.tile_count,
+		im.counters, b.keys);
+	MOSS_CHECK_LAUNCH(stream, flags);
+	blend_forward_kernel<<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+	MOSS_CHECK_LAUNCH(stream, flags);
+
+	if (flags & MOSS_FLAG_ASYNC) return MOSS_OK;
+	int R;
+	if (!(flags & MOSS_FLAG_REBIN)) {
+		MOSS_CUDA_TRY(cudaEventSynchronize(g_slots.ev[slot]));
+		R = *(volatile int*)(g_slots.host + slot);
+	} else {
+		uint32_t c[4];
+		MOSS_CUDA_TRY(cudaMemcpyAsync(c, im.counters, sizeof(c), cudaMemcpyDeviceToHost, stream));
+		MOSS_CUDA_TRY(cudaStreamSynchronize(stream));
+		R = (int)c[0];
+	}
+	if (num_rendered) *num_rendered = R;
+	if ((uint32_t)R > capacity) return MOSS_ERR_BINNING_OVERFLOW;
+	return MOSS_OK;
+}
+
+int moss_rasterize_backward(void* stream_, const MossScene* sc, unsigned flags, const int* radii,
+	const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!scene_valid(sc)) return MOSS_ERR_INVALID_ARGUMENT;
+	const int P = sc->P, W = sc->W, H = sc->H, N = W * H;
+	if (P == 0) return MOSS_OK;
+	if (!radii || !dL_dpix || !dL_ddepth || !dL_dalpha || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
+		!dL_dmean3D || !dL_dcov3D || (sc->shs && !dL_dsh) || (sc->scales && (!dL_dscale || !dL_drot)))
+		return MOSS_ERR_INVALID_ARGUMENT;
+	const ViewParams vp = make_view(sc);
+	const int T = vp.grid_x * vp.grid_y;
+	if (sc->image_bytes < moss_image_workspace_bytes(W, H) || sc->geom_bytes < moss_geom_workspace_bytes(P))
+		return MOSS_ERR_WORKSPACE_TOO_SMALL;
+	const bool export_keys = (flags & MOSS_FLAG_EXPORT_KEYS) != 0;
+	const long long cap_ll = sc->binning_ws ? moss_binning_capacity(sc->binning_bytes, export_keys) : 0;
+	const uint32_t capacity = (uint32_t)(cap_ll > 0xfffffff0ll ? 0xfffffff0ll : cap_ll);
+	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P);
+	ImageWS im = carve_image((char*)sc->image_ws, (size_t)N, (size_t)T);
+	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
+
+	blend_backward_kernel<<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha,
+		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
+	MOSS_CHECK_LAUNCH(stream, flags);
+	preprocess_backward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
+		P, vp, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
+		dL_dmean2D, dL_dconic, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);
+	MOSS_CHECK_LAUNCH(stream, flags);
+	return MOSS_OK;
+}
+
+int moss_mark_visible(void* stream_, int P, const float* means3D, const float* viewmatrix,
+	const float* projmatrix, uint8_t* present)
+{
+	(void)projmatrix;
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (P < 0) return MOSS_ERR_INVALID_ARGUMENT;
+	if (P == 0) return MOSS_OK;
+	if (!means3D || !viewmatrix || !present) return MOSS_ERR_INVALID_ARGUMENT;
+	mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, viewmatrix, present);
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+namespace {
+__global__ void expand_clamped_kernel(int P, const uint8_t* __restrict__ bits, uint8_t* __restrict__ out)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= P) return;
+	const uint8_t c = bits[i];
+	out[3 * i] = c & 1; out[3 * i + 1] = (c >> 1) & 1; out[3 * i + 2] = (c >> 2) & 1;
+}
+__global__ void extract_rgb_kernel(int P, const float4* __restrict__ feat, float* __restrict__ out)
+{
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= P) return;
+	const float4 f = feat[i];
+	out[3 * i] = f.x; out[3 * i + 1] = f.y; out[3 * i + 2] = f.z;
+}
+}
+
+long long moss_export_state(void* stream_, const MossScene* sc, int which, void* dst, long long max_bytes)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!sc || !dst) return -MOSS_ERR_INVALID_ARGUMENT;
+	const size_t P = sc->P, N = (size_t)sc->W * sc->H;
+	const int gx = (sc->W + TILE_X - 1) / TILE_X, gy = (sc->H + TILE_Y - 1) / TILE_Y;
+	const size_t T = (size_t)gx * gy;
+	GeomWS g = carve_geom((char*)sc->geom_ws, P);
+	ImageWS im = carve_image((char*)sc->image_ws, N, T);
+	uint32_t counters[4] = {0, 0, 0, 0};
+	if (which == MOSS_STATE_KEYS_SORTED || which == MOSS_STATE_POINT_LIST) {
+		if (cudaMemcpyAsync(counters, im.counters, sizeof(counters), cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+			cudaStreamSynchronize(stream) != cudaSuccess) return -MOSS_ERR_CUDA;
+	}
+	const size_t R = counters[0];
+	const void* src = nullptr;
+	long long n = -1;
+	switch (which) {
+	case MOSS_STATE_DEPTHS: src = g.depths; n = 4 * P; break;
+	case MOSS_STATE_MEANS2D: src = g.means2D; n = 8 * P; break;
+	case MOSS_STATE_COV3D: src = g.cov3D; n = 24 * P; break;
+	case MOSS_STATE_CONIC_OPACITY: src = g.conic_opacity; n = 16 * P; break;
+	case MOSS_STATE_TILES_TOUCHED: src = g.tiles_touched; n = 4 * P; break;
+	case MOSS_STATE_RANGES: src = im.ranges; n = 8 * T; break;
+	case MOSS_STATE_N_CONTRIB: src = im.n_contrib; n = 4 * N; break;
+	case MOSS_STATE_FINAL_T: src = im.final_T; n = 4 * N; break;
+	case MOSS_STATE_COUNTERS: src = im.counters; n = 16; break;
+	case MOSS_STATE_CLAMPED:
+		n = 3 * P;
+		if (n > max_bytes) return -MOSS_ERR_WORKSPACE_TOO_SMALL;
+		if (P) expand_clamped_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>((int)P, g.clamped, (uint8_t*)dst);
+		return n;
+	case MOSS_STATE_RGB:
+		n = 12 * P;
+		if (n > max_bytes) return -MOSS_ERR_WORKSPACE_TOO_SMALL;
+		if (P) extract_rgb_kernel<<<(unsigned)((P + 255) / 256), 256, 0, stream>>>((int)P, g.feat, (float*)dst);
+		return n;
+	case MOSS_STATE_KEYS_SORTED:
+	case MOSS_STATE_POINT_LIST: {
+		// counters[2] is the capacity the forward carved the binning workspace with; keys_sorted (present only
+		// with MOSS_FLAG_EXPORT_KEYS) lies behind keys and point_list, so one carve resolves both.
+		if (R > (size_t)counters[2]) return -MOSS_ERR_WORKSPACE_TOO_SMALL;
+		BinWS b = carve_bin((char*)sc->binning_ws, (size_t)counters[2], true);
+		if (which == MOSS_STATE_KEYS_SORTED) {
+			if (moss_binning_workspace_bytes_ex(counters[2], 1) > sc->binning_bytes) return -MOSS_ERR_WORKSPACE_TOO_SMALL;
+			src = b.keys_sorted; n = 8 * R;
+		} else { src = b.point_list; n = 4 * R; }
+		break;
+	}
+	default: return -MOSS_ERR_INVALID_ARGUMENT;
+	}
+	if (n > max_bytes) return -MOSS_ERR_WORKSPACE_TOO_SMALL;
+	if (n > 0 && cudaMemcpyAsync(dst, src, (size_t)n, cudaMemcpyDeviceToDevice, stream) != cudaSuccess) return -MOSS_ERR_CUDA;
+	return n;
+}
+
+} // extern "C"

@@ -1,0 +1,292 @@
+// K1: per-Gaussian forward preprocess (+ per-tile instance counting), K8: mark-visible.
+//
+// Semantics follow DGR/cuda_rasterizer/forward.cu:155-256 (preprocessCUDA), :74-113 (computeCov2D),
+// :118-152 (computeCov3D), :20-71 (computeColorFromSH) and DGR/cuda_rasterizer/auxiliary.h:41-56,139-164
+// (ndc2Pix in fp64, getRect, in_frustum).  The arithmetic is written with explicitly-rounded intrinsics in
+// the order nvcc contracts the reference's GLM expressions, because radii / rects / depth bits must be
+// bit-identical (they define the sorted key lists).  What is new here: one fused pass also bins the
+// Gaussian into its tiles (atomic per-tile counters) so no per-Gaussian prefix scan, key duplication pass
+// or global radix sort is needed downstream, and colour+depth are packed into one float4 per Gaussian.
+#pragma once
+#include "common.cuh"
+
+namespace moss {
+
+// SH basis constants (real spherical harmonics up to degree 3), same values as
+// DGR/cuda_rasterizer/auxiliary.h:22-39 / utils/sh_utils.py:24-55.
+#define MOSS_SH_C0 0.28209479177387814f
+#define MOSS_SH_C1 0.4886025119029199f
+#define MOSS_SH_C2_0 1.0925484305920792f
+#define MOSS_SH_C2_1 -1.0925484305920792f
+#define MOSS_SH_C2_2 0.31539156525252005f
+#define MOSS_SH_C2_3 -1.0925484305920792f
+#define MOSS_SH_C2_4 0.5462742152960396f
+#define MOSS_SH_C3_0 -0.5900435899266435f
+#define MOSS_SH_C3_1 2.890611442640554f
+#define MOSS_SH_C3_2 -0.4570457994644658f
+#define MOSS_SH_C3_3 0.3731763325901154f
+#define MOSS_SH_C3_4 -0.4570457994644658f
+#define MOSS_SH_C3_5 1.445305721320277f
+#define MOSS_SH_C3_6 -0.5900435899266435f
+
+struct Float3 { float x, y, z; };
+
+// 3D covariance from scale and UN-normalised quaternion (r,x,y,z) -- DGR forward.cu:118-152.
+__device__ __forceinline__ void cov3d_from_scale_rot(float sx, float sy, float sz, float mod,
+	float r, float x, float y, float z, float* cov)
+{
+	const float s0 = fmul(mod, sx), s1 = fmul(mod, sy), s2 = fmul(mod, sz);
+	const float yy = fmul(y, y), zz = fmul(z, z);
+	const float xy = fmul(x, y), rz = fmul(r, z);
+	const float xz = fmul(x, z), ry = fmul(r, y);
+	const float yz = fmul(y, z), rx = fmul(r, x);
+	const float yy_zz = fadd(yy, zz);
+	const float xx_zz = ffma(x, x, zz);
+	const float xx_yy = ffma(x, x, yy);
+	// R listed the way the reference hands it to glm::mat3 (column i, row j)
+	const float R00 = fsub(1.f, fadd(yy_zz, yy_zz));
+	const float R01 = fmul(2.f, fsub(xy, rz));
+	const float R02 = fmul(2.f, fadd(ry, xz));
+	const float R10 = fmul(2.f, fadd(xy, rz));
+	const float R11 = fsub(1.f, fadd(xx_zz, xx_zz));
+	const float R12 = fmul(2.f, fsub(yz, rx));
+	const float R20 = fmul(2.f, fsub(xz, ry));
+	const float R21 = fmul(2.f, fadd(rx, yz));
+	const float R22 = fsub(1.f, fadd(xx_yy, xx_yy));
+	// M = S * R (S diagonal): M[i][j] = s_j * R[i][j]
+	const float M00 = fmul(s0, R00), M01 = fmul(s1, R01), M02 = fmul(s2, R02);
+	const float M10 = fmul(s0, R10), M11 = fmul(s1, R11), M12 = fmul(s2, R12);
+	const float M20 = fmul(s0, R20), M21 = fmul(s1, R21), M22 = fmul(s2, R22);
+	// Sigma = M^T M
+	cov[0] = dot3_glm(M00, M00, M01, M01, M02, M02);
+	cov[1] = dot3_glm(M10, M00, M11, M01, M12, M02);
+	cov[2] = dot3_glm(M20, M00, M21, M01, M22, M02);
+	cov[3] = dot3_glm(M10, M10, M11, M11, M12, M12);
+	cov[4] = dot3_glm(M20, M10, M21, M11, M22, M12);
+	cov[5] = dot3_glm(M20, M20, M21, M21, M22, M22);
+}
+
+// EWA projection of the 3D covariance: returns (a, b, c) of the 2D covariance incl. the 0.3 px low-pass.
+// DGR forward.cu:74-113.  `v` = view matrix staged in shared memory.
+__device__ __forceinline__ Float3 cov2d_ewa(float tx, float ty, float tz, const float* v,
+	float focal_x, float focal_y, float tanfovx, float tanfovy, const float* c3, float* Tout = nullptr)
+{
+	const float limx = fmul(1.3f, tanfovx), limy = fmul(1.3f, tanfovy);
+	const float txtz = fdiv(tx, tz), tytz = fdiv(ty, tz);
+	const float cx = fminf(limx, fmaxf(-limx, txtz));
+	const float cy = fminf(limy, fmaxf(-limy, tytz));
+	const float tz2 = fmul(tz, tz);
+	const float J00 = fdiv(focal_x, tz);
+	const float J02 = fdiv(-fmul(focal_x, fmul(cx, tz)), tz2);
+	const float J11 = fdiv(focal_y, tz);
+	const float J12 = fdiv(-fmul(focal_y, fmul(cy, tz)), tz2);
+	// T = W * J (GLM), only the two non-zero columns
+	const float T00 = ffma(v[2], J02, fmul(v[0], J00));
+	const float T01 = ffma(v[6], J02, fmul(v[4], J00));
+	const float T02 = ffma(v[10], J02, fmul(v[8], J00));
+	const float T10 = ffma(v[2], J12, fmul(J11, v[1]));
+	const float T11 = ffma(v[6], J12, fmul(J11, v[5]));
+	const float T12 = ffma(v[10], J12, fmul(J11, v[9]));
+	if (Tout) { Tout[0] = T00; Tout[1] = T01; Tout[2] = T02; Tout[3] = T10; Tout[4] = T11; Tout[5] = T12; }
+	// A = T^T * Vrk^T
+	const float A00 = dot3_glm(T00, c3[0], T01, c3[1], T02, c3[2]);
+	const float A01 = dot3_glm(T10, c3[0], T11, c3[1], T12, c3[2]);
+	const float A10 = dot3_glm(T00, c3[1], T01, c3[3], T02, c3[4]);
+	const float A11 = dot3_glm(T10, c3[1], T11, c3[3], T12, c3[4]);
+	const float A20 = dot3_glm(T00, c3[2], T01, c3[4], T02, c3[5]);
+	const float A21 = dot3_glm(T10, c3[2], T11, c3[4], T12, c3[5]);
+	// cov = A * T
+	Float3 r;
+	r.x = fadd(dot3_glm(T00, A00, T01, A10, T02, A20), 0.3f);
+	r.y = dot3_glm(T00, A01, T01, A11, T02, A21);
+	r.z = fadd(dot3_glm(T10, A01, T11, A11, T12, A21), 0.3f);
+	return r;
+}
+
+// SH (degree D) -> rgb, DGR forward.cu:20-71.  sh points at this Gaussian's [M,3] block.
+__device__ __forceinline__ void sh_to_rgb(int D, const float* __restrict__ sh, float dx, float dy, float dz,
+	float* rgb)
+{
+	const float len = fsqrt(ffma(dz, dz, ffma(dx, dx, fmul(dy, dy))));
+	const float x = fdiv(dx, len), y = fdiv(dy, len), z = fdiv(dz, len);
+#pragma unroll
+	for (int c = 0; c < 3; c++)
+		rgb[c] = fmul(__ldg(sh + c), MOSS_SH_C0);
+	if (D > 0) {
+		const float a1 = fmul(y, MOSS_SH_C1), a2 = fmul(z, MOSS_SH_C1), a3 = fmul(x, MOSS_SH_C1);
+#pragma unroll
+		for (int c = 0; c < 3; c++) {
+			float r = fsub(rgb[c], fmul(a1, __ldg(sh + 3 + c)));
+			r = ffma(a2, __ldg(sh + 6 + c), r);
+			rgb[c] = fsub(r, fmul(a3, __ldg(sh + 9 + c)));
+		}
+		if (D > 1) {
+			const float xx = fmul(x, x), yy = fmul(y, y), zz = fmul(z, z);
+			const float xy = fmul(x, y), yz = fmul(y, z), xz = fmul(x, z);
+			const float zz2 = fadd(zz, zz);
+			const float xx_yy = fsub(xx, yy);
+			const float b4 = fmul(xy, MOSS_SH_C2_0);
+			const float b5 = fmul(yz, MOSS_SH_C2_1);
+			const float b6 = fmul(fsub(fsub(zz2, xx), yy), MOSS_SH_C2_2);
+			const float b7 = fmul(xz, MOSS_SH_C2_3);
+			const float b8 = fmul(xx_yy, MOSS_SH_C2_4);
+#pragma unroll
+			for (int c = 0; c < 3; c++) {
+				float r = ffma(b4, __ldg(sh + 12 + c), rgb[c]);
+				r = ffma(b5, __ldg(sh + 15 + c), r);
+				r = ffma(b6, __ldg(sh + 18 + c), r);
+				r = ffma(b7, __ldg(sh + 21 + c), r);
+				rgb[c] = ffma(b8, __ldg(sh + 24 + c), r);
+			}
+			if (D > 2) {
+				const float xx3 = fmul(xx, 3.f), yy3 = fmul(yy, 3.f);
+				const float zz4_xx_yy = fsub(fsub(fmul(zz, 4.f), xx), yy);
+				const float c9 = fmul(fmul(y, MOSS_SH_C3_0), fsub(xx3, yy));
+				const float c10 = fmul(z, fmul(xy, MOSS_SH_C3_1));
+				const float c11 = fmul(fmul(y, MOSS_SH_C3_2), zz4_xx_yy);
+				const float c12 = fmul(fmul(z, MOSS_SH_C3_3), fsub(fsub(zz2, xx3), yy3));
+				const float c13 = fmul(fmul(x, MOSS_SH_C3_4), zz4_xx_yy);
+				const float c14 = fmul(fmul(z, MOSS_SH_C3_5), xx_yy);
+				const float c15 = fmul(fmul(x, MOSS_SH_C3_6), fsub(xx, yy3));
+#pragma unroll
+				for (int c = 0; c < 3; c++) {
+					float r = ffma(c9, __ldg(sh + 27 + c), rgb[c]);
+					r = ffma(c10, __ldg(sh + 30 + c), r);
+					r = ffma(c11, __ldg(sh + 33 + c), r);
+					r = ffma(c12, __ldg(sh + 36 + c), r);
+					r = ffma(c13, __ldg(sh + 39 + c), r);
+					r = ffma(c14, __ldg(sh + 42 + c), r);
+					rgb[c] = ffma(c15, __ldg(sh + 45 + c), r);
+				}
+			}
+		}
+	}
+#pragma unroll
+	for (int c = 0; c < 3; c++)
+		rgb[c] = fadd(rgb[c], 0.5f);
+}
+
+// ndc -> pixel, evaluated in fp64 like the reference (DGR auxiliary.h:41-44).
+__device__ __forceinline__ float ndc_to_pix(float v, int S)
+{
+	return (float)(__dmul_rn(__fma_rn(__dadd_rn((double)v, 1.0), (double)S, -1.0), 0.5));
+}
+
+constexpr int PRE_THREADS = 256;
+
+__global__ void __launch_bounds__(PRE_THREADS)
+preprocess_forward_kernel(int P, ViewParams vp,
+	const float* __restrict__ means3D, const float* __restrict__ shs, const float* __restrict__ colors_precomp,
+	const float* __restrict__ opacities, const float* __restrict__ scales, const float* __restrict__ rotations,
+	const float* __restrict__ cov3D_precomp, int prefiltered,
+	GeomWS g, uint32_t* __restrict__ tile_count, int* __restrict__ radii)
+{
+	__shared__ float s_view[16], s_proj[16], s_cam[3];
+	if (threadIdx.x < 16) s_view[threadIdx.x] = vp.view[threadIdx.x];
+	else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
+	else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
+	__syncthreads();
+
+	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
+	if (idx >= P) return;
+
+	int my_radius = 0;
+	uint32_t touched = 0;
+	const float px = means3D[3 * idx], py = means3D[3 * idx + 1], pz = means3D[3 * idx + 2];
+	const float vz = affine_row(px, py, pz, s_view[2], s_view[6], s_view[10], s_view[14]);
+
+	do {
+		if (vz <= 0.2f) {  // near cull, DGR auxiliary.h:154
+			if (prefiltered) {
+				printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+				__trap();
+			}
+			break;
+		}
+		const float hx = affine_row(px, py, pz, s_proj[0], s_proj[4], s_proj[8], s_proj[12]);
+		const float hy = affine_row(px, py, pz, s_proj[1], s_proj[5], s_proj[9], s_proj[13]);
+		const float hw = affine_row(px, py, pz, s_proj[3], s_proj[7], s_proj[11], s_proj[15]);
+		const float p_w = frcp(fadd(hw, 0.0000001f));
+		const float ndc_x = fmul(hx, p_w), ndc_y = fmul(hy, p_w);
+
+		float c3[6];
+		if (cov3D_precomp != nullptr) {
+#pragma unroll
+			for (int k = 0; k < 6; k++) c3[k] = cov3D_precomp[6 * idx + k];
+		} else {
+			const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+			cov3d_from_scale_rot(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2], vp.scale_modifier,
+				q.x, q.y, q.z, q.w, c3);
+#pragma unroll
+			for (int k = 0; k < 6; k++) g.cov3D[6 * idx + k] = c3[k];
+		}
+
+		const float tx = affine_row(px, py, pz, s_view[0], s_view[4], s_view[8], s_view[12]);
+		const float ty = affine_row(px, py, pz, s_view[1], s_view[5], s_view[9], s_view[13]);
+		const Float3 cov = cov2d_ewa(tx, ty, vz, s_view, vp.focal_x, vp.focal_y, vp.tanfovx, vp.tanfovy, c3);
+
+		const float det = fsub(fmul(cov.x, cov.z), fmul(cov.y, cov.y));
+		if (det == 0.0f) break;
+		const float det_inv = frcp(det);
+		const float conic_x = fmul(cov.z, det_inv);
+		const float conic_y = fmul(det_inv, -cov.y);
+		const float conic_z = fmul(cov.x, det_inv);
+
+		const float mid = fmul(fadd(cov.x, cov.z), 0.5f);
+		const float sq = fsqrt(fmaxf(fsub(fmul(mid, mid), det), 0.1f));
+		const float lmax = fmaxf(fadd(mid, sq), fsub(mid, sq));
+		const float radius_f = ceilf(fmul(fsqrt(lmax), 3.f));
+		const float pix_x = ndc_to_pix(ndc_x, vp.W), pix_y = ndc_to_pix(ndc_y, vp.H);
+		const int ri = (int)radius_f;              // DGR auxiliary.h:46 (float -> int max_radius)
+		const float rf = (float)ri;
+		const uint32_t gx = vp.grid_x, gy = vp.grid_y;
+		const uint32_t rminx = min(gx, (uint32_t)max(0, (int)fmul(fsub(pix_x, rf), 0.0625f)));
+		const uint32_t rminy = min(gy, (uint32_t)max(0, (int)fmul(fsub(pix_y, rf), 0.0625f)));
+		const uint32_t rmaxx = min(gx, (uint32_t)max(0, (int)fmul(fadd(fadd(fadd(pix_x, rf), 16.f), -1.f), 0.0625f)));
+		const uint32_t rmaxy = min(gy, (uint32_t)max(0, (int)fmul(fadd(fadd(fadd(pix_y, rf), 16.f), -1.f), 0.0625f)));
+		const uint32_t area = (rmaxx - rminx) * (rmaxy - rminy);
+		if (area == 0) break;
+
+		float rgb[3];
+		uint8_t clamp_bits = 0;
+		if (colors_precomp == nullptr) {
+			sh_to_rgb(vp.D, shs + (size_t)idx * vp.M * 3, fsub(px, s_cam[0]), fsub(py, s_cam[1]), fsub(pz, s_cam[2]), rgb);
+#pragma unroll
+			for (int c = 0; c < 3; c++) {
+				if (rgb[c] < 0.f) { clamp_bits |= (1u << c); rgb[c] = 0.f; }
+			}
+		} else {
+#pragma unroll
+			for (int c = 0; c < 3; c++) rgb[c] = colors_precomp[3 * idx + c];
+		}
+
+		g.depths[idx] = vz;
+		g.means2D[idx] = make_float2(pix_x, pix_y);
+		g.conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, opacities[idx]);
+		g.feat[idx] = make_float4(rgb[0], rgb[1], rgb[2], vz);
+		g.clamped[idx] = clamp_bits;
+		g.rect[idx] = make_ushort4((unsigned short)rminx, (unsigned short)rminy, (unsigned short)rmaxx, (unsigned short)rmaxy);
+		my_radius = ri;
+		touched = area;
+		// bin: one counter per tile (replaces the per-Gaussian scan + key duplication + global sort)
+		for (uint32_t y = rminy; y < rmaxy; y++)
+			for (uint32_t x = rminx; x < rmaxx; x++)
+				atomicAdd(&tile_count[y * gx + x], 1u);
+	} while (false);
+
+	radii[idx] = my_radius;
+	g.tiles_touched[idx] = touched;
+}
+
+// present[i] = view.z > 0.2   (DGR rasterizer_impl.cu:54-66 with auxiliary.h:139-164)
+__global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
+	uint8_t* __restrict__ present)
+{
+	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+	if (idx >= P) return;
+	const float vz = affine_row(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2],
+		view[2], view[6], view[10], view[14]);
+	present[idx] = !(vz <= 0.2f);
+}
+
+} // namespace moss

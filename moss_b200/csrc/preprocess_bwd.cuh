@@ -1,0 +1,248 @@
+// K7: per-Gaussian backward preprocess -- one fused kernel for what the reference runs as two
+// (computeCov2DCUDA, DGR/cuda_rasterizer/backward.cu:144-274, then preprocessCUDA, :346-396, with the SH and
+// cov3D chain rules :20-139 and :278-341).  Every output row is written (zeros for culled Gaussians and for
+// SH coefficients above the active degree), so the caller never zero-fills dL_dmean3D / dL_dcov3D / dL_dsh /
+// dL_dscale / dL_drot (the reference memsets 9 tensors per call, DGR/rasterize_points.cu:158-166).
+// Gradients are toleranced (1e-3 relative), so plain fp32 expressions are used here.
+#pragma once
+#include "common.cuh"
+#include "preprocess.cuh"
+
+namespace moss {
+
+__global__ void __launch_bounds__(PRE_THREADS)
+preprocess_backward_kernel(int P, ViewParams vp,
+	const float* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
+	const float* __restrict__ scales, const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
+	GeomWS g,
+	const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconic, const float* __restrict__ dL_dcolor,
+	float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
+	float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
+{
+	__shared__ float v[16], pr[16], s_cam[3];
+	if (threadIdx.x < 16) v[threadIdx.x] = vp.view[threadIdx.x];
+	else if (threadIdx.x < 32) pr[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
+	else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
+	__syncthreads();
+
+	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
+	if (idx >= P) return;
+	const int M = vp.M, D = vp.D;
+
+	if (!(radii[idx] > 0)) {
+#pragma unroll
+		for (int k = 0; k < 3; k++) dL_dmean3D[3 * idx + k] = 0.f;
+#pragma unroll
+		for (int k = 0; k < 6; k++) dL_dcov3D[6 * idx + k] = 0.f;
+		if (shs) for (int k = 0; k < 3 * M; k++) dL_dsh[(size_t)idx * 3 * M + k] = 0.f;
+		if (scales) {
+#pragma unroll
+			for (int k = 0; k < 3; k++) dL_dscale[3 * idx + k] = 0.f;
+			reinterpret_cast<float4*>(dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+		}
+		return;
+	}
+
+	const float mx = means3D[3 * idx], my = means3D[3 * idx + 1], mz = means3D[3 * idx + 2];
+	const float* c3 = cov3D_precomp ? (cov3D_precomp + 6 * idx) : (g.cov3D + 6 * idx);
+	const float V0 = c3[0], V1 = c3[1], V2 = c3[2], V3 = c3[3], V4 = c3[4], V5 = c3[5];
+
+	// ---- conic -> cov2D -> cov3D and mean (through J) ----------------------------------------------
+	const float dcx = dL_dconic[4 * idx], dcy = dL_dconic[4 * idx + 1], dcz = dL_dconic[4 * idx + 3];
+	float tx = v[0] * mx + v[4] * my + v[8] * mz + v[12];
+	float ty = v[1] * mx + v[5] * my + v[9] * mz + v[13];
+	const float tz = v[2] * mx + v[6] * my + v[10] * mz + v[14];
+	const float limx = 1.3f * vp.tanfovx, limy = 1.3f * vp.tanfovy;
+	const float txtz = tx / tz, tytz = ty / tz;
+	tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
+	ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
+	const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+	const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+	const float hx = vp.focal_x, hy = vp.focal_y;
+
+	const float J00 = hx / tz, J02 = -(hx * tx) / (tz * tz);
+	const float J11 = hy / tz, J12 = -(hy * ty) / (tz * tz);
+	// T = W*J : two non-zero columns (T0*, T1*)
+	const float T00 = v[0] * J00 + v[2] * J02, T01 = v[4] * J00 + v[6] * J02, T02 = v[8] * J00 + v[10] * J02;
+	const float T10 = v[1] * J11 + v[2] * J12, T11 = v[5] * J11 + v[6] * J12, T12 = v[9] * J11 + v[10] * J12;
+	// V*T columns
+	const float VT00 = T00 * V0 + T01 * V1 + T02 * V2;
+	const float VT01 = T00 * V1 + T01 * V3 + T02 * V4;
+	const float VT02 = T00 * V2 + T01 * V4 + T02 * V5;
+	const float VT10 = T10 * V0 + T11 * V1 + T12 * V2;
+	const float VT11 = T10 * V1 + T11 * V3 + T12 * V4;
+	const float VT12 = T10 * V2 + T11 * V4 + T12 * V5;
+	const float a = (T00 * VT00 + T01 * VT01 + T02 * VT02) + 0.3f;
+	const float bq = T00 * VT10 + T01 * VT11 + T02 * VT12;
+	const float c = (T10 * VT10 + T11 * VT11 + T12 * VT12) + 0.3f;
+
+	const float denom = a * c - bq * bq;
+	float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
+	const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+	float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+	if (denom2inv != 0.f) {
+		dL_da = denom2inv * (-c * c * dcx + 2 * bq * c * dcy + (denom - a * c) * dcz);
+		dL_dc = denom2inv * (-a * a * dcz + 2 * a * bq * dcy + (denom - a * c) * dcx);
+		dL_db = denom2inv * 2 * (bq * c * dcx - (denom + 2 * bq * bq) * dcy + a * bq * dcz);
+		dcov[0] = T00 * T00 * dL_da + T00 * T10 * dL_db + T10 * T10 * dL_dc;
+		dcov[3] = T01 * T01 * dL_da + T01 * T11 * dL_db + T11 * T11 * dL_dc;
+		dcov[5] = T02 * T02 * dL_da + T02 * T12 * dL_db + T12 * T12 * dL_dc;
+		dcov[1] = 2 * T00 * T01 * dL_da + (T00 * T11 + T01 * T10) * dL_db + 2 * T10 * T11 * dL_dc;
+		dcov[2] = 2 * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + 2 * T10 * T12 * dL_dc;
+		dcov[4] = 2 * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2 * T11 * T12 * dL_dc;
+	}
+#pragma unroll
+	for (int k = 0; k < 6; k++) dL_dcov3D[6 * idx + k] = dcov[k];
+
+	const float dT00 = 2 * VT00 * dL_da + VT10 * dL_db;
+	const float dT01 = 2 * VT01 * dL_da + VT11 * dL_db;
+	const float dT02 = 2 * VT02 * dL_da + VT12 * dL_db;
+	const float dT10 = 2 * VT10 * dL_dc + VT00 * dL_db;
+	const float dT11 = 2 * VT11 * dL_dc + VT01 * dL_db;
+	const float dT12 = 2 * VT12 * dL_dc + VT02 * dL_db;
+	const float dJ00 = v[0] * dT00 + v[4] * dT01 + v[8] * dT02;
+	const float dJ02 = v[2] * dT00 + v[6] * dT01 + v[10] * dT02;
+	const float dJ11 = v[1] * dT10 + v[5] * dT11 + v[9] * dT12;
+	const float dJ12 = v[2] * dT10 + v[6] * dT11 + v[10] * dT12;
+	const float itz = 1.f / tz, itz2 = itz * itz, itz3 = itz2 * itz;
+	const float dtx = x_grad_mul * -hx * itz2 * dJ02;
+	const float dty = y_grad_mul * -hy * itz2 * dJ12;
+	// z-dependence of the frustum clamp is ignored exactly like the reference (backward.cu:264)
+	const float dtz = -hx * itz2 * dJ00 - hy * itz2 * dJ11 + (2 * hx * tx) * itz3 * dJ02 + (2 * hy * ty) * itz3 * dJ12;
+	float gmx = v[0] * dtx + v[1] * dty + v[2] * dtz;
+	float gmy = v[4] * dtx + v[5] * dty + v[6] * dtz;
+	float gmz = v[8] * dtx + v[9] * dty + v[10] * dtz;
+
+	// ---- 2D mean -> 3D mean through the projection ---------------------------------------------------
+	{
+		const float m_w = 1.0f / ((pr[3] * mx + pr[7] * my + pr[11] * mz + pr[15]) + 0.0000001f);
+		const float mul1 = (pr[0] * mx + pr[4] * my + pr[8] * mz + pr[12]) * m_w * m_w;
+		const float mul2 = (pr[1] * mx + pr[5] * my + pr[9] * mz + pr[13]) * m_w * m_w;
+		const float d2x = dL_dmean2D[3 * idx], d2y = dL_dmean2D[3 * idx + 1];
+		gmx += (pr[0] * m_w - pr[3] * mul1) * d2x + (pr[1] * m_w - pr[3] * mul2) * d2y;
+		gmy += (pr[4] * m_w - pr[7] * mul1) * d2x + (pr[5] * m_w - pr[7] * mul2) * d2y;
+		gmz += (pr[8] * m_w - pr[11] * mul1) * d2x + (pr[9] * m_w - pr[11] * mul2) * d2y;
+	}
+
+	// ---- colour -> SH coefficients and view direction -> mean ---------------------------------------
+	if (shs) {
+		const float* sh = shs + (size_t)idx * 3 * M;
+		float* dsh = dL_dsh + (size_t)idx * 3 * M;
+		const float ox = mx - s_cam[0], oy = my - s_cam[1], oz = mz - s_cam[2];
+		const float ilen = 1.f / sqrtf(ox * ox + oy * oy + oz * oz);
+		const float x = ox * ilen, y = oy * ilen, z = oz * ilen;
+		const uint8_t cl = g.clamped[idx];
+		float dRGB[3];
+#pragma unroll
+		for (int ch = 0; ch < 3; ch++) dRGB[ch] = ((cl >> ch) & 1) ? 0.f : dL_dcolor[3 * idx + ch];
+
+		float basis[16];
+#pragma unroll
+		for (int k = 0; k < 16; k++) basis[k] = 0.f;
+		float dx3[3] = {0.f, 0.f, 0.f}, dy3[3] = {0.f, 0.f, 0.f}, dz3[3] = {0.f, 0.f, 0.f};
+		basis[0] = MOSS_SH_C0;
+		if (D > 0) {
+			basis[1] = -MOSS_SH_C1 * y; basis[2] = MOSS_SH_C1 * z; basis[3] = -MOSS_SH_C1 * x;
+#pragma unroll
+			for (int ch = 0; ch < 3; ch++) {
+				dx3[ch] = -MOSS_SH_C1 * sh[9 + ch];
+				dy3[ch] = -MOSS_SH_C1 * sh[3 + ch];
+				dz3[ch] = MOSS_SH_C1 * sh[6 + ch];
+			}
+			if (D > 1) {
+				const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+				basis[4] = MOSS_SH_C2_0 * xy; basis[5] = MOSS_SH_C2_1 * yz;
+				basis[6] = MOSS_SH_C2_2 * (2.f * zz - xx - yy);
+				basis[7] = MOSS_SH_C2_3 * xz; basis[8] = MOSS_SH_C2_4 * (xx - yy);
+#pragma unroll
+				for (int ch = 0; ch < 3; ch++) {
+					const float s4 = sh[12 + ch], s5 = sh[15 + ch], s6 = sh[18 + ch], s7 = sh[21 + ch], s8 = sh[24 + ch];
+					dx3[ch] += MOSS_SH_C2_0 * y * s4 + MOSS_SH_C2_2 * 2.f * -x * s6 + MOSS_SH_C2_3 * z * s7 + MOSS_SH_C2_4 * 2.f * x * s8;
+					dy3[ch] += MOSS_SH_C2_0 * x * s4 + MOSS_SH_C2_1 * z * s5 + MOSS_SH_C2_2 * 2.f * -y * s6 + MOSS_SH_C2_4 * 2.f * -y * s8;
+					dz3[ch] += MOSS_SH_C2_1 * y * s5 + MOSS_SH_C2_2 * 2.f * 2.f * z * s6 + MOSS_SH_C2_3 * x * s7;
+				}
+				if (D > 2) {
+					basis[9] = MOSS_SH_C3_0 * y * (3.f * xx - yy);
+					basis[10] = MOSS_SH_C3_1 * xy * z;
+					basis[11] = MOSS_SH_C3_2 * y * (4.f * zz - xx - yy);
+					basis[12] = MOSS_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+					basis[13] = MOSS_SH_C3_4 * x * (4.f * zz - xx - yy);
+					basis[14] = MOSS_SH_C3_5 * z * (xx - yy);
+					basis[15] = MOSS_SH_C3_6 * x * (xx - 3.f * yy);
+#pragma unroll
+					for (int ch = 0; ch < 3; ch++) {
+						const float s9 = sh[27 + ch], s10 = sh[30 + ch], s11 = sh[33 + ch], s12 = sh[36 + ch],
+							s13 = sh[39 + ch], s14 = sh[42 + ch], s15 = sh[45 + ch];
+						dx3[ch] += MOSS_SH_C3_0 * s9 * 3.f * 2.f * xy + MOSS_SH_C3_1 * s10 * yz + MOSS_SH_C3_2 * s11 * -2.f * xy +
+							MOSS_SH_C3_3 * s12 * -3.f * 2.f * xz + MOSS_SH_C3_4 * s13 * (-3.f * xx + 4.f * zz - yy) +
+							MOSS_SH_C3_5 * s14 * 2.f * xz + MOSS_SH_C3_6 * s15 * 3.f * (xx - yy);
+						dy3[ch] += MOSS_SH_C3_0 * s9 * 3.f * (xx - yy) + MOSS_SH_C3_1 * s10 * xz +
+							MOSS_SH_C3_2 * s11 * (-3.f * yy + 4.f * zz - xx) + MOSS_SH_C3_3 * s12 * -3.f * 2.f * yz +
+							MOSS_SH_C3_4 * s13 * -2.f * xy + MOSS_SH_C3_5 * s14 * -2.f * yz + MOSS_SH_C3_6 * s15 * -3.f * 2.f * xy;
+						dz3[ch] += MOSS_SH_C3_1 * s10 * xy + MOSS_SH_C3_2 * s11 * 4.f * 2.f * yz +
+							MOSS_SH_C3_3 * s12 * 3.f * (2.f * zz - xx - yy) + MOSS_SH_C3_4 * s13 * 4.f * 2.f * xz +
+							MOSS_SH_C3_5 * s14 * (xx - yy);
+					}
+				}
+			}
+		}
+		const int ncoef = (D + 1) * (D + 1);
+#pragma unroll
+		for (int k = 0; k < 16; k++) {
+			if (k < M) {
+				const float bk = (k < ncoef) ? basis[k] : 0.f;
+				dsh[3 * k] = bk * dRGB[0]; dsh[3 * k + 1] = bk * dRGB[1]; dsh[3 * k + 2] = bk * dRGB[2];
+			}
+		}
+		for (int k = 16; k < M; k++) { dsh[3 * k] = 0.f; dsh[3 * k + 1] = 0.f; dsh[3 * k + 2] = 0.f; }
+
+		const float ddx = dx3[0] * dRGB[0] + dx3[1] * dRGB[1] + dx3[2] * dRGB[2];
+		const float ddy = dy3[0] * dRGB[0] + dy3[1] * dRGB[1] + dy3[2] * dRGB[2];
+		const float ddz = dz3[0] * dRGB[0] + dz3[1] * dRGB[1] + dz3[2] * dRGB[2];
+		// d normalize(v)/dv applied to dL_ddir (DGR auxiliary.h:107-117)
+		const float sum2 = ox * ox + oy * oy + oz * oz;
+		const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+		gmx += ((sum2 - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * invsum32;
+		gmy += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * invsum32;
+		gmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
+	}
+	dL_dmean3D[3 * idx] = gmx; dL_dmean3D[3 * idx + 1] = gmy; dL_dmean3D[3 * idx + 2] = gmz;
+
+	// ---- cov3D -> scale, (un-normalised) quaternion --------------------------------------------------
+	if (scales) {
+		const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+		const float r = q.x, x = q.y, y = q.z, z = q.w;
+		const float s[3] = {vp.scale_modifier * scales[3 * idx], vp.scale_modifier * scales[3 * idx + 1],
+			vp.scale_modifier * scales[3 * idx + 2]};
+		// R[i][j]: column i, row j (GLM listing of DGR backward.cu:288-292)
+		const float R[3][3] = {
+			{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+			{2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+			{2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+		const float dS[3][3] = {
+			{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
+			{0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
+			{0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
+		// dL_dM[i][j] = sum_k 2*M[k][j]*dS[i][k],  M[k][j] = s_j * R[k][j];  dMt[a][b] = dL_dM[b][a]
+		float dMt[3][3];
+#pragma unroll
+		for (int i = 0; i < 3; i++)
+#pragma unroll
+			for (int j = 0; j < 3; j++)
+				dMt[j][i] = 2.0f * s[j] * R[0][j] * dS[i][0] + 2.0f * s[j] * R[1][j] * dS[i][1] + 2.0f * s[j] * R[2][j] * dS[i][2];
+		// dL_dscale_k = dot(Rt[k], dMt[k]),  Rt[k][j] = R[j][k]   (not multiplied by the modifier, as the reference)
+#pragma unroll
+		for (int k = 0; k < 3; k++)
+			dL_dscale[3 * idx + k] = R[0][k] * dMt[k][0] + R[1][k] * dMt[k][1] + R[2][k] * dMt[k][2];
+#pragma unroll
+		for (int k = 0; k < 3; k++) { dMt[k][0] *= s[k]; dMt[k][1] *= s[k]; dMt[k][2] *= s[k]; }
+		float4 dq;
+		dq.x = 2 * z * (dMt[0][1] - dMt[1][0]) + 2 * y * (dMt[2][0] - dMt[0][2]) + 2 * x * (dMt[1][2] - dMt[2][1]);
+		dq.y = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) - 4 * x * (dMt[2][2] + dMt[1][1]);
+		dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
+		dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
+		reinterpret_cast<float4*>(dL_drot)[idx] = dq;   // no normalisation Jacobian (DGR backward.cu:340)
+	}
+}
+
+} // namespace moss

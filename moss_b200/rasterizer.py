@@ -1,0 +1,280 @@
+"""Host-side mirror of the vendored ``diff_gaussian_rasterization`` Python API.
+
+Same names, argument meaning, return tuple and error behaviour as
+DGR/diff_gaussian_rasterization/__init__.py (``GaussianRasterizationSettings`` :160-172,
+``GaussianRasterizer`` :174-223, ``rasterize_gaussians`` :21-42, ``_RasterizeGaussians`` :44-158), so
+``gaussian_renderer/__init__.py::render()`` (:16, :36-55, :112-120) runs unchanged.  Underneath, torch only
+provides device memory and the current stream; all compute is the sm_100a C-ABI library (no fallback).
+
+Differences that are invisible through the API:
+  * launches go to torch's CURRENT stream (the reference uses the legacy default stream);
+  * no blocking D2H copy in the middle of the forward, no per-call zero-fills of outputs;
+  * the three opaque state tensors are caller-owned workspaces (`geom+image` in one allocation, `binning`).
+"""
+from typing import NamedTuple
+import ctypes as C
+
+import torch
+import torch.nn as nn
+
+from . import _abi
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+
+
+def _align(n, a=256):
+    return (n + a - 1) // a * a
+
+
+def _ptr(t):
+    """Device pointer of a tensor, or NULL for the reference's empty-tensor placeholders."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32c(t, name):
+    if t.numel() == 0:
+        return t
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32")
+    return t.contiguous()
+
+
+# remembered instance counts so that the binning workspace is right-sized without a host sync
+_capacity_hint = {}
+
+
+class RasterState:
+    """Workspaces + scene descriptor of one forward call (kept alive for the backward)."""
+    __slots__ = ("scene", "ws", "binning", "flags", "num_rendered", "keep")
+
+    def __init__(self):
+        self.scene = _abi.MossScene()
+        self.ws = None
+        self.binning = None
+        self.flags = 0
+        self.num_rendered = 0
+        self.keep = None
+
+
+def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings,
+                flags=0):
+    """Forward through the C ABI.  Returns (color, radii, depth, alpha, RasterState)."""
+    lib = _abi.load()
+    rs = raster_settings
+    if means3D.ndim != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")   # DGR/rasterize_points.cu:57-59
+    if not means3D.is_cuda:
+        raise RuntimeError("moss_b200 rasterizer needs CUDA tensors (there is no CPU path)")
+    dev = means3D.device
+    means3D = _f32c(means3D, "means3D")
+    sh = _f32c(sh, "sh"); colors_precomp = _f32c(colors_precomp, "colors_precomp")
+    opacities = _f32c(opacities, "opacities"); scales = _f32c(scales, "scales")
+    rotations = _f32c(rotations, "rotations"); cov3Ds_precomp = _f32c(cov3Ds_precomp, "cov3Ds_precomp")
+    bg = _f32c(rs.bg, "bg"); view = _f32c(rs.viewmatrix, "viewmatrix")
+    proj = _f32c(rs.projmatrix, "projmatrix"); campos = _f32c(rs.campos, "campos")
+
+    P = means3D.shape[0]
+    H, W = int(rs.image_height), int(rs.image_width)
+    M = sh.shape[1] if sh.numel() != 0 else 0
+    if rs.debug:
+        flags |= _abi.FLAG_DEBUG
+    export = 1 if (flags & _abi.FLAG_EXPORT_KEYS) else 0
+
+    with torch.cuda.device(dev):
+        out = torch.empty((5, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        gbytes = _align(lib.moss_geom_workspace_bytes(P))
+        ibytes = lib.moss_image_workspace_bytes(W, H)
+        ws = torch.empty((gbytes + ibytes,), dtype=torch.uint8, device=dev)
+        key = (P, W, H, dev.index)
+        cap = _capacity_hint.get(key, 0)
+        cap = max(int(cap * 1.25) + 4096, 4 * P + 4096)
+        st = RasterState()
+        sc = st.scene
+        sc.P, sc.D, sc.M, sc.W, sc.H = P, int(rs.sh_degree), M, W, H
+        sc.bg = _ptr(bg); sc.means3D = _ptr(means3D); sc.shs = _ptr(sh); sc.colors_precomp = _ptr(colors_precomp)
+        sc.opacities = _ptr(opacities); sc.scales = _ptr(scales); sc.rotations = _ptr(rotations)
+        sc.cov3D_precomp = _ptr(cov3Ds_precomp); sc.viewmatrix = _ptr(view); sc.projmatrix = _ptr(proj)
+        sc.campos = _ptr(campos)
+        sc.scale_modifier = float(rs.scale_modifier); sc.tanfovx = float(rs.tanfovx); sc.tanfovy = float(rs.tanfovy)
+        sc.prefiltered = 1 if rs.prefiltered else 0
+        sc.geom_ws = ws.data_ptr(); sc.geom_bytes = gbytes
+        sc.image_ws = ws.data_ptr() + gbytes; sc.image_bytes = ibytes
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        nr = C.c_int(0)
+        color, depth, alpha = out[0:3], out[3:4], out[4:5]
+        call_flags = flags
+        while True:
+            bbytes = lib.moss_binning_workspace_bytes_ex(cap, export)
+            binning = torch.empty((bbytes,), dtype=torch.uint8, device=dev)
+            sc.binning_ws = binning.data_ptr(); sc.binning_bytes = bbytes
+            status = lib.moss_rasterize_forward(stream, C.byref(sc), call_flags, color.data_ptr(), depth.data_ptr(),
+                                                alpha.data_ptr(), _ptr(radii), C.byref(nr))
+            if status == _abi.MOSS_ERR_BINNING_OVERFLOW:
+                cap = int(nr.value * 1.25) + 4096
+                call_flags = flags | _abi.FLAG_REBIN
+                continue
+            _abi.check(status, "moss_rasterize_forward")
+            break
+        if nr.value >= 0:
+            _capacity_hint[key] = nr.value
+        st.ws, st.binning, st.flags, st.num_rendered = ws, binning, flags, nr.value
+        # tensors whose device pointers sit in the scene struct must outlive the backward
+        st.keep = (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, bg, view, proj, campos)
+    return color, radii, depth, alpha, st
+
+
+def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0):
+    """Backward through the C ABI.  Returns the 8 gradient tensors in the reference's C++ order
+    (DGR/rasterize_points.cu:205): dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot."""
+    lib = _abi.load()
+    sc = st.scene
+    P, M, H, W = sc.P, sc.M, sc.H, sc.W
+    dev = radii.device
+    with torch.cuda.device(dev):
+        def _g(t, shape):
+            if t is None:
+                return torch.zeros(shape, dtype=torch.float32, device=dev)
+            return _f32c(t, "grad").expand(shape).contiguous() if tuple(t.shape) != tuple(shape) else _f32c(t, "grad")
+        grad_color = _g(grad_color, (3, H, W)); grad_depth = _g(grad_depth, (1, H, W)); grad_alpha = _g(grad_alpha, (1, H, W))
+        acc = torch.zeros((P * 11,), dtype=torch.float32, device=dev)       # atomically accumulated
+        dmeans2D = acc[0:3 * P].view(P, 3)
+        dconic = acc[3 * P:7 * P].view(P, 2, 2)
+        dopacity = acc[7 * P:8 * P].view(P, 1)
+        dcolors = acc[8 * P:11 * P].view(P, 3)
+        has_sh = sc.shs is not None
+        has_sr = sc.scales is not None
+        n_out = P * (3 + 6 + (3 * M if has_sh else 0) + (7 if has_sr else 0))
+        outb = torch.empty((n_out,), dtype=torch.float32, device=dev)        # fully written by K7
+        o = 0
+        dmeans3D = outb[o:o + 3 * P].view(P, 3); o += 3 * P
+        dcov3D = outb[o:o + 6 * P].view(P, 6); o += 6 * P
+        if has_sh:
+            dsh = outb[o:o + 3 * M * P].view(P, M, 3); o += 3 * M * P
+        else:
+            dsh = torch.zeros((P, 0, 3), dtype=torch.float32, device=dev)
+        if has_sr:
+            dscales = outb[o:o + 3 * P].view(P, 3); o += 3 * P
+            drot = outb[o:o + 4 * P].view(P, 4); o += 4 * P
+        else:
+            dscales = torch.zeros((P, 3), dtype=torch.float32, device=dev)
+            drot = torch.zeros((P, 4), dtype=torch.float32, device=dev)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        status = lib.moss_rasterize_backward(
+            stream, C.byref(sc), flags | st.flags, _ptr(radii),
+            grad_color.data_ptr(), grad_depth.data_ptr(), grad_alpha.data_ptr(),
+            _ptr(dmeans2D), _ptr(dconic), _ptr(dopacity), _ptr(dcolors), _ptr(dmeans3D), _ptr(dcov3D),
+            _ptr(dsh) if has_sh else None, _ptr(dscales) if has_sr else None, _ptr(drot) if has_sr else None)
+        _abi.check(status, "moss_rasterize_backward")
+    return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                        raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                     cov3Ds_precomp, raster_settings)
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                raster_settings):
+        color, radii, depth, alpha, st = forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations,
+                                                     cov3Ds_precomp, raster_settings)
+        ctx.raster_settings = raster_settings
+        ctx.num_rendered = st.num_rendered
+        ctx.state = st
+        ctx.mark_non_differentiable(radii)
+        ctx.save_for_backward(radii)
+        return color, radii, depth, alpha
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_radii, grad_depth, grad_alpha):
+        (radii,) = ctx.saved_tensors
+        st = ctx.state
+        (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
+         grad_scales, grad_rotations) = backward_raw(st, radii, grad_out_color, grad_depth, grad_alpha)
+        # same order as DGR/diff_gaussian_rasterization/__init__.py:146-156
+        return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
+                grad_rotations, grad_cov3Ds_precomp, None)
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """bool[P]: view-space z > 0.2 (DGR/diff_gaussian_rasterization/__init__.py:179-188)."""
+        lib = _abi.load()
+        with torch.no_grad():
+            rs = self.raster_settings
+            pos = _f32c(positions, "positions")
+            if not pos.is_cuda:
+                raise RuntimeError("moss_b200 rasterizer needs CUDA tensors (there is no CPU path)")
+            P = pos.shape[0]
+            present = torch.empty((P,), dtype=torch.bool, device=pos.device)
+            view = _f32c(rs.viewmatrix, "viewmatrix"); proj = _f32c(rs.projmatrix, "projmatrix")
+            with torch.cuda.device(pos.device):
+                status = lib.moss_mark_visible(torch.cuda.current_stream(pos.device).cuda_stream, P, _ptr(pos),
+                                               _ptr(view), _ptr(proj), _ptr(present))
+            _abi.check(status, "moss_mark_visible")
+        return present
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        raster_settings = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        empty = torch.Tensor([])
+        shs = empty if shs is None else shs
+        colors_precomp = empty if colors_precomp is None else colors_precomp
+        scales = empty if scales is None else scales
+        rotations = empty if rotations is None else rotations
+        cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                   cov3D_precomp, raster_settings)
+
+
+def export_state(st, name):
+    """Copy one internal state array of a forward call into a fresh tensor (parity tests)."""
+    lib = _abi.load()
+    sc = st.scene
+    P, N = sc.P, sc.W * sc.H
+    T = ((sc.W + 15) // 16) * ((sc.H + 15) // 16)
+    R = max(st.num_rendered, 0)
+    dev = st.ws.device
+    spec = {
+        "depths": (torch.float32, (P,)), "clamped": (torch.uint8, (P, 3)), "means2D": (torch.float32, (P, 2)),
+        "cov3D": (torch.float32, (P, 6)), "conic_opacity": (torch.float32, (P, 4)), "rgb": (torch.float32, (P, 3)),
+        "tiles_touched": (torch.int32, (P,)), "keys_sorted": (torch.int64, (R,)), "point_list": (torch.int32, (R,)),
+        "ranges": (torch.int32, (T, 2)), "n_contrib": (torch.int32, (N,)), "final_T": (torch.float32, (N,)),
+        "counters": (torch.int32, (4,)),
+    }[name]
+    out = torch.empty(spec[1], dtype=spec[0], device=dev)
+    with torch.cuda.device(dev):
+        n = lib.moss_export_state(torch.cuda.current_stream(dev).cuda_stream, C.byref(sc), _abi.STATE[name],
+                                  out.data_ptr(), out.numel() * out.element_size())
+    if n < 0:
+        raise RuntimeError(f"moss_export_state({name}) failed: {lib.moss_error_string(int(-n)).decode()}")
+    return out
