@@ -45,6 +45,14 @@ __device__ __forceinline__ void block_bitonic_sort(KeyPtr a, int n)
 	}
 }
 
+// power = -0.5f*(A dx^2 + C dy^2) - B dx dy  (DGR forward.cu:340, backward.cu:507) in the rounding sequence of
+// the reference's sm_100 SASS: q = fma(dx, dx*A, dy*(dy*C)); power = fma(q, -0.5, -(dy*(dx*B))).
+__device__ __forceinline__ float blend_power(float dx, float dy, const float4& co)
+{
+	const float q = ffma(dx, fmul(dx, co.x), fmul(dy, fmul(dy, co.z)));
+	return ffma(q, -0.5f, -fmul(dy, fmul(dx, co.y)));
+}
+
 __device__ __forceinline__ void pixel_of_thread(int tile_x, int tile_y, int& px, int& py)
 {
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -116,9 +124,7 @@ blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Geo
 			const float2 xy = s_xy[j];
 			const float4 co = s_co[j];
 			const float dx = fsub(xy.x, pxf), dy = fsub(xy.y, pyf);
-			// power = -0.5f*(A dx^2 + C dy^2) - B dx dy     (DGR forward.cu:340)
-			const float power = fsub(fmul(ffma(dx, fmul(dx, co.x), fmul(dy, fmul(dy, co.z))), -0.5f),
-				fmul(dy, fmul(dx, co.y)));
+			const float power = blend_power(dx, dy, co);
 			if (power > 0.0f) continue;
 			const float alpha = fminf(fmul(co.w, expf(power)), 0.99f);
 			if (alpha < 1.0f / 255.0f) continue;
@@ -253,8 +259,7 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 			const float2 xy = s_xy[j];
 			const float4 co = s_co[j];
 			const float dx = xy.x - pxf, dy = xy.y - pyf;
-			const float power = fsub(fmul(ffma(dx, fmul(dx, co.x), fmul(dy, fmul(dy, co.z))), -0.5f),
-				fmul(dy, fmul(dx, co.y)));
+			const float power = blend_power(dx, dy, co);
 			valid = valid && !(power > 0.0f);
 			const float G = expf(power);
 			const float alpha = fminf(fmul(co.w, G), 0.99f);

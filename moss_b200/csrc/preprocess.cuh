@@ -36,22 +36,25 @@ __device__ __forceinline__ void cov3d_from_scale_rot(float sx, float sy, float s
 	float r, float x, float y, float z, float* cov)
 {
 	const float s0 = fmul(mod, sx), s1 = fmul(mod, sy), s2 = fmul(mod, sz);
+	// Rounding sequence read off the reference's sm_100 SASS (ptxas fuses one product of every
+	// "a*b +- c*d" pair that NVVM left unfused): e.g. xy - rz = fma(x, y, -(r*z)).
 	const float yy = fmul(y, y), zz = fmul(z, z);
-	const float xy = fmul(x, y), rz = fmul(r, z);
-	const float xz = fmul(x, z), ry = fmul(r, y);
-	const float yz = fmul(y, z), rx = fmul(r, x);
+	const float xz = fmul(x, z), rx = fmul(r, x), rz = fmul(r, z);
 	const float yy_zz = fadd(yy, zz);
 	const float xx_zz = ffma(x, x, zz);
 	const float xx_yy = ffma(x, x, yy);
+	const float xy_m_rz = ffma(x, y, -rz), xy_p_rz = ffma(x, y, rz);
+	const float ry_p_xz = ffma(r, y, xz), xz_m_ry = ffma(-r, y, xz);
+	const float yz_m_rx = ffma(y, z, -rx), rx_p_yz = ffma(y, z, rx);
 	// R listed the way the reference hands it to glm::mat3 (column i, row j)
 	const float R00 = fsub(1.f, fadd(yy_zz, yy_zz));
-	const float R01 = fmul(2.f, fsub(xy, rz));
-	const float R02 = fmul(2.f, fadd(ry, xz));
-	const float R10 = fmul(2.f, fadd(xy, rz));
+	const float R01 = fadd(xy_m_rz, xy_m_rz);
+	const float R02 = fadd(ry_p_xz, ry_p_xz);
+	const float R10 = fadd(xy_p_rz, xy_p_rz);
 	const float R11 = fsub(1.f, fadd(xx_zz, xx_zz));
-	const float R12 = fmul(2.f, fsub(yz, rx));
-	const float R20 = fmul(2.f, fsub(xz, ry));
-	const float R21 = fmul(2.f, fadd(rx, yz));
+	const float R12 = fadd(yz_m_rx, yz_m_rx);
+	const float R20 = fadd(xz_m_ry, xz_m_ry);
+	const float R21 = fadd(rx_p_yz, rx_p_yz);
 	const float R22 = fsub(1.f, fadd(xx_yy, xx_yy));
 	// M = S * R (S diagonal): M[i][j] = s_j * R[i][j]
 	const float M00 = fmul(s0, R00), M01 = fmul(s1, R01), M02 = fmul(s2, R02);
@@ -116,9 +119,9 @@ __device__ __forceinline__ void sh_to_rgb(int D, const float* __restrict__ sh, f
 		const float a1 = fmul(y, MOSS_SH_C1), a2 = fmul(z, MOSS_SH_C1), a3 = fmul(x, MOSS_SH_C1);
 #pragma unroll
 		for (int c = 0; c < 3; c++) {
-			float r = fsub(rgb[c], fmul(a1, __ldg(sh + 3 + c)));
+			float r = ffma(-a1, __ldg(sh + 3 + c), rgb[c]);
 			r = ffma(a2, __ldg(sh + 6 + c), r);
-			rgb[c] = fsub(r, fmul(a3, __ldg(sh + 9 + c)));
+			rgb[c] = ffma(-a3, __ldg(sh + 9 + c), r);
 		}
 		if (D > 1) {
 			const float xx = fmul(x, x), yy = fmul(y, y), zz = fmul(z, z);
@@ -139,15 +142,16 @@ __device__ __forceinline__ void sh_to_rgb(int D, const float* __restrict__ sh, f
 				rgb[c] = ffma(b8, __ldg(sh + 24 + c), r);
 			}
 			if (D > 2) {
-				const float xx3 = fmul(xx, 3.f), yy3 = fmul(yy, 3.f);
-				const float zz4_xx_yy = fsub(fsub(fmul(zz, 4.f), xx), yy);
-				const float c9 = fmul(fmul(y, MOSS_SH_C3_0), fsub(xx3, yy));
-				const float c10 = fmul(z, fmul(xy, MOSS_SH_C3_1));
+				// fused forms as in the reference's SASS: 3xx-yy = fma(xx,3,-yy); 4zz-xx-yy = fma(zz,4,-xx)-yy;
+				// 2zz-3xx-3yy = fma(yy,-3, fma(xx,-3, 2zz)); xx-3yy = fma(yy,-3,xx)
+				const float zz4_xx_yy = fsub(ffma(zz, 4.f, -xx), yy);
+				const float c9 = fmul(fmul(y, MOSS_SH_C3_0), ffma(xx, 3.f, -yy));
+				const float c10 = fmul(fmul(xy, MOSS_SH_C3_1), z);
 				const float c11 = fmul(fmul(y, MOSS_SH_C3_2), zz4_xx_yy);
-				const float c12 = fmul(fmul(z, MOSS_SH_C3_3), fsub(fsub(zz2, xx3), yy3));
+				const float c12 = fmul(fmul(z, MOSS_SH_C3_3), ffma(yy, -3.f, ffma(xx, -3.f, zz2)));
 				const float c13 = fmul(fmul(x, MOSS_SH_C3_4), zz4_xx_yy);
 				const float c14 = fmul(fmul(z, MOSS_SH_C3_5), xx_yy);
-				const float c15 = fmul(fmul(x, MOSS_SH_C3_6), fsub(xx, yy3));
+				const float c15 = fmul(fmul(x, MOSS_SH_C3_6), ffma(yy, -3.f, xx));
 #pragma unroll
 				for (int c = 0; c < 3; c++) {
 					float r = ffma(c9, __ldg(sh + 27 + c), rgb[c]);
@@ -225,7 +229,7 @@ preprocess_forward_kernel(int P, ViewParams vp,
 		const float ty = affine_row(px, py, pz, s_view[1], s_view[5], s_view[9], s_view[13]);
 		const Float3 cov = cov2d_ewa(tx, ty, vz, s_view, vp.focal_x, vp.focal_y, vp.tanfovx, vp.tanfovy, c3);
 
-		const float det = fsub(fmul(cov.x, cov.z), fmul(cov.y, cov.y));
+		const float det = ffma(cov.x, cov.z, -fmul(cov.y, cov.y));   // SASS: FMUL b*b; FFMA a*c-bb
 		if (det == 0.0f) break;
 		const float det_inv = frcp(det);
 		const float conic_x = fmul(cov.z, det_inv);
@@ -233,7 +237,7 @@ preprocess_forward_kernel(int P, ViewParams vp,
 		const float conic_z = fmul(cov.x, det_inv);
 
 		const float mid = fmul(fadd(cov.x, cov.z), 0.5f);
-		const float sq = fsqrt(fmaxf(fsub(fmul(mid, mid), det), 0.1f));
+		const float sq = fsqrt(fmaxf(ffma(mid, mid, -det), 0.1f));
 		const float lmax = fmaxf(fadd(mid, sq), fsub(mid, sq));
 		const float radius_f = ceilf(fmul(fsqrt(lmax), 3.f));
 		const float pix_x = ndc_to_pix(ndc_x, vp.W), pix_y = ndc_to_pix(ndc_y, vp.H);
