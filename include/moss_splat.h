@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MOSS_ABI_VERSION 1
+#define MOSS_ABI_VERSION 2
 
 /* status codes */
 #define MOSS_OK                  0
@@ -125,7 +125,27 @@ int moss_mark_visible(void* stream, int P, const float* means3D, const float* vi
 #define MOSS_STATE_COUNTERS      15 /* u32[4]: num_rendered, overflow flag, capacity, reserved */
 long long moss_export_state(void* stream, const MossScene* scene, int which, void* dst, long long max_bytes);
 
+/* Instrumentation (no reference counterpart: the reference only has cudaDeviceSynchronize-after-every-launch
+ * debugging, DGR/cuda_rasterizer/auxiliary.h:166-173).
+ *   moss_kernel_launches(): number of kernels this library has launched in this process (bench.py's gpu_launches).
+ *   moss_profile_enable(1): bracket every kernel launch with CUDA events on the launching stream;
+ *   moss_profile_read(): synchronise the recorded events, add their durations per stage into ms[0..MOSS_STAGE_COUNT),
+ *   launch counts into launches[], and clear the pool.  Returns MOSS_OK or MOSS_ERR_CUDA. */
+#define MOSS_STAGE_PREPROCESS      0
+#define MOSS_STAGE_TILE_SCAN       1
+#define MOSS_STAGE_SCATTER         2
+#define MOSS_STAGE_BLEND_FWD       3
+#define MOSS_STAGE_BLEND_BWD       4
+#define MOSS_STAGE_PREPROCESS_BWD  5
+#define MOSS_STAGE_OTHER           6
+#define MOSS_STAGE_COUNT           7
+unsigned long long moss_kernel_launches(void);
+int moss_profile_enable(int on);
+int moss_profile_read(double* ms, unsigned long long* launches);
+const char* moss_stage_name(int stage);
+
 int moss_abi_version(void);
+size_t moss_sizeof_scene(void);
 const char* moss_error_string(int status);
 int moss_last_cuda_error(void);
 

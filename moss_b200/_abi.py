@@ -30,8 +30,10 @@ SYMBOLS = [
     "moss_geom_workspace_bytes", "moss_image_workspace_bytes", "moss_binning_workspace_bytes",
     "moss_binning_workspace_bytes_ex", "moss_binning_capacity", "moss_rasterize_forward",
     "moss_rasterize_backward", "moss_mark_visible", "moss_export_state", "moss_abi_version",
-    "moss_error_string", "moss_last_cuda_error",
+    "moss_error_string", "moss_last_cuda_error", "moss_sizeof_scene", "moss_kernel_launches",
+    "moss_profile_enable", "moss_profile_read", "moss_stage_name",
 ]
+STAGE_COUNT = 7
 
 
 class MossScene(C.Structure):
@@ -88,8 +90,27 @@ def load():
     lib.moss_error_string.restype = C.c_char_p
     lib.moss_error_string.argtypes = [C.c_int]
     lib.moss_last_cuda_error.restype = C.c_int
+    lib.moss_sizeof_scene.restype = C.c_size_t
+    lib.moss_kernel_launches.restype = C.c_ulonglong
+    lib.moss_profile_enable.restype = C.c_int
+    lib.moss_profile_enable.argtypes = [C.c_int]
+    lib.moss_profile_read.restype = C.c_int
+    lib.moss_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
+    lib.moss_stage_name.restype = C.c_char_p
+    lib.moss_stage_name.argtypes = [C.c_int]
+    if lib.moss_sizeof_scene() != C.sizeof(MossScene):
+        raise RuntimeError("moss_b200: MossScene layout mismatch between _abi.py and the library; rebuild")
     _lib = lib
     return lib
+
+
+def profile_read():
+    """-> {stage name: (total ms, launches)} accumulated since the last read (needs moss_profile_enable(1))."""
+    lib = load()
+    ms = (C.c_double * STAGE_COUNT)()
+    n = (C.c_ulonglong * STAGE_COUNT)()
+    check(lib.moss_profile_read(ms, n), "moss_profile_read")
+    return {lib.moss_stage_name(i).decode(): (ms[i], int(n[i])) for i in range(STAGE_COUNT)}
 
 
 def check(status, what="moss"):

@@ -10,6 +10,8 @@
 #include <stdio.h>
 #include <string.h>
 #include <mutex>
+#include <atomic>
+#include <vector>
 #include "../../include/moss_splat.h"
 #include "common.cuh"
 #include "preprocess.cuh"
@@ -33,6 +35,55 @@ inline int check_launch(cudaStream_t s, unsigned flags)
 	return MOSS_OK;
 }
 #define MOSS_CHECK_LAUNCH(s, flags) do { int r__ = check_launch(s, flags); if (r__ != MOSS_OK) return r__; } while (0)
+
+// ---- instrumentation: launch counter + optional per-stage CUDA-event timing ----------------------------
+std::atomic<unsigned long long> g_launches{0};
+struct Profiler {
+	static constexpr int CAP = 8192;
+	bool on = false;
+	std::vector<cudaEvent_t> ev;       // 2 per record
+	std::vector<int> stage;
+	int n = 0;
+	double ms[MOSS_STAGE_COUNT] = {0};
+	unsigned long long cnt[MOSS_STAGE_COUNT] = {0};
+	std::mutex mu;
+	int drain()
+	{
+		for (int i = 0; i < n; i++) {
+			float t = 0.f;
+			if (cudaEventSynchronize(ev[2 * i + 1]) != cudaSuccess) return MOSS_ERR_CUDA;
+			if (cudaEventElapsedTime(&t, ev[2 * i], ev[2 * i + 1]) != cudaSuccess) return MOSS_ERR_CUDA;
+			ms[stage[i]] += t; cnt[stage[i]]++;
+		}
+		n = 0;
+		return MOSS_OK;
+	}
+	void begin(int st, cudaStream_t s)
+	{
+		std::lock_guard<std::mutex> lk(mu);
+		if (n == CAP) drain();
+		if ((int)ev.size() < 2 * (n + 1)) {
+			cudaEvent_t a, b;
+			cudaEventCreate(&a); cudaEventCreate(&b);
+			ev.push_back(a); ev.push_back(b); stage.push_back(st);
+		}
+		stage[n] = st;
+		cudaEventRecord(ev[2 * n], s);
+	}
+	void end(cudaStream_t s)
+	{
+		std::lock_guard<std::mutex> lk(mu);
+		cudaEventRecord(ev[2 * n + 1], s);
+		n++;
+	}
+};
+Profiler g_prof;
+struct StageScope {
+	cudaStream_t s; bool on;
+	StageScope(int stage, cudaStream_t s_) : s(s_), on(g_prof.on) { g_launches.fetch_add(1, std::memory_order_relaxed); if (on) g_prof.begin(stage, s); }
+	~StageScope() { if (on) g_prof.end(s); }
+};
+#define MOSS_STAGE(stage, stream) StageScope stage_scope__(stage, stream)
 
 // Pinned, device-mapped slots through which K2 hands num_rendered to the host without a blocking copy.
 struct HostSlots {
@@ -106,6 +157,31 @@ __global__ void fill_background_kernel(int N, const float* __restrict__ bg, floa
 extern "C" {
 
 int moss_abi_version(void) { return MOSS_ABI_VERSION; }
+size_t moss_sizeof_scene(void) { return sizeof(MossScene); }
+unsigned long long moss_kernel_launches(void) { return g_launches.load(); }
+int moss_profile_enable(int on)
+{
+	std::lock_guard<std::mutex> lk(g_prof.mu);
+	g_prof.on = on != 0;
+	return MOSS_OK;
+}
+int moss_profile_read(double* ms, unsigned long long* launches)
+{
+	std::lock_guard<std::mutex> lk(g_prof.mu);
+	const int r = g_prof.drain();
+	for (int i = 0; i < MOSS_STAGE_COUNT; i++) {
+		if (ms) ms[i] = g_prof.ms[i];
+		if (launches) launches[i] = g_prof.cnt[i];
+		g_prof.ms[i] = 0; g_prof.cnt[i] = 0;
+	}
+	return r;
+}
+const char* moss_stage_name(int stage)
+{
+	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
+		"blend_backward", "preprocess_backward", "other"};
+	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
+}
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
 
 const char* moss_error_string(int status)
@@ -165,7 +241,8 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 	ImageWS im = carve_image((char*)sc->image_ws, (size_t)N, (size_t)T);
 	if (P == 0) {
 		// DGR/rasterize_points.cu:83: nothing rendered; outputs are background / zeros, state says "no contributors"
-		fill_background_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, sc->bg, out_color, out_depth, out_alpha);
+		{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
+		fill_background_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, sc->bg, out_color, out_depth, out_alpha); }
 		MOSS_CUDA_TRY(cudaMemsetAsync(sc->image_ws, 0, moss_image_workspace_bytes(W, H) - 256, stream));
 		MOSS_CHECK_LAUNCH(stream, flags);
 		return MOSS_OK;
@@ -185,24 +262,29 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 
 	if (!(flags & MOSS_FLAG_REBIN)) {
 		MOSS_CUDA_TRY(cudaMemsetAsync(im.tile_count, 0, (size_t)T * sizeof(uint32_t), stream));
+		{ MOSS_STAGE(MOSS_STAGE_PREPROCESS, stream);
 		preprocess_forward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
 			P, vp, sc->means3D, sc->shs, sc->colors_precomp, sc->opacities, sc->scales, sc->rotations,
-			sc->cov3D_precomp, sc->prefiltered, g, im.tile_count, radii);
+			sc->cov3D_precomp, sc->prefiltered, g, im.tile_count, radii); }
 		MOSS_CHECK_LAUNCH(stream, flags);
 		int* host_R = nullptr;
 		if (slot >= 0) MOSS_CUDA_TRY(cudaHostGetDevicePointer((void**)&host_R, g_slots.host + slot, 0));
-		tile_scan_kernel<<<1, SCAN_THREADS, 0, stream>>>(T, im.tile_count, im.ranges, im.counters, capacity, host_R);
+		{ MOSS_STAGE(MOSS_STAGE_TILE_SCAN, stream);
+		tile_scan_kernel<<<1, SCAN_THREADS, 0, stream>>>(T, im.tile_count, im.ranges, im.counters, capacity, host_R); }
 		MOSS_CHECK_LAUNCH(stream, flags);
 		if (slot >= 0) MOSS_CUDA_TRY(cudaEventRecord(g_slots.ev[slot], stream));
 	} else {
-		reset_overflow_kernel<<<1, 1, 0, stream>>>(im.counters, capacity);
+		{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
+		reset_overflow_kernel<<<1, 1, 0, stream>>>(im.counters, capacity); }
 		MOSS_CHECK_LAUNCH(stream, flags);
 	}
 
+	{ MOSS_STAGE(MOSS_STAGE_SCATTER, stream);
 	scatter_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, vp.grid_x, radii, g, im.ranges, im.tile_count,
-		im.counters, b.keys);
+		im.counters, b.keys); }
 	MOSS_CHECK_LAUNCH(stream, flags);
-	blend_forward_kernel<<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+	{ MOSS_STAGE(MOSS_STAGE_BLEND_FWD, stream);
+	blend_forward_kernel<<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 
 	if (flags & MOSS_FLAG_ASYNC) return MOSS_OK;
@@ -244,12 +326,14 @@ int moss_rasterize_backward(void* stream_, const MossScene* sc, unsigned flags, 
 	ImageWS im = carve_image((char*)sc->image_ws, (size_t)N, (size_t)T);
 	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
 
+	{ MOSS_STAGE(MOSS_STAGE_BLEND_BWD, stream);
 	blend_backward_kernel<<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha,
-		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor);
+		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor); }
 	MOSS_CHECK_LAUNCH(stream, flags);
+	{ MOSS_STAGE(MOSS_STAGE_PREPROCESS_BWD, stream);
 	preprocess_backward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
 		P, vp, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
-		dL_dmean2D, dL_dconic, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);
+		dL_dmean2D, dL_dconic, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	return MOSS_OK;
 }
@@ -262,7 +346,8 @@ int moss_mark_visible(void* stream_, int P, const float* means3D, const float* v
 	if (P < 0) return MOSS_ERR_INVALID_ARGUMENT;
 	if (P == 0) return MOSS_OK;
 	if (!means3D || !viewmatrix || !present) return MOSS_ERR_INVALID_ARGUMENT;
-	mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, viewmatrix, present);
+	{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
+	mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, viewmatrix, present); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }

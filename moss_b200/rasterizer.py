@@ -62,7 +62,7 @@ _capacity_hint = {}
 
 class RasterState:
     """Workspaces + scene descriptor of one forward call (kept alive for the backward)."""
-    __slots__ = ("scene", "ws", "binning", "flags", "num_rendered", "keep")
+    __slots__ = ("scene", "ws", "binning", "flags", "num_rendered", "keep", "grad_buf", "param_grad_numel")
 
     def __init__(self):
         self.scene = _abi.MossScene()
@@ -71,6 +71,8 @@ class RasterState:
         self.flags = 0
         self.num_rendered = 0
         self.keep = None
+        self.grad_buf = None
+        self.param_grad_numel = 0
 
 
 def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings,
@@ -141,9 +143,27 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
     return color, radii, depth, alpha, st
 
 
-def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0):
+def grad_layout(P, M, has_sh, has_sr):
+    """Packed gradient buffer (floats): parameter gradients first -- the prefix a data-parallel job all-reduces
+    -- then the two blend-only accumulators.  -> (dict name -> (offset, numel)), param_numel, zero_from, total."""
+    lay, o = {}, 0
+    for name, n in (("means3D", 3 * P), ("cov3D", 6 * P), ("sh", 3 * M * P if has_sh else 0),
+                    ("scales", 3 * P if has_sr else 0), ("rotations", 4 * P if has_sr else 0)):
+        lay[name] = (o, n); o += n
+    zero_from = o                      # everything from here on is accumulated atomically by the blend backward
+    for name, n in (("opacity", P), ("means2D", 3 * P)):
+        lay[name] = (o, n); o += n
+    param_numel = o
+    for name, n in (("colors", 3 * P), ("conic", 4 * P)):
+        lay[name] = (o, n); o += n
+    return lay, param_numel, zero_from, o
+
+
+def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=None):
     """Backward through the C ABI.  Returns the 8 gradient tensors in the reference's C++ order
-    (DGR/rasterize_points.cu:205): dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot."""
+    (DGR/rasterize_points.cu:205): dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot.
+    They are views of ONE packed buffer (kept in ``st.grad_buf``; ``st.param_grad_numel`` floats of parameter
+    gradient lead it), which may be supplied as ``out``."""
     lib = _abi.load()
     sc = st.scene
     P, M, H, W = sc.P, sc.M, sc.H, sc.W
@@ -154,25 +174,20 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0):
                 return torch.zeros(shape, dtype=torch.float32, device=dev)
             return _f32c(t, "grad").expand(shape).contiguous() if tuple(t.shape) != tuple(shape) else _f32c(t, "grad")
         grad_color = _g(grad_color, (3, H, W)); grad_depth = _g(grad_depth, (1, H, W)); grad_alpha = _g(grad_alpha, (1, H, W))
-        acc = torch.zeros((P * 11,), dtype=torch.float32, device=dev)       # atomically accumulated
-        dmeans2D = acc[0:3 * P].view(P, 3)
-        dconic = acc[3 * P:7 * P].view(P, 2, 2)
-        dopacity = acc[7 * P:8 * P].view(P, 1)
-        dcolors = acc[8 * P:11 * P].view(P, 3)
         has_sh = sc.shs is not None
         has_sr = sc.scales is not None
-        n_out = P * (3 + 6 + (3 * M if has_sh else 0) + (7 if has_sr else 0))
-        outb = torch.empty((n_out,), dtype=torch.float32, device=dev)        # fully written by K7
-        o = 0
-        dmeans3D = outb[o:o + 3 * P].view(P, 3); o += 3 * P
-        dcov3D = outb[o:o + 6 * P].view(P, 6); o += 6 * P
-        if has_sh:
-            dsh = outb[o:o + 3 * M * P].view(P, M, 3); o += 3 * M * P
-        else:
-            dsh = torch.zeros((P, 0, 3), dtype=torch.float32, device=dev)
+        lay, param_numel, zero_from, total = grad_layout(P, M, has_sh, has_sr)
+        buf = out if out is not None else torch.empty((total,), dtype=torch.float32, device=dev)
+        buf[zero_from:].zero_()        # K7 fully writes the rest (no 9-tensor zero fill as DGR/rasterize_points.cu:158-166)
+
+        def v(name, *shape):
+            o, n = lay[name]
+            return buf[o:o + n].view(*shape)
+        dmeans3D, dcov3D = v("means3D", P, 3), v("cov3D", P, 6)
+        dopacity, dmeans2D, dcolors, dconic = v("opacity", P, 1), v("means2D", P, 3), v("colors", P, 3), v("conic", P, 2, 2)
+        dsh = v("sh", P, M, 3) if has_sh else torch.zeros((P, 0, 3), dtype=torch.float32, device=dev)
         if has_sr:
-            dscales = outb[o:o + 3 * P].view(P, 3); o += 3 * P
-            drot = outb[o:o + 4 * P].view(P, 4); o += 4 * P
+            dscales, drot = v("scales", P, 3), v("rotations", P, 4)
         else:
             dscales = torch.zeros((P, 3), dtype=torch.float32, device=dev)
             drot = torch.zeros((P, 4), dtype=torch.float32, device=dev)
@@ -183,6 +198,7 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0):
             _ptr(dmeans2D), _ptr(dconic), _ptr(dopacity), _ptr(dcolors), _ptr(dmeans3D), _ptr(dcov3D),
             _ptr(dsh) if has_sh else None, _ptr(dscales) if has_sr else None, _ptr(drot) if has_sr else None)
         _abi.check(status, "moss_rasterize_backward")
+        st.grad_buf, st.param_grad_numel = buf, param_numel
     return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot
 
 
