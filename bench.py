@@ -166,7 +166,7 @@ def run_ours(args, rank, world, dev):
     # clocks
     samples, stop = [], threading.Event()
     th = threading.Thread(target=clock_sampler, args=(dev.index, stop, samples), daemon=True)
-    if rank == 0:
+    if rank == 0 and not os.environ.get("MOSS_NO_SAMPLER"):
         th.start()
         time.sleep(0.3)
 
@@ -213,11 +213,25 @@ def run_ours(args, rank, world, dev):
         for j, r in enumerate(res):
             if j not in out_host:
                 out_host[j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
-            out_host[j].copy_(r, non_blocking=True)
+            out_host[j].copy_(r.detach(), non_blocking=True)   # detach: a pinned tensor must not join the autograd graph
         torch.cuda.current_stream(dev).synchronize()      # the step's result is on the host
+        if os.environ.get("MOSS_TRACE_ALLOC"):
+            ms_ = torch.cuda.memory_stats(dev)
+            print("alloc-trace", i, ms_["num_device_alloc"], ms_["num_device_free"], ms_["reserved_bytes.all.current"] >> 20,
+                  ms_["allocated_bytes.all.current"] >> 20, ms_["num_alloc_retries"], file=sys.stderr)
 
     e2e_steps = max(10, min(args.steps, 200)) if not args.quick else 2
+    if os.environ.get("MOSS_HOST_PROFILE"):          # developer aid: where does the host spend the e2e step?
+        import cProfile, pstats
+        pr = cProfile.Profile(); pr.enable()
+        timed_loop(e2e_step, e2e_steps, 3)
+        pr.disable()
+        pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(14)
+    def n_malloc():
+        return torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
+    m0 = n_malloc()
     e2e_ms, _, _ = timed_loop(e2e_step, e2e_steps, max(3, min(args.warmup, 10)) if not args.quick else 1)
+    e2e_mallocs = n_malloc() - m0
     h2d = sum(host[k].numel() * 4 for k in lay_names)
     d2h = sum(v.numel() * v.element_size() for v in out_host.values())
 
@@ -266,7 +280,7 @@ def run_ours(args, rank, world, dev):
                    "image": [W, H], "views_per_step": world, "l2": "flushed between steps (256 MiB fill, outside the timed events)",
                    "parallelism": f"dp{world} (views sharded, packed parameter gradient all-reduced)" if world > 1 else "single GPU"},
         "e2e": {"value": round(mpix / (e2e_ms_step * 1e-3), 2), "unit": "Mpix/s", "ms_per_step": round(e2e_ms_step, 5),
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps, "device_mallocs": e2e_mallocs},
         "gpu_launches": int(launches_timed),
         "roofline": roof, "clocks": clocks,
     }
@@ -361,7 +375,7 @@ def run_reference(args, rank, world, dev):
         for j, r in enumerate(res):
             if j not in out_host:
                 out_host[j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
-            out_host[j].copy_(r, non_blocking=True)
+            out_host[j].copy_(r.detach(), non_blocking=True)   # detach: a pinned tensor must not join the autograd graph
         torch.cuda.current_stream(dev).synchronize()
 
     def timed_loop(fn, steps, warmup):

@@ -44,6 +44,9 @@ extern "C" {
                                      larger binning workspace moss_binning_workspace_bytes_ex(R, 1) */
 #define MOSS_FLAG_DEBUG       8u  /* synchronise + check after every launch (DGR/cuda_rasterizer/auxiliary.h:166-173) */
 #define MOSS_FLAG_DETERMINISTIC 16u /* backward: fixed-order gradient reduction (bit-reproducible run to run) */
+#define MOSS_FLAG_NO_CULL     32u /* forward: disable the per-patch culling of instances (every instance is offered to
+                                       every pixel of its tile, as DGR forward.cu:330-365 does); results are identical
+                                       by construction -- the flag exists so tests can prove it at full sizes */
 
 /* Workspace sizes.  Replace the reference's `required<GeometryState|ImageState|BinningState>()`
  * (DGR/cuda_rasterizer/rasterizer_impl.h:64-72) and its three grow-callbacks

@@ -21,6 +21,7 @@ FLAG_REBIN = 2
 FLAG_EXPORT_KEYS = 4
 FLAG_DEBUG = 8
 FLAG_DETERMINISTIC = 16
+FLAG_NO_CULL = 32
 
 STATE = dict(depths=0, clamped=1, means2D=2, cov3D=3, conic_opacity=4, rgb=5, tiles_touched=7,
              keys_sorted=9, point_list=11, ranges=12, n_contrib=13, final_T=14, counters=15)

@@ -1,15 +1,23 @@
 // K4: per-tile segment sort + front-to-back alpha blend (forward);  K6: reverse-order blend backward.
 //
 // Blend semantics: DGR/cuda_rasterizer/forward.cu:261-383 (renderCUDA) and backward.cu:399-587.
-// One 256-thread block per 16x16 tile.  New relative to the reference:
+// One 256-thread block per 16x16 tile; a warp owns an 8x4 pixel patch.  New relative to the reference:
 //  * the tile's (depth|id) segment is sorted inside the block (shared memory bitonic network; in-place global
 //    fallback for oversized segments) right before blending, replacing the global radix sort;
 //  * colour+depth are staged in shared memory with the conic (one float4 gather per instance) instead of
 //    per-pair global reads;
-//  * a warp covers an 8x4 pixel patch (not 16x2) so whole warps skip Gaussians that miss their patch;
-//  * backward: gradients are reduced across the warp with a recursive-halving shuffle tree (14 shuffles for
-//    9 values instead of 45) and only then hit global atomics (8 atomics per warp per Gaussian, issued by
-//    8 different lanes), and batches behind the tile's last contributor are never loaded.
+//  * PATCH CULLING: while a batch of 256 instances is staged, the loading thread tests its instance against the
+//    tile's eight 8x4 patches (exact minimum of the conic's quadratic form over the patch rectangle versus the
+//    alpha >= 1/255 threshold, with a conservative margin) and stores an 8-bit hit mask.  Each warp then walks
+//    only the instances that can reach its patch (ballot -> bit scan), which cuts the serial per-pixel loop
+//    ~3x at ZJU splat sizes.  A culled instance is one every pixel of the patch would have skipped through
+//    `alpha < 1/255` (forward.cu:350), so the image stays bit-identical.  The masks are written next to the
+//    sorted list and re-used by the backward;
+//  * the alpha of up to four hits is evaluated independently before the serial transmittance chain (ILP:
+//    the kernel is latency-bound, ~3 warps per scheduler at ZJU shape);
+//  * backward: per-hit gradients are reduced across the warp with a recursive-halving shuffle tree, summed
+//    across the tile's warps in shared memory, and flushed with ONE global atomic per (instance, tile,
+//    component) after each batch; batches behind the tile's last contributor are never loaded.
 // The forward arithmetic uses explicitly-rounded intrinsics in the reference's contraction order so the
 // image is bit-identical on identical sorted lists (thresholds at power>0, alpha<1/255, T<1e-4 make a 1-ulp
 // difference visible).
@@ -19,6 +27,7 @@
 namespace moss {
 
 constexpr int SORT_CAP = 4096;   // instances per tile sorted in shared memory (32 KB)
+constexpr int NPATCH = TILE_PIX / 32;   // 8 warps = 2 (x) by 4 (y) patches of 8x4 pixels
 
 // Ascending bitonic network over a[0..n) with virtual +inf padding up to the next power of two
 // ("flip" formulation: every compare-exchange is ascending, so padding never moves).
@@ -60,6 +69,45 @@ __device__ __forceinline__ void pixel_of_thread(int tile_x, int tile_y, int& px,
 	py = tile_y * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
 }
 
+// Bit w set <=> the instance may reach alpha >= 1/255 on some pixel of patch w (= warp w's 8x4 pixels).
+// alpha = o*exp(-q/2) >= 1/255  <=>  q(d) = A dx^2 + 2B dx dy + C dy^2 <= 2 ln(255 o).  The minimum of the convex q
+// over the patch's offset rectangle [dxl,dxh]x[dyl,dyh] is 0 if the centre is inside; otherwise it lies on an edge
+// facing the centre, i.e. at (ex, clamp(-B ex/C)) or (clamp(-B ey/A), ey) with (ex,ey) the rectangle point
+// nearest to 0 per axis.  Both are feasible points, so min(q1,q2) is exact up to rounding; the margin
+// (0.02 absolute on q, 3e-5 relative on the positive terms) is >30x the fp32 error of either evaluation and
+// of expf/logf, so the test never culls an instance the exact per-pixel test would blend.
+// NaN anywhere -> comparison false -> not culled.
+__device__ __forceinline__ uint32_t patch_hit_mask(const float2 xy, const float4 co, float tile_px0, float tile_py0)
+{
+	const float A = co.x, B = co.y, Cc = co.z;
+	const float thr = 2.0f * logf(255.0f * co.w) + 0.02f;
+	const float nbc = __fdividef(-B, Cc), nba = __fdividef(-B, A);
+	const float B2 = 2.0f * B;
+	const float mx = xy.x - tile_px0, my = xy.y - tile_py0;
+	uint32_t m = 0;
+#pragma unroll
+	for (int r = 0; r < 4; r++) {
+		const float dyh = my - 4.0f * r, dyl = dyh - 3.0f;
+		const float ey = fminf(fmaxf(0.0f, dyl), dyh);
+		const float cey2 = Cc * ey * ey;
+		const float tx = nba * ey;
+#pragma unroll
+		for (int c = 0; c < 2; c++) {
+			const float dxh = mx - 8.0f * c, dxl = dxh - 7.0f;
+			const float ex = fminf(fmaxf(0.0f, dxl), dxh);
+			const float dy1 = fminf(fmaxf(nbc * ex, dyl), dyh);
+			const float dx2 = fminf(fmaxf(tx, dxl), dxh);
+			const float m1 = A * ex * ex + Cc * dy1 * dy1;
+			const float m2 = A * dx2 * dx2 + cey2;
+			const float q1 = m1 + B2 * ex * dy1 - 3e-5f * m1;
+			const float q2 = m2 + B2 * dx2 * ey - 3e-5f * m2;
+			if (!(fminf(q1, q2) > thr)) m |= 1u << (r * 2 + c);
+		}
+	}
+	return m;
+}
+
+template <bool CULL>
 __global__ void __launch_bounds__(TILE_PIX)
 blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b,
 	float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha)
@@ -68,6 +116,7 @@ blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Geo
 	__shared__ float2 s_xy[TILE_PIX];
 	__shared__ float4 s_co[TILE_PIX];
 	__shared__ float4 s_feat[TILE_PIX];
+	__shared__ uint8_t s_mask[TILE_PIX];
 
 	if (im.counters[1]) return;   // binning overflow: the host re-runs with a larger buffer
 	const int tile = blockIdx.x;
@@ -75,6 +124,8 @@ blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Geo
 	const uint2 range = im.ranges[tile];
 	const int n = (int)(range.y - range.x);
 	const bool in_smem = n <= SORT_CAP;
+	const unsigned full = 0xffffffffu;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
 	// ---- sort this tile's segment by (depth bits, gaussian id) --------------------------------------
 	if (n > 0) {
@@ -104,40 +155,70 @@ blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Geo
 	pixel_of_thread(tile_x, tile_y, px, py);
 	const bool inside = px < W && py < H;
 	const float pxf = (float)px, pyf = (float)py;
+	const float tile_px0 = (float)(tile_x * TILE_X), tile_py0 = (float)(tile_y * TILE_Y);
 	bool done = !inside;
 	float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, Dp = 0.f;
-	uint32_t contributor = 0, last_contributor = 0;
+	uint32_t last_contributor = 0;
 
 	for (int base = 0; base < n; base += TILE_PIX) {
 		if (__syncthreads_count(done) == TILE_PIX) break;
 		const int i = base + threadIdx.x;
+		uint32_t hit = 0;
 		if (i < n) {
 			const uint32_t id = in_smem ? (uint32_t)s_keys[i] : (uint32_t)b.keys[range.x + i];
-			s_xy[threadIdx.x] = g.means2D[id];
-			s_co[threadIdx.x] = g.conic_opacity[id];
+			const float2 xy = g.means2D[id];
+			const float4 co = g.conic_opacity[id];
+			s_xy[threadIdx.x] = xy;
+			s_co[threadIdx.x] = co;
 			s_feat[threadIdx.x] = g.feat[id];
+			hit = CULL ? patch_hit_mask(xy, co, tile_px0, tile_py0) : 0xffu;
+			b.hit_mask[range.x + i] = (uint8_t)hit;
 		}
+		s_mask[threadIdx.x] = (uint8_t)hit;
 		__syncthreads();
+		if (__all_sync(full, done)) continue;          // this warp's patch is finished (still helps staging)
 		const int cnt = min(TILE_PIX, n - base);
-		for (int j = 0; !done && j < cnt; j++) {
-			contributor++;
-			const float2 xy = s_xy[j];
-			const float4 co = s_co[j];
-			const float dx = fsub(xy.x, pxf), dy = fsub(xy.y, pyf);
-			const float power = blend_power(dx, dy, co);
-			if (power > 0.0f) continue;
-			const float alpha = fminf(fmul(co.w, expf(power)), 0.99f);
-			if (alpha < 1.0f / 255.0f) continue;
-			const float test_T = fmul(T, fsub(1.0f, alpha));
-			if (test_T < 0.0001f) { done = true; continue; }
-			const float4 f = s_feat[j];
-			C0 = ffma(T, fmul(alpha, f.x), C0);
-			C1 = ffma(T, fmul(alpha, f.y), C1);
-			C2 = ffma(T, fmul(alpha, f.z), C2);
-			weight = ffma(T, alpha, weight);
-			Dp = ffma(T, fmul(alpha, f.w), Dp);
-			T = test_T;
-			last_contributor = contributor;
+		for (int sb = 0; sb < cnt; sb += 32) {
+			uint32_t bits = __ballot_sync(full, (s_mask[sb + lane] >> warp) & 1u);
+			while (bits) {
+				// up to four hits: independent alpha evaluations first, then the serial transmittance chain
+				int jj[4];
+				float al[4];
+				bool ok[4];
+#pragma unroll
+				for (int k = 0; k < 4; k++) {
+					const bool has = bits != 0u;
+					const int j = sb + (has ? (__ffs(bits) - 1) : 0);
+					bits &= bits - 1u;
+					jj[k] = j;
+					const float2 xy = s_xy[j];
+					const float4 co = s_co[j];
+					const float dx = fsub(xy.x, pxf), dy = fsub(xy.y, pyf);
+					const float power = blend_power(dx, dy, co);
+					const float alpha = fminf(fmul(co.w, expf(power)), 0.99f);
+					al[k] = alpha;
+					ok[k] = has && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+				}
+#pragma unroll
+				for (int k = 0; k < 4; k++) {
+					if (ok[k] && !done) {
+						const float alpha = al[k];
+						const float test_T = fmul(T, fsub(1.0f, alpha));
+						if (test_T < 0.0001f) { done = true; }
+						else {
+							const float4 f = s_feat[jj[k]];
+							C0 = ffma(T, fmul(alpha, f.x), C0);
+							C1 = ffma(T, fmul(alpha, f.y), C1);
+							C2 = ffma(T, fmul(alpha, f.z), C2);
+							weight = ffma(T, alpha, weight);
+							Dp = ffma(T, fmul(alpha, f.w), Dp);
+							T = test_T;
+							last_contributor = (uint32_t)(base + jj[k] + 1);
+						}
+					}
+				}
+				if (__all_sync(full, done)) { bits = 0u; sb = cnt; }
+			}
 		}
 	}
 
@@ -188,17 +269,24 @@ __device__ __forceinline__ float warp_reduce1(float v)
 	return v;
 }
 
+constexpr int NGRAD = 9;          // dcolor[3], dmean2D.xy, dconic.{x,y,w}, dopacity
+constexpr int BWD_BATCH = 128;    // instances staged per round of the backward
+
 __global__ void __launch_bounds__(TILE_PIX)
 blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b,
 	const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas,
 	float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
 	float* __restrict__ dL_dcolor)
 {
-	__shared__ uint32_t s_id[TILE_PIX];
-	__shared__ float2 s_xy[TILE_PIX];
-	__shared__ float4 s_co[TILE_PIX];
-	__shared__ float4 s_feat[TILE_PIX];
-	__shared__ uint32_t s_warp_last[TILE_PIX / 32];
+	__shared__ uint32_t s_id[BWD_BATCH];
+	__shared__ float2 s_xy[BWD_BATCH];
+	__shared__ float4 s_co[BWD_BATCH];
+	__shared__ float4 s_feat[BWD_BATCH];
+	__shared__ uint8_t s_mask[BWD_BATCH];
+	__shared__ uint32_t s_written[BWD_BATCH];                 // bit w: warp w stored a gradient row for this slot
+	__shared__ float s_grad[NPATCH * BWD_BATCH * NGRAD];      // [warp][slot][component]: each (warp, slot) is written
+	                                                          // at most once per batch -> plain stores, no atomics
+	__shared__ uint32_t s_warp_last[NPATCH];
 
 	const int tile = blockIdx.x;
 	const int tile_y = tile / grid_x, tile_x = tile - tile_y * grid_x;
@@ -212,6 +300,7 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 	const int pix = py * W + px;
 	const float pxf = (float)px, pyf = (float)py;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const unsigned full = 0xffffffffu;
 
 	const float T_final = inside ? im.final_T[pix] : 0.f;
 	float T = T_final;
@@ -226,94 +315,130 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 	const float bg_dot_dpixel = bg[0] * dpix[0] + bg[1] * dpix[1] + bg[2] * dpix[2];
 
 	// nothing behind the furthest "last contributor" of the tile (of the warp) can receive gradient
-	const uint32_t warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+	const uint32_t warp_last = __reduce_max_sync(full, last_contributor);
 	if (lane == 0) s_warp_last[warp] = warp_last;
 	__syncthreads();
 	uint32_t tile_last = 0;
 #pragma unroll
-	for (int w = 0; w < TILE_PIX / 32; w++) tile_last = max(tile_last, s_warp_last[w]);
+	for (int w = 0; w < NPATCH; w++) tile_last = max(tile_last, s_warp_last[w]);
 	if (tile_last == 0) return;
 
 	float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
 	float accum_depth_rec = 0.f, last_depth = 0.f, accum_alpha_rec = 0.f, last_alpha = 0.f;
 	const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
-	// forward position (1-based) of the instance handled next, walking back to front
-	uint32_t contributor = tile_last;
-	for (int base = 0; base < (int)tile_last; base += TILE_PIX) {
+	// batch slot j holds forward position (0-based) tile_last-1-(base+j): the walk is back to front
+	for (int base = 0; base < (int)tile_last; base += BWD_BATCH) {
 		__syncthreads();
-		const int i = base + threadIdx.x;   // distance behind position tile_last-1
-		if (i < (int)tile_last) {
-			const uint32_t id = b.point_list[range.x + tile_last - 1 - i];
+		const int i = base + threadIdx.x;
+		uint32_t hit = 0;
+		if (threadIdx.x < BWD_BATCH && i < (int)tile_last) {
+			const uint32_t pos = range.x + tile_last - 1 - i;
+			const uint32_t id = b.point_list[pos];
+			hit = b.hit_mask[pos];
 			s_id[threadIdx.x] = id;
 			s_xy[threadIdx.x] = g.means2D[id];
 			s_co[threadIdx.x] = g.conic_opacity[id];
 			s_feat[threadIdx.x] = g.feat[id];
 		}
+		if (threadIdx.x < BWD_BATCH) { s_mask[threadIdx.x] = (uint8_t)hit; s_written[threadIdx.x] = 0u; }
 		__syncthreads();
-		const int cnt = min(TILE_PIX, (int)tile_last - base);
-		for (int j = 0; j < cnt; j++) {
-			contributor--;
-			if (contributor >= warp_last) continue;   // warp-uniform
-			bool valid = contributor < last_contributor;
-			const float2 xy = s_xy[j];
-			const float4 co = s_co[j];
-			const float dx = xy.x - pxf, dy = xy.y - pyf;
-			const float power = blend_power(dx, dy, co);
-			valid = valid && !(power > 0.0f);
-			const float G = expf(power);
-			const float alpha = fminf(fmul(co.w, G), 0.99f);
-			valid = valid && !(alpha < 1.0f / 255.0f);
-			if (!__any_sync(0xffffffffu, valid)) continue;
 
-			float v[8], v_opa = 0.f;
+		const int cnt = min(BWD_BATCH, (int)tile_last - base);
+		for (int sb = 0; sb < cnt; sb += 32) {
+			// forward position of slot sb+lane; instances at/behind the warp's last contributor get no gradient
+			const int fpos = (int)tile_last - 1 - (base + sb + lane);
+			uint32_t bits = __ballot_sync(full, ((s_mask[sb + lane] >> warp) & 1u) && fpos < (int)warp_last);
+			while (bits) {
+				const int j = sb + __ffs(bits) - 1;
+				bits &= bits - 1u;
+				const uint32_t contributor = tile_last - 1 - (uint32_t)(base + j);
+				bool valid = contributor < last_contributor;
+				const float2 xy = s_xy[j];
+				const float4 co = s_co[j];
+				const float dx = xy.x - pxf, dy = xy.y - pyf;
+				const float power = blend_power(dx, dy, co);
+				valid = valid && !(power > 0.0f);
+				const float G = expf(power);
+				const float alpha = fminf(fmul(co.w, G), 0.99f);
+				valid = valid && !(alpha < 1.0f / 255.0f);
+				if (!__any_sync(full, valid)) continue;
+
+				float v[8], v_opa = 0.f;
 #pragma unroll
-			for (int k = 0; k < 8; k++) v[k] = 0.f;
-			if (valid) {
-				const float4 f = s_feat[j];
-				T = T / (1.f - alpha);
-				const float dchannel_dcolor = alpha * T;
-				float dL_dopa = 0.0f;
-				const float c[3] = {f.x, f.y, f.z};
+				for (int k = 0; k < 8; k++) v[k] = 0.f;
+				if (valid) {
+					const float4 f = s_feat[j];
+					T = T / (1.f - alpha);
+					const float dchannel_dcolor = alpha * T;
+					float dL_dopa = 0.0f;
+					const float c[3] = {f.x, f.y, f.z};
 #pragma unroll
-				for (int ch = 0; ch < 3; ch++) {
-					accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-					last_color[ch] = c[ch];
-					dL_dopa += (c[ch] - accum_rec[ch]) * dpix[ch];
-					v[ch] = dchannel_dcolor * dpix[ch];
+					for (int ch = 0; ch < 3; ch++) {
+						accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+						last_color[ch] = c[ch];
+						dL_dopa += (c[ch] - accum_rec[ch]) * dpix[ch];
+						v[ch] = dchannel_dcolor * dpix[ch];
+					}
+					accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
+					last_depth = f.w;
+					dL_dopa += (f.w - accum_depth_rec) * ddepth;
+					accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
+					dL_dopa += (1.f - accum_alpha_rec) * dalpha;
+					dL_dopa *= T;
+					last_alpha = alpha;
+					dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+
+					const float dL_dG = co.w * dL_dopa;
+					const float gdx = G * dx, gdy = G * dy;
+					const float dG_ddelx = -gdx * co.x - gdy * co.y;
+					const float dG_ddely = -gdy * co.z - gdx * co.y;
+					v[3] = dL_dG * dG_ddelx * ddelx_dx;
+					v[4] = dL_dG * dG_ddely * ddely_dy;
+					v[5] = -0.5f * gdx * dx * dL_dG;
+					v[6] = -0.5f * gdx * dy * dL_dG;
+					v[7] = -0.5f * gdy * dy * dL_dG;
+					v_opa = G * dL_dopa;
 				}
-				accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
-				last_depth = f.w;
-				dL_dopa += (f.w - accum_depth_rec) * ddepth;
-				accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
-				dL_dopa += (1.f - accum_alpha_rec) * dalpha;
-				dL_dopa *= T;
-				last_alpha = alpha;
-				dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-
-				const float dL_dG = co.w * dL_dopa;
-				const float gdx = G * dx, gdy = G * dy;
-				const float dG_ddelx = -gdx * co.x - gdy * co.y;
-				const float dG_ddely = -gdy * co.z - gdx * co.y;
-				v[3] = dL_dG * dG_ddelx * ddelx_dx;
-				v[4] = dL_dG * dG_ddely * ddely_dy;
-				v[5] = -0.5f * gdx * dx * dL_dG;
-				v[6] = -0.5f * gdx * dy * dL_dG;
-				v[7] = -0.5f * gdy * dy * dL_dG;
-				v_opa = G * dL_dopa;
+				const float s8 = warp_reduce8(v);
+				const float s1 = warp_reduce1(v_opa);
+				float* row = s_grad + (warp * BWD_BATCH + j) * NGRAD;
+				if ((lane & 3) == 0) row[lane >> 2] = s8;
+				else if (lane == 1) { row[8] = s1; atomicOr(&s_written[j], 1u << warp); }
 			}
-			const float s8 = warp_reduce8(v);
-			const float s1 = warp_reduce1(v_opa);
-			const uint32_t id = s_id[j];
-			if ((lane & 3) == 0) {
-				const int k = lane >> 2;
-				float* dst;
-				if (k < 3) dst = dL_dcolor + 3 * (size_t)id + k;
-				else if (k < 5) dst = dL_dmean2D + 3 * (size_t)id + (k - 3);
-				else dst = dL_dconic + 4 * (size_t)id + (k == 7 ? 3 : k - 5);
-				atomicAdd(dst, s8);
-			} else if (lane == 1) {
-				atomicAdd(dL_dopacity + id, s1);
+		}
+		__syncthreads();
+
+		// flush the batch: the rows of the warps that hit a slot are summed in warp order, then ONE global atomic
+		// per (instance, component); thread t takes slot t%128 and components 0-4 (t<128) or 5-8
+		{
+			const int j = threadIdx.x & (BWD_BATCH - 1);
+			const uint32_t wmask = s_written[j];
+			if (wmask) {
+				const int k0 = (threadIdx.x < BWD_BATCH) ? 0 : 5;
+				float r[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+				for (int w = 0; w < NPATCH; w++) {
+					if (wmask & (1u << w)) {
+						const float* row = s_grad + (w * BWD_BATCH + j) * NGRAD + k0;
+#pragma unroll
+						for (int k = 0; k < 4; k++) r[k] += row[k];
+						if (k0 == 0) r[4] += row[4];
+					}
+				}
+				const size_t id = s_id[j];
+				if (k0 == 0) {
+					atomicAdd(dL_dcolor + 3 * id + 0, r[0]);
+					atomicAdd(dL_dcolor + 3 * id + 1, r[1]);
+					atomicAdd(dL_dcolor + 3 * id + 2, r[2]);
+					atomicAdd(dL_dmean2D + 3 * id + 0, r[3]);
+					atomicAdd(dL_dmean2D + 3 * id + 1, r[4]);
+				} else {
+					atomicAdd(dL_dconic + 4 * id + 0, r[0]);
+					atomicAdd(dL_dconic + 4 * id + 1, r[1]);
+					atomicAdd(dL_dconic + 4 * id + 3, r[2]);
+					atomicAdd(dL_dopacity + id, r[3]);
+				}
 			}
 		}
 	}

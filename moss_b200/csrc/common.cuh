@@ -61,6 +61,7 @@ struct ImageWS {
 struct BinWS {
 	unsigned long long* keys; // [cap] (depth_bits << 32 | gaussian id), grouped per tile, sorted in place
 	uint32_t* point_list;     // [cap] sorted gaussian ids
+	uint8_t* hit_mask;        // [cap] bit w: the instance can reach alpha >= 1/255 in patch (warp) w of its tile
 	unsigned long long* keys_sorted; // [cap] (tile << 32 | depth_bits), only with EXPORT_KEYS
 };
 
@@ -105,6 +106,7 @@ __host__ __device__ inline BinWS carve_bin(char* base, size_t cap, bool export_k
 	BinWS b;
 	b.keys = carve<unsigned long long>(p, cap);
 	b.point_list = carve<uint32_t>(p, cap);
+	b.hit_mask = carve<uint8_t>(p, cap);
 	b.keys_sorted = export_keys ? carve<unsigned long long>(p, cap) : nullptr;
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return b;

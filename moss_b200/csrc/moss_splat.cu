@@ -218,7 +218,7 @@ size_t moss_binning_workspace_bytes_ex(long long capacity, int export_keys)
 size_t moss_binning_workspace_bytes(long long capacity) { return moss_binning_workspace_bytes_ex(capacity, 0); }
 long long moss_binning_capacity(size_t bytes, int export_keys)
 {
-	const size_t per = export_keys ? 20 : 12;
+	const size_t per = export_keys ? 21 : 13;
 	long long lo = 0, hi = (long long)(bytes / per) + 1;   // largest cap with bytes_ex(cap) <= bytes
 	while (lo < hi) {
 		const long long mid = lo + (hi - lo + 1) / 2;
@@ -284,7 +284,10 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 		im.counters, b.keys); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_FWD, stream);
-	blend_forward_kernel<<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha); }
+	if (flags & MOSS_FLAG_NO_CULL)
+		blend_forward_kernel<false><<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+	else
+		blend_forward_kernel<true><<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 
 	if (flags & MOSS_FLAG_ASYNC) return MOSS_OK;

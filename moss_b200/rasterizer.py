@@ -216,14 +216,19 @@ class _RasterizeGaussians(torch.autograd.Function):
                                                      cov3Ds_precomp, raster_settings)
         ctx.raster_settings = raster_settings
         ctx.num_rendered = st.num_rendered
-        ctx.state = st
         ctx.mark_non_differentiable(radii)
-        ctx.save_for_backward(radii)
+        # The workspaces and the inputs whose device pointers sit in st.scene go through save_for_backward, like
+        # the reference's three state tensors (DGR/diff_gaussian_rasterization/__init__.py:97): autograd frees
+        # them right after the backward unless retain_graph is set.
+        ctx.save_for_backward(radii, st.ws, st.binning, *st.keep)
+        st.ws = st.binning = st.keep = None
+        ctx.state = st
         return color, radii, depth, alpha
 
     @staticmethod
     def backward(ctx, grad_out_color, grad_radii, grad_depth, grad_alpha):
-        (radii,) = ctx.saved_tensors
+        saved = ctx.saved_tensors           # raises the usual error when the graph was already freed
+        radii = saved[0]
         st = ctx.state
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
          grad_scales, grad_rotations) = backward_raw(st, radii, grad_out_color, grad_depth, grad_alpha)
