@@ -44,6 +44,9 @@ extern "C" {
                                      larger binning workspace moss_binning_workspace_bytes_ex(R, 1) */
 #define MOSS_FLAG_DEBUG       8u  /* synchronise + check after every launch (DGR/cuda_rasterizer/auxiliary.h:166-173) */
 #define MOSS_FLAG_DETERMINISTIC 16u /* backward: fixed-order gradient reduction (bit-reproducible run to run) */
+#define MOSS_FLAG_SPLIT_SHIFT  8   /* bits 8-9: blend block shape; 0 = automatic, 1 = whole tile (8 warps), 2 = half
+                                     tile (4 warps), 3 = quarter tile (2 warps).  Results do not depend on it. */
+#define MOSS_FLAG_SPLIT_MASK   (3u << MOSS_FLAG_SPLIT_SHIFT)
 #define MOSS_FLAG_NO_CULL     32u /* forward: disable the per-patch culling of instances (every instance is offered to
                                        every pixel of its tile, as DGR forward.cu:330-365 does); results are identical
                                        by construction -- the flag exists so tests can prove it at full sizes */
@@ -141,7 +144,8 @@ long long moss_export_state(void* stream, const MossScene* scene, int which, voi
 #define MOSS_STAGE_BLEND_BWD       4
 #define MOSS_STAGE_PREPROCESS_BWD  5
 #define MOSS_STAGE_OTHER           6
-#define MOSS_STAGE_COUNT           7
+#define MOSS_STAGE_TILE_SORT       7
+#define MOSS_STAGE_COUNT           8
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

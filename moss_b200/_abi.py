@@ -22,6 +22,7 @@ FLAG_EXPORT_KEYS = 4
 FLAG_DEBUG = 8
 FLAG_DETERMINISTIC = 16
 FLAG_NO_CULL = 32
+FLAG_SPLIT_SHIFT = 8          # bits 8-9: 0 auto, 1 whole-tile blocks, 2 half-tile, 3 quarter-tile
 
 STATE = dict(depths=0, clamped=1, means2D=2, cov3D=3, conic_opacity=4, rgb=5, tiles_touched=7,
              keys_sorted=9, point_list=11, ranges=12, n_contrib=13, final_T=14, counters=15)
@@ -34,7 +35,7 @@ SYMBOLS = [
     "moss_error_string", "moss_last_cuda_error", "moss_sizeof_scene", "moss_kernel_launches",
     "moss_profile_enable", "moss_profile_read", "moss_stage_name",
 ]
-STAGE_COUNT = 7
+STAGE_COUNT = 8
 
 
 class MossScene(C.Structure):

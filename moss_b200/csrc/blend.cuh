@@ -1,75 +1,47 @@
-// K4: per-tile segment sort + front-to-back alpha blend (forward);  K6: reverse-order blend backward.
+// K4b: front-to-back alpha blend (forward);  K6: reverse-order blend backward.
 //
 // Blend semantics: DGR/cuda_rasterizer/forward.cu:261-383 (renderCUDA) and backward.cu:399-587.
-// One 256-thread block per 16x16 tile; a warp owns an 8x4 pixel patch.  New relative to the reference:
-//  * the tile's (depth|id) segment is sorted inside the block (shared memory bitonic network; in-place global
-//    fallback for oversized segments) right before blending, replacing the global radix sort;
-//  * colour+depth are staged in shared memory with the conic (one float4 gather per instance) instead of
-//    per-pair global reads;
-//  * PATCH CULLING: while a batch of 256 instances is staged, the loading thread tests its instance against the
-//    tile's eight 8x4 patches (exact minimum of the conic's quadratic form over the patch rectangle versus the
-//    alpha >= 1/255 threshold, with a conservative margin) and stores an 8-bit hit mask.  Each warp then walks
-//    only the instances that can reach its patch (ballot -> bit scan), which cuts the serial per-pixel loop
-//    ~3x at ZJU splat sizes.  A culled instance is one every pixel of the patch would have skipped through
-//    `alpha < 1/255` (forward.cu:350), so the image stays bit-identical.  The masks are written next to the
-//    sorted list and re-used by the backward;
-//  * the alpha of up to four hits is evaluated independently before the serial transmittance chain (ILP:
-//    the kernel is latency-bound, ~3 warps per scheduler at ZJU shape);
-//  * backward: per-hit gradients are reduced across the warp with a recursive-halving shuffle tree, summed
-//    across the tile's warps in shared memory, and flushed with ONE global atomic per (instance, tile,
-//    component) after each batch; batches behind the tile's last contributor are never loaded.
+// The reference runs one 256-thread block per 16x16 tile and lets every pixel walk every instance of the tile.
+// At ZJU shape only ~200 tiles are busy and the deepest ones (1000-1700 instances) set the launch time, so this
+// version is organised around the critical path of ONE deep tile:
+//  * a warp owns an 8x4 pixel patch; a block is NW warps (NW = 8, 4 or 2: whole, half or quarter tile).  With
+//    NW < 8 the patches of a deep tile run on different SMs, each warp has a scheduler to itself (the hit loop is
+//    issue-bound at two warps per scheduler) and every sub-block stops as soon as ITS pixels are saturated;
+//  * PATCH CULLING: while a batch of instances is staged in shared memory, the staging thread tests its instance
+//    against the block's patches (exact minimum of the conic's quadratic form over the patch rectangle versus the
+//    alpha >= 1/255 threshold, conservative margin).  Each warp compacts the slots that can reach its patch into a
+//    byte list and walks only those (~1/3 of the tile's instances at ZJU splat sizes).  A culled instance is one
+//    every pixel of the patch would have skipped through `alpha < 1/255` (forward.cu:350), so image, final_T and
+//    n_contrib stay bit-identical (tests: test_patch_culling_is_invisible, MOSS_FLAG_NO_CULL);
+//  * the hit loop is branch-free: FWD_GROUP hits are fetched with one broadcast load of their slot bytes, their
+//    alphas are evaluated independently (ILP), then a short predicated chain T -> T(1-alpha) -> compare runs
+//    per hit.  (Guarded loads compile to divergent branches; each exposed a shared-memory latency: 4x slower.)
+//  * colour+depth are staged with the conic (one float4 gather per instance) and the gathers of batch k+1 are in
+//    flight while batch k is blended;
+//  * backward: same culling/compaction, gradients reduced across the warp with a recursive-halving shuffle tree,
+//    stored (not atomically added) into per-warp rows in shared memory, summed over the block's warps and flushed
+//    with ONE global atomic per (instance, block, component) per batch; batches behind the block's last
+//    contributor are never loaded.
 // The forward arithmetic uses explicitly-rounded intrinsics in the reference's contraction order so the
 // image is bit-identical on identical sorted lists (thresholds at power>0, alpha<1/255, T<1e-4 make a 1-ulp
 // difference visible).
 #pragma once
 #include "common.cuh"
+#include "tile_sort.cuh"
 
 namespace moss {
 
-constexpr int SORT_CAP = 4096;   // instances per tile sorted in shared memory (32 KB)
-constexpr int NPATCH = TILE_PIX / 32;   // 8 warps = 2 (x) by 4 (y) patches of 8x4 pixels
-
-// Ascending bitonic network over a[0..n) with virtual +inf padding up to the next power of two
-// ("flip" formulation: every compare-exchange is ascending, so padding never moves).
-template <typename KeyPtr>
-__device__ __forceinline__ void block_bitonic_sort(KeyPtr a, int n)
+// Patch p (0..7) of a tile: column p&1 (8 px wide), row p>>1 (4 px high).  Block `sub` of a tile split into
+// 8/NW blocks owns patches sub*NW .. sub*NW+NW-1.
+template <int NW>
+__device__ __forceinline__ void pixel_of_thread(int tile_x, int tile_y, int sub, int& px, int& py)
 {
-	int npow2 = 1;
-	while (npow2 < n) npow2 <<= 1;
-	const int half = npow2 >> 1;
-	for (int k = 2; k <= npow2; k <<= 1) {
-		for (int j = k >> 1; j > 0; j >>= 1) {
-			const bool flip = (j == (k >> 1));
-			for (int t = threadIdx.x; t < half; t += TILE_PIX) {
-				const int blk = t / j, off = t - blk * j;
-				const int i = blk * 2 * j + off;
-				const int p = flip ? (blk * 2 * j + 2 * j - 1 - off) : (i + j);
-				if (p < n) {
-					const unsigned long long x = a[i], y = a[p];
-					if (x > y) { a[i] = y; a[p] = x; }
-				}
-			}
-			__syncthreads();
-		}
-	}
+	const int patch = sub * NW + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+	px = tile_x * TILE_X + (patch & 1) * 8 + (lane & 7);
+	py = tile_y * TILE_Y + (patch >> 1) * 4 + (lane >> 3);
 }
 
-// power = -0.5f*(A dx^2 + C dy^2) - B dx dy  (DGR forward.cu:340, backward.cu:507) in the rounding sequence of
-// the reference's sm_100 SASS: q = fma(dx, dx*A, dy*(dy*C)); power = fma(q, -0.5, -(dy*(dx*B))).
-__device__ __forceinline__ float blend_power(float dx, float dy, const float4& co)
-{
-	const float q = ffma(dx, fmul(dx, co.x), fmul(dy, fmul(dy, co.z)));
-	return ffma(q, -0.5f, -fmul(dy, fmul(dx, co.y)));
-}
-
-__device__ __forceinline__ void pixel_of_thread(int tile_x, int tile_y, int& px, int& py)
-{
-	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	px = tile_x * TILE_X + (warp & 1) * 8 + (lane & 7);
-	py = tile_y * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
-}
-
-// Bit w set <=> the instance may reach alpha >= 1/255 on some pixel of patch w (= warp w's 8x4 pixels).
+// Bit w set <=> the instance may reach alpha >= 1/255 on some pixel of the block's w-th patch.
 // alpha = o*exp(-q/2) >= 1/255  <=>  q(d) = A dx^2 + 2B dx dy + C dy^2 <= 2 ln(255 o).  The minimum of the convex q
 // over the patch's offset rectangle [dxl,dxh]x[dyl,dyh] is 0 if the centre is inside; otherwise it lies on an edge
 // facing the centre, i.e. at (ex, clamp(-B ex/C)) or (clamp(-B ey/A), ey) with (ex,ey) the rectangle point
@@ -77,16 +49,20 @@ __device__ __forceinline__ void pixel_of_thread(int tile_x, int tile_y, int& px,
 // (0.02 absolute on q, 3e-5 relative on the positive terms) is >30x the fp32 error of either evaluation and
 // of expf/logf, so the test never culls an instance the exact per-pixel test would blend.
 // NaN anywhere -> comparison false -> not culled.
-__device__ __forceinline__ uint32_t patch_hit_mask(const float2 xy, const float4 co, float tile_px0, float tile_py0)
+template <int NW>
+__device__ __forceinline__ uint32_t patch_hit_mask(const float2 xy, const float4 co, float tile_px0, float tile_py0, int sub)
 {
+	static_assert(NW == 2 || NW == 4 || NW == 8, "a block owns whole patch rows");
 	const float A = co.x, B = co.y, Cc = co.z;
-	const float thr = 2.0f * logf(255.0f * co.w) + 0.02f;
+	const float thr = 2.0f * __logf(255.0f * co.w) + 0.02f;     // fast log: |error| << the 0.02 margin
 	const float nbc = __fdividef(-B, Cc), nba = __fdividef(-B, A);
 	const float B2 = 2.0f * B;
-	const float mx = xy.x - tile_px0, my = xy.y - tile_py0;
+	const float mx = xy.x - tile_px0;
+	constexpr int ROWS = NW / 2;
+	const float my = xy.y - tile_py0 - 4.0f * (float)(sub * ROWS);
 	uint32_t m = 0;
 #pragma unroll
-	for (int r = 0; r < 4; r++) {
+	for (int r = 0; r < ROWS; r++) {
 		const float dyh = my - 4.0f * r, dyl = dyh - 3.0f;
 		const float ey = fminf(fmaxf(0.0f, dyl), dyh);
 		const float cey2 = Cc * ey * ey;
@@ -107,120 +83,169 @@ __device__ __forceinline__ uint32_t patch_hit_mask(const float2 xy, const float4
 	return m;
 }
 
-template <bool CULL>
-__global__ void __launch_bounds__(TILE_PIX)
+// instances staged in shared memory per round: 128, or one per thread for the 256-thread whole-tile block
+template <int NW> struct BlendCfg { static constexpr int NT = 32 * NW, BATCH = NT > 128 ? NT : 128, PER = BATCH / NT; };
+constexpr int FWD_GROUP = 8;       // hits whose alpha is evaluated together before the serial transmittance chain
+
+template <int NW>
+struct BlendSmem {
+	static constexpr int BATCH = BlendCfg<NW>::BATCH;
+	float2 xy[BATCH];
+	float4 co[BATCH];
+	float4 feat[BATCH];
+	uint8_t mask[BATCH];
+	// per warp: slots of the staged batch that can reach the warp's patch, in list order (+ pad for the last group)
+	__align__(8) uint8_t hits[NW][BATCH + FWD_GROUP];
+};
+
+// Per-warp compaction of the batch's hit slots into hits[]; returns their number.  One ballot per 32 slots.
+template <int BATCH>
+__device__ __forceinline__ int compact_hits(const uint8_t* mask, uint8_t* hits, int cnt, int warp, int lane)
+{
+	int nh = 0;
+#pragma unroll
+	for (int sb = 0; sb < BATCH; sb += 32) {
+		const bool mine = (sb + lane < cnt) && ((mask[sb + lane] >> warp) & 1u);
+		const uint32_t bits = __ballot_sync(0xffffffffu, mine);
+		if (mine) hits[nh + __popc(bits & ((1u << lane) - 1u))] = (uint8_t)(sb + lane);
+		nh += __popc(bits);
+	}
+	__syncwarp();
+	return nh;
+}
+
+template <bool CULL, int NW>
+__global__ void __launch_bounds__(32 * NW)
 blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b,
 	float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha)
 {
-	__shared__ unsigned long long s_keys[SORT_CAP];
-	__shared__ float2 s_xy[TILE_PIX];
-	__shared__ float4 s_co[TILE_PIX];
-	__shared__ float4 s_feat[TILE_PIX];
-	__shared__ uint8_t s_mask[TILE_PIX];
+	constexpr int NT = BlendCfg<NW>::NT;          // threads per block
+	constexpr int BLEND_BATCH = BlendCfg<NW>::BATCH;
+	constexpr int PER = BlendCfg<NW>::PER;        // instances staged per thread per batch
+	constexpr int SPLIT = NPATCH / NW;            // blocks per tile
+	__shared__ BlendSmem<NW> bs;
 
 	if (im.counters[1]) return;   // binning overflow: the host re-runs with a larger buffer
-	const int tile = blockIdx.x;
+	const int tile = (int)im.tile_order[blockIdx.x / SPLIT];   // deepest tiles first (binning.cuh)
+	const int sub = blockIdx.x % SPLIT;
 	const int tile_y = tile / grid_x, tile_x = tile - tile_y * grid_x;
 	const uint2 range = im.ranges[tile];
 	const int n = (int)(range.y - range.x);
-	const bool in_smem = n <= SORT_CAP;
 	const unsigned full = 0xffffffffu;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-	// ---- sort this tile's segment by (depth bits, gaussian id) --------------------------------------
-	if (n > 0) {
-		unsigned long long* gk = b.keys + range.x;
-		if (in_smem) {
-			for (int i = threadIdx.x; i < n; i += TILE_PIX) s_keys[i] = gk[i];
-			__syncthreads();
-			block_bitonic_sort(s_keys, n);
-			for (int i = threadIdx.x; i < n; i += TILE_PIX) {
-				const unsigned long long k = s_keys[i];
-				b.point_list[range.x + i] = (uint32_t)k;
-				if (b.keys_sorted) b.keys_sorted[range.x + i] = ((unsigned long long)tile << 32) | (k >> 32);
-			}
-		} else {
-			__syncthreads();
-			block_bitonic_sort(gk, n);
-			for (int i = threadIdx.x; i < n; i += TILE_PIX) {
-				const unsigned long long k = gk[i];
-				b.point_list[range.x + i] = (uint32_t)k;
-				if (b.keys_sorted) b.keys_sorted[range.x + i] = ((unsigned long long)tile << 32) | (k >> 32);
-			}
-		}
-	}
-
-	// ---- blend ---------------------------------------------------------------------------------------
 	int px, py;
-	pixel_of_thread(tile_x, tile_y, px, py);
+	pixel_of_thread<NW>(tile_x, tile_y, sub, px, py);
 	const bool inside = px < W && py < H;
 	const float pxf = (float)px, pyf = (float)py;
 	const float tile_px0 = (float)(tile_x * TILE_X), tile_py0 = (float)(tile_y * TILE_Y);
 	bool done = !inside;
 	float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, weight = 0.f, Dp = 0.f;
 	uint32_t last_contributor = 0;
+#ifdef MOSS_TILE_TIMING
+	if (sub == 0) MOSS_TT(2);
+#endif
 
-	for (int base = 0; base < n; base += TILE_PIX) {
-		if (__syncthreads_count(done) == TILE_PIX) break;
-		const int i = base + threadIdx.x;
-		uint32_t hit = 0;
+	// software pipeline: the gathers of batch k+1 are in flight while batch k is blended
+	float2 nxy[PER];
+	float4 nco[PER], nfeat[PER];
+#pragma unroll
+	for (int u = 0; u < PER; u++) {
+		const int i = u * NT + (int)threadIdx.x;
+		nxy[u] = make_float2(0.f, 0.f); nco[u] = make_float4(0.f, 0.f, 0.f, 0.f); nfeat[u] = nco[u];
 		if (i < n) {
-			const uint32_t id = in_smem ? (uint32_t)s_keys[i] : (uint32_t)b.keys[range.x + i];
-			const float2 xy = g.means2D[id];
-			const float4 co = g.conic_opacity[id];
-			s_xy[threadIdx.x] = xy;
-			s_co[threadIdx.x] = co;
-			s_feat[threadIdx.x] = g.feat[id];
-			hit = CULL ? patch_hit_mask(xy, co, tile_px0, tile_py0) : 0xffu;
-			b.hit_mask[range.x + i] = (uint8_t)hit;
-		}
-		s_mask[threadIdx.x] = (uint8_t)hit;
-		__syncthreads();
-		if (__all_sync(full, done)) continue;          // this warp's patch is finished (still helps staging)
-		const int cnt = min(TILE_PIX, n - base);
-		for (int sb = 0; sb < cnt; sb += 32) {
-			uint32_t bits = __ballot_sync(full, (s_mask[sb + lane] >> warp) & 1u);
-			while (bits) {
-				// up to four hits: independent alpha evaluations first, then the serial transmittance chain
-				int jj[4];
-				float al[4];
-				bool ok[4];
-#pragma unroll
-				for (int k = 0; k < 4; k++) {
-					const bool has = bits != 0u;
-					const int j = sb + (has ? (__ffs(bits) - 1) : 0);
-					bits &= bits - 1u;
-					jj[k] = j;
-					const float2 xy = s_xy[j];
-					const float4 co = s_co[j];
-					const float dx = fsub(xy.x, pxf), dy = fsub(xy.y, pyf);
-					const float power = blend_power(dx, dy, co);
-					const float alpha = fminf(fmul(co.w, expf(power)), 0.99f);
-					al[k] = alpha;
-					ok[k] = has && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-				}
-#pragma unroll
-				for (int k = 0; k < 4; k++) {
-					if (ok[k] && !done) {
-						const float alpha = al[k];
-						const float test_T = fmul(T, fsub(1.0f, alpha));
-						if (test_T < 0.0001f) { done = true; }
-						else {
-							const float4 f = s_feat[jj[k]];
-							C0 = ffma(T, fmul(alpha, f.x), C0);
-							C1 = ffma(T, fmul(alpha, f.y), C1);
-							C2 = ffma(T, fmul(alpha, f.z), C2);
-							weight = ffma(T, alpha, weight);
-							Dp = ffma(T, fmul(alpha, f.w), Dp);
-							T = test_T;
-							last_contributor = (uint32_t)(base + jj[k] + 1);
-						}
-					}
-				}
-				if (__all_sync(full, done)) { bits = 0u; sb = cnt; }
-			}
+			const uint32_t id = b.point_list[range.x + i];
+			nxy[u] = g.means2D[id]; nco[u] = g.conic_opacity[id]; nfeat[u] = g.feat[id];
 		}
 	}
+
+	for (int base = 0; base < n; base += BLEND_BATCH) {
+		if (__syncthreads_count(done) == NT) break;
+#pragma unroll
+		for (int u = 0; u < PER; u++) {
+			const int s = u * NT + (int)threadIdx.x;
+			uint32_t hit = 0;
+			if (base + s < n) {
+				bs.xy[s] = nxy[u];
+				bs.co[s] = nco[u];
+				bs.feat[s] = nfeat[u];
+				hit = CULL ? patch_hit_mask<NW>(nxy[u], nco[u], tile_px0, tile_py0, sub) : 0xffu;
+			}
+			bs.mask[s] = (uint8_t)hit;
+		}
+		__syncthreads();
+#pragma unroll
+		for (int u = 0; u < PER; u++) {
+			const int i = base + BLEND_BATCH + u * NT + (int)threadIdx.x;
+			if (i < n) {
+				const uint32_t id = b.point_list[range.x + i];
+				nxy[u] = g.means2D[id]; nco[u] = g.conic_opacity[id]; nfeat[u] = g.feat[id];
+			}
+		}
+		if (__all_sync(full, done)) continue;          // this warp's patch is finished (still helps staging)
+		const int cnt = min(BLEND_BATCH, n - base);
+		const int nh = compact_hits<BLEND_BATCH>(bs.mask, bs.hits[warp], cnt, warp, lane);
+
+		// Software pipeline over groups of FWD_GROUP hits: the alphas of group g+1 (independent work: loads, power,
+		// exp) are evaluated in the same straight-line block as the serial transmittance chain of group g, so the
+		// chain's dependent latency is covered by the next group's arithmetic.
+		int jj[FWD_GROUP];
+		float al[FWD_GROUP];
+		bool ok[FWD_GROUP];
+		auto eval_group = [&](int h0, int (&oj)[FWD_GROUP], float (&oa)[FWD_GROUP], bool (&ook)[FWD_GROUP]) {
+			const unsigned long long packed = lds_u64(&bs.hits[warp][h0]);
+#pragma unroll
+			for (int k = 0; k < FWD_GROUP; k++) {
+				// pad bytes are stale; masked to a valid slot
+				const int j = (int)((packed >> (8 * k)) & (unsigned long long)(BLEND_BATCH - 1));
+				oj[k] = j;
+				const float2 xy = bs.xy[j];
+				const float4 co = bs.co[j];
+				const float dx = fsub(xy.x, pxf), dy = fsub(xy.y, pyf);
+				const float power = blend_power(dx, dy, co);
+				const float alpha = fminf(fmul(co.w, expf(power)), 0.99f);
+				oa[k] = alpha;
+				ook[k] = (h0 + k < nh) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+			}
+		};
+		if (nh > 0) eval_group(0, jj, al, ok);
+		for (int h = 0; h < nh; h += FWD_GROUP) {
+			int njj[FWD_GROUP];
+			float nal[FWD_GROUP];
+			bool nok[FWD_GROUP];
+			// (reads past the list end stay inside hits[warp][] thanks to its FWD_GROUP pad; results are masked)
+			eval_group(min(h + FWD_GROUP, BLEND_BATCH), njj, nal, nok);
+			// serial part, branch-free: the feature rows are fetched up front (independent LDS) and every
+			// update is predicated, so a hit costs one short dependent chain T -> test_T -> compare
+			float4 f[FWD_GROUP];
+#pragma unroll
+			for (int k = 0; k < FWD_GROUP; k++) f[k] = lds_f4(&bs.feat[jj[k]]);
+#pragma unroll
+			for (int k = 0; k < FWD_GROUP; k++) {
+				const float alpha = al[k];
+				const float test_T = fmul(T, fsub(1.0f, alpha));
+				const bool live = ok[k] && !done;
+				const bool stop = live && (test_T < 0.0001f);
+				const bool upd = live && !stop;
+				done = done || stop;
+				const float c0 = ffma(T, fmul(alpha, f[k].x), C0);
+				const float c1 = ffma(T, fmul(alpha, f[k].y), C1);
+				const float c2 = ffma(T, fmul(alpha, f[k].z), C2);
+				const float wn = ffma(T, alpha, weight);
+				const float dn = ffma(T, fmul(alpha, f[k].w), Dp);
+				C0 = upd ? c0 : C0; C1 = upd ? c1 : C1; C2 = upd ? c2 : C2;
+				weight = upd ? wn : weight; Dp = upd ? dn : Dp;
+				T = upd ? test_T : T;
+				last_contributor = upd ? (uint32_t)(base + jj[k] + 1) : last_contributor;
+			}
+#pragma unroll
+			for (int k = 0; k < FWD_GROUP; k++) { jj[k] = njj[k]; al[k] = nal[k]; ok[k] = nok[k]; }
+			if (__all_sync(full, done)) break;
+		}
+	}
+#ifdef MOSS_TILE_TIMING
+	if (sub == 0) MOSS_TT(3);
+#endif
 
 	if (inside) {
 		const int pix = py * W + px;
@@ -262,43 +287,60 @@ __device__ __forceinline__ float warp_reduce8(const float (&v)[8])
 	s += __shfl_xor_sync(full, s, 1);
 	return s;
 }
-__device__ __forceinline__ float warp_reduce1(float v)
+// Sum a and b over the warp: lanes 0-15 end with the total of a, lanes 16-31 with the total of b (5 shuffles).
+__device__ __forceinline__ float warp_reduce2(float a, float b)
 {
+	const unsigned full = 0xffffffffu;
+	const bool hi = threadIdx.x & 16;
+	float s = (hi ? b : a) + __shfl_xor_sync(full, hi ? a : b, 16);
 #pragma unroll
-	for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-	return v;
+	for (int o = 8; o > 0; o >>= 1) s += __shfl_xor_sync(full, s, o);
+	return s;
 }
 
 constexpr int NGRAD = 9;          // dcolor[3], dmean2D.xy, dconic.{x,y,w}, dopacity
 constexpr int BWD_BATCH = 128;    // instances staged per round of the backward
+constexpr int BWD_GROUP = 2;      // hits processed together (their independent halves interleave)
 
-__global__ void __launch_bounds__(TILE_PIX)
+template <int NW>
+struct BwdSmem {
+	uint32_t id[BWD_BATCH];
+	float2 xy[BWD_BATCH];
+	float4 co[BWD_BATCH];
+	float4 feat[BWD_BATCH];
+	uint8_t mask[BWD_BATCH];
+	uint32_t written[BWD_BATCH];                      // bit w: warp w stored a gradient row for this slot
+	__align__(8) uint8_t hits[NW][BWD_BATCH + 8];
+	uint32_t warp_last[NW];
+	float grad[NW * BWD_BATCH * NGRAD];               // [warp][slot][component]: each (warp, slot) is written at
+	                                                  // most once per batch -> plain stores, no shared atomics
+};
+
+template <int NW>
+__global__ void __launch_bounds__(32 * NW)
 blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b,
 	const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas,
 	float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
 	float* __restrict__ dL_dcolor)
 {
-	__shared__ uint32_t s_id[BWD_BATCH];
-	__shared__ float2 s_xy[BWD_BATCH];
-	__shared__ float4 s_co[BWD_BATCH];
-	__shared__ float4 s_feat[BWD_BATCH];
-	__shared__ uint8_t s_mask[BWD_BATCH];
-	__shared__ uint32_t s_written[BWD_BATCH];                 // bit w: warp w stored a gradient row for this slot
-	__shared__ float s_grad[NPATCH * BWD_BATCH * NGRAD];      // [warp][slot][component]: each (warp, slot) is written
-	                                                          // at most once per batch -> plain stores, no atomics
-	__shared__ uint32_t s_warp_last[NPATCH];
+	constexpr int NT = 32 * NW;
+	constexpr int SPLIT = NPATCH / NW;
+	constexpr int PER = (BWD_BATCH + NT - 1) / NT;
+	__shared__ BwdSmem<NW> sm;
 
-	const int tile = blockIdx.x;
+	const int tile = (int)im.tile_order[blockIdx.x / SPLIT];   // deepest tiles first (binning.cuh)
+	const int sub = blockIdx.x % SPLIT;
 	const int tile_y = tile / grid_x, tile_x = tile - tile_y * grid_x;
 	const uint2 range = im.ranges[tile];
 	const int n = (int)(range.y - range.x);
 	if (n == 0) return;
 
 	int px, py;
-	pixel_of_thread(tile_x, tile_y, px, py);
+	pixel_of_thread<NW>(tile_x, tile_y, sub, px, py);
 	const bool inside = px < W && py < H;
 	const int pix = py * W + px;
 	const float pxf = (float)px, pyf = (float)py;
+	const float tile_px0 = (float)(tile_x * TILE_X), tile_py0 = (float)(tile_y * TILE_Y);
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const unsigned full = 0xffffffffu;
 
@@ -314,119 +356,179 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 	}
 	const float bg_dot_dpixel = bg[0] * dpix[0] + bg[1] * dpix[1] + bg[2] * dpix[2];
 
-	// nothing behind the furthest "last contributor" of the tile (of the warp) can receive gradient
+	// nothing behind the furthest "last contributor" of the block (of the warp) can receive gradient
 	const uint32_t warp_last = __reduce_max_sync(full, last_contributor);
-	if (lane == 0) s_warp_last[warp] = warp_last;
+	if (lane == 0) sm.warp_last[warp] = warp_last;
 	__syncthreads();
-	uint32_t tile_last = 0;
+	uint32_t block_last = 0;
 #pragma unroll
-	for (int w = 0; w < NPATCH; w++) tile_last = max(tile_last, s_warp_last[w]);
-	if (tile_last == 0) return;
+	for (int w = 0; w < NW; w++) block_last = max(block_last, sm.warp_last[w]);
+	if (block_last == 0) return;
+#ifdef MOSS_TILE_TIMING
+	if (sub == 0) MOSS_TT(4);
+#endif
 
 	float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
 	float accum_depth_rec = 0.f, last_depth = 0.f, accum_alpha_rec = 0.f, last_alpha = 0.f;
 	const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
-	// batch slot j holds forward position (0-based) tile_last-1-(base+j): the walk is back to front
-	for (int base = 0; base < (int)tile_last; base += BWD_BATCH) {
-		__syncthreads();
-		const int i = base + threadIdx.x;
-		uint32_t hit = 0;
-		if (threadIdx.x < BWD_BATCH && i < (int)tile_last) {
-			const uint32_t pos = range.x + tile_last - 1 - i;
-			const uint32_t id = b.point_list[pos];
-			hit = b.hit_mask[pos];
-			s_id[threadIdx.x] = id;
-			s_xy[threadIdx.x] = g.means2D[id];
-			s_co[threadIdx.x] = g.conic_opacity[id];
-			s_feat[threadIdx.x] = g.feat[id];
+	// batch slot s holds forward position (0-based) block_last-1-(base+s): the walk is back to front.
+	// Software pipeline as in the forward: the gathers of the next batch are issued before this one is processed.
+	uint32_t nid[PER];
+	float2 nxy[PER];
+	float4 nco[PER], nfeat[PER];
+#pragma unroll
+	for (int u = 0; u < PER; u++) {
+		const int i = u * NT + (int)threadIdx.x;
+		nid[u] = 0u; nxy[u] = make_float2(0.f, 0.f); nco[u] = make_float4(0.f, 0.f, 0.f, 0.f); nfeat[u] = nco[u];
+		if (u * NT + (int)threadIdx.x < BWD_BATCH && i < (int)block_last) {
+			nid[u] = b.point_list[range.x + block_last - 1 - i];
+			nxy[u] = g.means2D[nid[u]]; nco[u] = g.conic_opacity[nid[u]]; nfeat[u] = g.feat[nid[u]];
 		}
-		if (threadIdx.x < BWD_BATCH) { s_mask[threadIdx.x] = (uint8_t)hit; s_written[threadIdx.x] = 0u; }
+	}
+
+	for (int base = 0; base < (int)block_last; base += BWD_BATCH) {
 		__syncthreads();
-
-		const int cnt = min(BWD_BATCH, (int)tile_last - base);
-		for (int sb = 0; sb < cnt; sb += 32) {
-			// forward position of slot sb+lane; instances at/behind the warp's last contributor get no gradient
-			const int fpos = (int)tile_last - 1 - (base + sb + lane);
-			uint32_t bits = __ballot_sync(full, ((s_mask[sb + lane] >> warp) & 1u) && fpos < (int)warp_last);
-			while (bits) {
-				const int j = sb + __ffs(bits) - 1;
-				bits &= bits - 1u;
-				const uint32_t contributor = tile_last - 1 - (uint32_t)(base + j);
-				bool valid = contributor < last_contributor;
-				const float2 xy = s_xy[j];
-				const float4 co = s_co[j];
-				const float dx = xy.x - pxf, dy = xy.y - pyf;
-				const float power = blend_power(dx, dy, co);
-				valid = valid && !(power > 0.0f);
-				const float G = expf(power);
-				const float alpha = fminf(fmul(co.w, G), 0.99f);
-				valid = valid && !(alpha < 1.0f / 255.0f);
-				if (!__any_sync(full, valid)) continue;
-
-				float v[8], v_opa = 0.f;
 #pragma unroll
-				for (int k = 0; k < 8; k++) v[k] = 0.f;
-				if (valid) {
-					const float4 f = s_feat[j];
-					T = T / (1.f - alpha);
-					const float dchannel_dcolor = alpha * T;
-					float dL_dopa = 0.0f;
-					const float c[3] = {f.x, f.y, f.z};
-#pragma unroll
-					for (int ch = 0; ch < 3; ch++) {
-						accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-						last_color[ch] = c[ch];
-						dL_dopa += (c[ch] - accum_rec[ch]) * dpix[ch];
-						v[ch] = dchannel_dcolor * dpix[ch];
-					}
-					accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
-					last_depth = f.w;
-					dL_dopa += (f.w - accum_depth_rec) * ddepth;
-					accum_alpha_rec = last_alpha + (1.f - last_alpha) * accum_alpha_rec;
-					dL_dopa += (1.f - accum_alpha_rec) * dalpha;
-					dL_dopa *= T;
-					last_alpha = alpha;
-					dL_dopa += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-
-					const float dL_dG = co.w * dL_dopa;
-					const float gdx = G * dx, gdy = G * dy;
-					const float dG_ddelx = -gdx * co.x - gdy * co.y;
-					const float dG_ddely = -gdy * co.z - gdx * co.y;
-					v[3] = dL_dG * dG_ddelx * ddelx_dx;
-					v[4] = dL_dG * dG_ddely * ddely_dy;
-					v[5] = -0.5f * gdx * dx * dL_dG;
-					v[6] = -0.5f * gdx * dy * dL_dG;
-					v[7] = -0.5f * gdy * dy * dL_dG;
-					v_opa = G * dL_dopa;
+		for (int u = 0; u < PER; u++) {
+			const int s = u * NT + (int)threadIdx.x;
+			if (s < BWD_BATCH) {
+				uint32_t hit = 0;
+				if (base + s < (int)block_last) {
+					sm.id[s] = nid[u]; sm.xy[s] = nxy[u]; sm.co[s] = nco[u]; sm.feat[s] = nfeat[u];
+					hit = patch_hit_mask<NW>(nxy[u], nco[u], tile_px0, tile_py0, sub);
 				}
-				const float s8 = warp_reduce8(v);
-				const float s1 = warp_reduce1(v_opa);
-				float* row = s_grad + (warp * BWD_BATCH + j) * NGRAD;
-				if ((lane & 3) == 0) row[lane >> 2] = s8;
-				else if (lane == 1) { row[8] = s1; atomicOr(&s_written[j], 1u << warp); }
+				sm.mask[s] = (uint8_t)hit;
+				sm.written[s] = 0u;
+			}
+		}
+		__syncthreads();
+#pragma unroll
+		for (int u = 0; u < PER; u++) {
+			const int s = u * NT + (int)threadIdx.x;
+			const int i = base + BWD_BATCH + s;
+			if (s < BWD_BATCH && i < (int)block_last) {
+				nid[u] = b.point_list[range.x + block_last - 1 - i];
+				nxy[u] = g.means2D[nid[u]]; nco[u] = g.conic_opacity[nid[u]]; nfeat[u] = g.feat[nid[u]];
+			}
+		}
+
+		// compact the slots that can reach this warp's patch AND lie in front of the warp's last contributor
+		const int cnt = min(BWD_BATCH, (int)block_last - base);
+		int nh = 0;
+#pragma unroll
+		for (int sb = 0; sb < BWD_BATCH; sb += 32) {
+			const int fpos = (int)block_last - 1 - (base + sb + lane);
+			const bool mine = (sb + lane < cnt) && ((sm.mask[sb + lane] >> warp) & 1u) && fpos < (int)warp_last;
+			const uint32_t bits = __ballot_sync(full, mine);
+			if (mine) sm.hits[warp][nh + __popc(bits & ((1u << lane) - 1u))] = (uint8_t)(sb + lane);
+			nh += __popc(bits);
+		}
+		__syncwarp();
+
+		for (int h = 0; h < nh; h += BWD_GROUP) {
+			// ---- independent part of both hits: geometry, alpha, validity ------------------------------
+			int jj[BWD_GROUP];
+			float dx[BWD_GROUP], dy[BWD_GROUP], Gs[BWD_GROUP], al[BWD_GROUP], ra[BWD_GROUP];
+			float4 cos_[BWD_GROUP], fs[BWD_GROUP];
+			bool valid[BWD_GROUP];
+#pragma unroll
+			for (int k = 0; k < BWD_GROUP; k++) {
+				const int j = (int)sm.hits[warp][min(h + k, nh - 1)];
+				jj[k] = j;
+				const float2 xy = sm.xy[j];
+				const float4 co = sm.co[j];
+				cos_[k] = co;
+				fs[k] = lds_f4(&sm.feat[j]);
+				dx[k] = xy.x - pxf; dy[k] = xy.y - pyf;
+				const float power = blend_power(dx[k], dy[k], co);
+				Gs[k] = expf(power);
+				al[k] = fminf(fmul(co.w, Gs[k]), 0.99f);
+				ra[k] = __fdividef(1.0f, 1.0f - al[k]);
+				const uint32_t contributor = block_last - 1u - (uint32_t)(base + j);
+				valid[k] = (h + k < nh) && contributor < last_contributor && !(power > 0.0f) && !(al[k] < 1.0f / 255.0f);
+			}
+			bool any_valid = false;
+#pragma unroll
+			for (int k = 0; k < BWD_GROUP; k++) any_valid = any_valid || valid[k];
+			if (!__any_sync(full, any_valid)) continue;
+
+			// ---- recurrences (serial over the hits, predicated) and gradient terms ------------------------
+			float v[BWD_GROUP][8], v_opa[BWD_GROUP];
+#pragma unroll
+			for (int k = 0; k < BWD_GROUP; k++) {
+				const bool ok = valid[k];
+				const float alpha = al[k];
+				const float4 f = fs[k];
+				const float4 co = cos_[k];
+				const float Tn = T * ra[k];                       // T / (1 - alpha), DGR backward.cu:520
+				const float omla = 1.f - last_alpha;
+				const float dchannel_dcolor = alpha * Tn;
+				const float c[3] = {f.x, f.y, f.z};
+				float dL_dopa = 0.0f;
+#pragma unroll
+				for (int ch = 0; ch < 3; ch++) {
+					const float arc = last_alpha * last_color[ch] + omla * accum_rec[ch];
+					dL_dopa += (c[ch] - arc) * dpix[ch];
+					v[k][ch] = ok ? dchannel_dcolor * dpix[ch] : 0.f;
+					accum_rec[ch] = ok ? arc : accum_rec[ch];
+					last_color[ch] = ok ? c[ch] : last_color[ch];
+				}
+				const float adr = last_alpha * last_depth + omla * accum_depth_rec;
+				dL_dopa += (f.w - adr) * ddepth;
+				const float aar = last_alpha + omla * accum_alpha_rec;
+				dL_dopa += (1.f - aar) * dalpha;
+				dL_dopa *= Tn;
+				dL_dopa += (-T_final * ra[k]) * bg_dot_dpixel;
+				accum_depth_rec = ok ? adr : accum_depth_rec;
+				last_depth = ok ? f.w : last_depth;
+				accum_alpha_rec = ok ? aar : accum_alpha_rec;
+				last_alpha = ok ? alpha : last_alpha;
+				T = ok ? Tn : T;
+
+				const float dL_dG = co.w * dL_dopa;
+				const float gdx = Gs[k] * dx[k], gdy = Gs[k] * dy[k];
+				const float dG_ddelx = -gdx * co.x - gdy * co.y;
+				const float dG_ddely = -gdy * co.z - gdx * co.y;
+				v[k][3] = ok ? dL_dG * dG_ddelx * ddelx_dx : 0.f;
+				v[k][4] = ok ? dL_dG * dG_ddely * ddely_dy : 0.f;
+				v[k][5] = ok ? -0.5f * gdx * dx[k] * dL_dG : 0.f;
+				v[k][6] = ok ? -0.5f * gdx * dy[k] * dL_dG : 0.f;
+				v[k][7] = ok ? -0.5f * gdy * dy[k] * dL_dG : 0.f;
+				v_opa[k] = ok ? Gs[k] * dL_dopa : 0.f;
+			}
+			// ---- warp reduction, one row per (warp, slot) ---------------------------------------------------
+			const float so = warp_reduce2(v_opa[0], v_opa[1]);
+#pragma unroll
+			for (int k = 0; k < BWD_GROUP; k++) {
+				const float s8 = warp_reduce8(v[k]);
+				if (h + k < nh) {
+					float* row = sm.grad + (warp * BWD_BATCH + jj[k]) * NGRAD;
+					if ((lane & 3) == 0) row[lane >> 2] = s8;
+					if (lane == 1 + 16 * k) { row[8] = so; atomicOr(&sm.written[jj[k]], 1u << warp); }
+				}
 			}
 		}
 		__syncthreads();
 
-		// flush the batch: the rows of the warps that hit a slot are summed in warp order, then ONE global atomic
-		// per (instance, component); thread t takes slot t%128 and components 0-4 (t<128) or 5-8
-		{
-			const int j = threadIdx.x & (BWD_BATCH - 1);
-			const uint32_t wmask = s_written[j];
+		// flush the batch: the rows of the warps that hit a slot are summed in warp order, then ONE global atomic per
+		// (instance, component); a thread takes one slot and one of the component groups {0-4}, {5-8}
+		for (int t = threadIdx.x; t < 2 * BWD_BATCH; t += NT) {
+			const int j = t & (BWD_BATCH - 1);
+			const uint32_t wmask = sm.written[j];
 			if (wmask) {
-				const int k0 = (threadIdx.x < BWD_BATCH) ? 0 : 5;
+				const int k0 = (t < BWD_BATCH) ? 0 : 5;
 				float r[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-				for (int w = 0; w < NPATCH; w++) {
+				for (int w = 0; w < NW; w++) {
 					if (wmask & (1u << w)) {
-						const float* row = s_grad + (w * BWD_BATCH + j) * NGRAD + k0;
+						const float* row = sm.grad + (w * BWD_BATCH + j) * NGRAD + k0;
 #pragma unroll
 						for (int k = 0; k < 4; k++) r[k] += row[k];
 						if (k0 == 0) r[4] += row[4];
 					}
 				}
-				const size_t id = s_id[j];
+				const size_t id = sm.id[j];
 				if (k0 == 0) {
 					atomicAdd(dL_dcolor + 3 * id + 0, r[0]);
 					atomicAdd(dL_dcolor + 3 * id + 1, r[1]);
@@ -442,6 +544,9 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 			}
 		}
 	}
+#ifdef MOSS_TILE_TIMING
+	if (sub == 0) { MOSS_TT(5); if (threadIdx.x == 0) { g_tile_timing[tile * 8 + 6] = (long long)block_last; g_tile_timing[tile * 8 + 7] = (long long)n; } }
+#endif
 }
 
 } // namespace moss

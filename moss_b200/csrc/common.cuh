@@ -56,12 +56,12 @@ struct ImageWS {
 	uint32_t* n_contrib;      // [N]
 	uint32_t* tile_count;     // [T]  per-tile instance count, then scatter cursor
 	uint2*    ranges;         // [T]  [first, last) into the sorted list
-	uint32_t* counters;       // [4]  num_rendered, overflow, capacity, reserved
+	uint32_t* tile_order;     // [T]  launch order of the blend kernels: tiles by descending instance count
+	uint32_t* counters;       // [4]  num_rendered, overflow, capacity, non-empty tiles
 };
 struct BinWS {
 	unsigned long long* keys; // [cap] (depth_bits << 32 | gaussian id), grouped per tile, sorted in place
 	uint32_t* point_list;     // [cap] sorted gaussian ids
-	uint8_t* hit_mask;        // [cap] bit w: the instance can reach alpha >= 1/255 in patch (warp) w of its tile
 	unsigned long long* keys_sorted; // [cap] (tile << 32 | depth_bits), only with EXPORT_KEYS
 };
 
@@ -96,6 +96,7 @@ __host__ __device__ inline ImageWS carve_image(char* base, size_t N, size_t T, s
 	s.n_contrib = carve<uint32_t>(p, N);
 	s.tile_count = carve<uint32_t>(p, T);
 	s.ranges = carve<uint2>(p, T);
+	s.tile_order = carve<uint32_t>(p, T);
 	s.counters = carve<uint32_t>(p, 4);
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return s;
@@ -106,7 +107,6 @@ __host__ __device__ inline BinWS carve_bin(char* base, size_t cap, bool export_k
 	BinWS b;
 	b.keys = carve<unsigned long long>(p, cap);
 	b.point_list = carve<uint32_t>(p, cap);
-	b.hit_mask = carve<uint8_t>(p, cap);
 	b.keys_sorted = export_keys ? carve<unsigned long long>(p, cap) : nullptr;
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return b;

@@ -137,6 +137,16 @@ inline ViewParams make_view(const MossScene* sc)
 	return vp;
 }
 
+// Blend block shape (1 whole tile / 2 half / 3 quarter).  Small images have few busy tiles and the deepest one sets
+// the launch time, so its patches are spread over more SMs; large images have enough tiles to fill the machine
+// and prefer fewer, larger blocks (less duplicated staging).
+inline int blend_split(unsigned flags, int T)
+{
+	const int f = (int)((flags & MOSS_FLAG_SPLIT_MASK) >> MOSS_FLAG_SPLIT_SHIFT);
+	if (f) return f;
+	return T <= 2048 ? 3 : (T <= 6144 ? 2 : 1);
+}
+
 __global__ void reset_overflow_kernel(uint32_t* counters, uint32_t capacity)
 {
 	counters[1] = counters[0] > capacity ? 1u : 0u;
@@ -179,7 +189,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -218,7 +228,7 @@ size_t moss_binning_workspace_bytes_ex(long long capacity, int export_keys)
 size_t moss_binning_workspace_bytes(long long capacity) { return moss_binning_workspace_bytes_ex(capacity, 0); }
 long long moss_binning_capacity(size_t bytes, int export_keys)
 {
-	const size_t per = export_keys ? 21 : 13;
+	const size_t per = export_keys ? 20 : 12;
 	long long lo = 0, hi = (long long)(bytes / per) + 1;   // largest cap with bytes_ex(cap) <= bytes
 	while (lo < hi) {
 		const long long mid = lo + (hi - lo + 1) / 2;
@@ -270,7 +280,7 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 		int* host_R = nullptr;
 		if (slot >= 0) MOSS_CUDA_TRY(cudaHostGetDevicePointer((void**)&host_R, g_slots.host + slot, 0));
 		{ MOSS_STAGE(MOSS_STAGE_TILE_SCAN, stream);
-		tile_scan_kernel<<<1, SCAN_THREADS, 0, stream>>>(T, im.tile_count, im.ranges, im.counters, capacity, host_R); }
+		tile_scan_kernel<<<1, SCAN_THREADS, 0, stream>>>(T, im.tile_count, im.ranges, im.counters, capacity, host_R, im.tile_order); }
 		MOSS_CHECK_LAUNCH(stream, flags);
 		if (slot >= 0) MOSS_CUDA_TRY(cudaEventRecord(g_slots.ev[slot], stream));
 	} else {
@@ -283,11 +293,25 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 	scatter_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, vp.grid_x, radii, g, im.ranges, im.tile_count,
 		im.counters, b.keys); }
 	MOSS_CHECK_LAUNCH(stream, flags);
+	{ MOSS_STAGE(MOSS_STAGE_TILE_SORT, stream);
+	tile_sort_kernel<<<T, TILE_PIX, 0, stream>>>(im, b); }
+	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_FWD, stream);
-	if (flags & MOSS_FLAG_NO_CULL)
-		blend_forward_kernel<false><<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
-	else
-		blend_forward_kernel<true><<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha); }
+	const bool cull = !(flags & MOSS_FLAG_NO_CULL);
+	switch (blend_split(flags, T)) {
+	case 1:
+		if (cull) blend_forward_kernel<true, 8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+		else blend_forward_kernel<false, 8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+		break;
+	case 2:
+		if (cull) blend_forward_kernel<true, 4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+		else blend_forward_kernel<false, 4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+		break;
+	default:
+		if (cull) blend_forward_kernel<true, 2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+		else blend_forward_kernel<false, 2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+		break;
+	} }
 	MOSS_CHECK_LAUNCH(stream, flags);
 
 	if (flags & MOSS_FLAG_ASYNC) return MOSS_OK;
@@ -330,8 +354,14 @@ int moss_rasterize_backward(void* stream_, const MossScene* sc, unsigned flags, 
 	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
 
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_BWD, stream);
-	blend_backward_kernel<<<T, TILE_PIX, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha,
-		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor); }
+	switch (blend_split(flags, T)) {
+	case 1: blend_backward_kernel<8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha,
+		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor); break;
+	case 2: blend_backward_kernel<4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha,
+		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor); break;
+	default: blend_backward_kernel<2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha,
+		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor); break;
+	} }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_PREPROCESS_BWD, stream);
 	preprocess_backward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
@@ -427,5 +457,18 @@ long long moss_export_state(void* stream_, const MossScene* sc, int which, void*
 	if (n > 0 && cudaMemcpyAsync(dst, src, (size_t)n, cudaMemcpyDeviceToDevice, stream) != cudaSuccess) return -MOSS_ERR_CUDA;
 	return n;
 }
+
+#ifdef MOSS_TILE_TIMING
+int moss_debug_tile_timing(long long* dst, int tiles)
+{
+	cudaDeviceSynchronize();
+	return (int)cudaMemcpyFromSymbol(dst, moss::g_tile_timing, sizeof(long long) * 8 * (size_t)tiles);
+}
+int moss_debug_tile_detail(long long* dst, int tiles)
+{
+	cudaDeviceSynchronize();
+	return (int)cudaMemcpyFromSymbol(dst, moss::g_tile_detail, sizeof(long long) * 16 * (size_t)tiles);
+}
+#endif
 
 } // extern "C"

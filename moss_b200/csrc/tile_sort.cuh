@@ -1,0 +1,264 @@
+// K4a: per-tile segment sort (one 256-thread block per tile, deepest tiles first).
+//
+// Replaces the reference's global 64-bit radix sort over all instances + identifyTileRanges
+// (DGR/cuda_rasterizer/rasterizer_impl.cu:302-320): binning.cuh already grouped the instances by tile, so every
+// tile sorts its own (depth_bits<<32 | id) keys -- a total order, hence the result is bit-identical to the
+// reference's stable sort of (tile|depth) keys emitted in ascending Gaussian order.
+// Also holds the small device helpers shared by the blend kernels (blend.cuh).
+#pragma once
+#include "common.cuh"
+
+namespace moss {
+
+#ifdef MOSS_TILE_TIMING
+// developer build only (tools/tile_timing.py): per-tile phase clocks, [tile][8]
+__device__ long long g_tile_timing[16384 * 8];
+__device__ long long g_tile_detail[16384 * 16];
+__device__ __forceinline__ long long moss_gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return (long long)t; }
+#define MOSS_TT(slot) do { if (threadIdx.x == 0) g_tile_timing[tile * 8 + (slot)] = moss_gtime(); } while (0)
+#define MOSS_TD(slot) do { if (threadIdx.x == 0) g_tile_detail[tile * 16 + (slot)] = clock64(); } while (0)
+#else
+#define MOSS_TT(slot) do { } while (0)
+#define MOSS_TD(slot) do { } while (0)
+#endif
+
+// Shared-memory loads the compiler may not sink under a predicate.  nvcc turns `cond && smem[i] < x` (and even a
+// select on a clamped index) into a divergent branch around the LDS, which exposes one shared-memory latency plus
+// a BSSY/BSYNC pair per element; these latency-bound loops want the load issued unconditionally and masked after.
+__device__ __forceinline__ unsigned long long lds_u64(const void* p)
+{
+	unsigned long long v;
+	asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+	return v;
+}
+__device__ __forceinline__ float4 lds_f4(const void* p)
+{
+	float4 v;
+	asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+		: "r"((uint32_t)__cvta_generic_to_shared(p)));
+	return v;
+}
+
+constexpr int SORT_CAP = 4096;   // instances per tile sorted in shared memory (32 KB)
+constexpr int NPATCH = TILE_PIX / 32;   // 8 warps = 2 (x) by 4 (y) patches of 8x4 pixels
+
+// Ascending bitonic network over a[0..n) with virtual +inf padding up to the next power of two
+// ("flip" formulation: every compare-exchange is ascending, so padding never moves).
+template <typename KeyPtr>
+__device__ __forceinline__ void block_bitonic_sort(KeyPtr a, int n)
+{
+	int npow2 = 1;
+	while (npow2 < n) npow2 <<= 1;
+	const int half = npow2 >> 1;
+	for (int k = 2; k <= npow2; k <<= 1) {
+		for (int j = k >> 1; j > 0; j >>= 1) {
+			const bool flip = (j == (k >> 1));
+			for (int t = threadIdx.x; t < half; t += TILE_PIX) {
+				const int blk = t / j, off = t - blk * j;
+				const int i = blk * 2 * j + off;
+				const int p = flip ? (blk * 2 * j + 2 * j - 1 - off) : (i + j);
+				if (p < n) {
+					const unsigned long long x = a[i], y = a[p];
+					if (x > y) { a[i] = y; a[p] = x; }
+				}
+			}
+			__syncthreads();
+		}
+	}
+}
+
+// power = -0.5f*(A dx^2 + C dy^2) - B dx dy  (DGR forward.cu:340, backward.cu:507) in the rounding sequence of
+// the reference's sm_100 SASS: q = fma(dx, dx*A, dy*(dy*C)); power = fma(q, -0.5, -(dy*(dx*B))).
+__device__ __forceinline__ float blend_power(float dx, float dy, const float4& co)
+{
+	const float q = ffma(dx, fmul(dx, co.x), fmul(dy, fmul(dy, co.z)));
+	return ffma(q, -0.5f, -fmul(dy, fmul(dx, co.y)));
+}
+
+// ---- per-tile sort -----------------------------------------------------------------------------------
+// Sorts the tile's n (depth_bits<<32 | id) keys (all distinct: ids are) and writes the sorted id list (and, for
+// parity exports, the reference's 64-bit tile|depth keys).
+//   n <= 256           : bitonic network in shared memory (<= 36 compare-exchange stages);
+//   256 < n <= SORT_CAP: SAMPLE SORT, O(n) work: the depth words of 255 evenly spaced keys are rank-sorted and
+//                        used as splitters; every key finds its bucket by binary search, buckets are laid out
+//                        by a counting sort (shared-memory atomics), and the final position of a key is its
+//                        bucket's start + the number of smaller keys in that bucket (expected bucket size
+//                        n/256 <= 16, observed maximum ~45).  The deepest ZJU tile (1704 keys) takes ~22k
+//                        cycles; the bitonic network took ~8x that, and it sits on the launch's critical path;
+//   n > SORT_CAP       : in-place bitonic network on the global segment (rare; correctness fallback).
+struct SortSmem {
+	unsigned long long keys[SORT_CAP];   // bucketed keys (sample sort) / the keys themselves (bitonic)
+	uint32_t samp[256];                  // sorted depth words of the splitters
+	uint32_t start[257];
+	uint32_t cur[256];
+	uint32_t wsum[8];
+	uint8_t bucket[SORT_CAP];            // bucket of key i (by position in the unsorted segment)
+	uint8_t bslot[SORT_CAP];             // bucket of the key stored in slot p of the bucketed array
+};
+
+__device__ __forceinline__ void emit_sorted(const BinWS& b, uint32_t dst, int tile, unsigned long long k)
+{
+	b.point_list[dst] = (uint32_t)k;
+	if (b.keys_sorted) b.keys_sorted[dst] = ((unsigned long long)tile << 32) | (k >> 32);
+}
+
+__device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 range, int n, int tile)
+{
+	unsigned long long* gk = b.keys + range.x;
+	const int tid = threadIdx.x;
+	if (n <= TILE_PIX) {
+		if (tid < n) sm.keys[tid] = gk[tid];
+		__syncthreads();
+		block_bitonic_sort(sm.keys, n);
+		if (tid < n) emit_sorted(b, range.x + tid, tile, sm.keys[tid]);
+		return;
+	}
+	if (n > SORT_CAP) {
+		__syncthreads();
+		block_bitonic_sort(gk, n);
+		for (int i = tid; i < n; i += TILE_PIX) emit_sorted(b, range.x + i, tile, gk[i]);
+		return;
+	}
+	MOSS_TD(8);
+	// 1. splitters: the depth words of 255 evenly spaced keys, sorted by rank (every thread counts the samples
+	//    below its own: 255 broadcast reads, no barrier inside -- a 36-stage bitonic network costs ~5x more).
+	//    Buckets are defined on the depth word only: bucket(k) = #splitters < depth(k) is monotone in the full
+	//    key, which is all the counting sort needs; the ranking inside a bucket compares full keys.
+	const uint32_t mine = tid < 255 ? (uint32_t)(gk[(int)(((long long)(tid + 1) * n) >> 8)] >> 32) : 0xffffffffu;
+	uint32_t* scratch = reinterpret_cast<uint32_t*>(sm.keys);   // the bucketed keys are written only in step 4
+	scratch[tid] = mine;
+	sm.cur[tid] = 0u;
+	__syncthreads();
+	{
+		// (value, index) compared as one 64-bit number: ties broken by sample index, so ranks are a permutation;
+		// four independent counters keep the adds off one dependent chain
+		const unsigned long long me = ((unsigned long long)mine << 8) | (unsigned)tid;
+		int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+#pragma unroll 16
+		for (int q = 0; q < 256; q += 4) {
+			const uint4 v = *reinterpret_cast<const uint4*>(scratch + q);
+			r0 += ((((unsigned long long)v.x << 8) | (unsigned)(q + 0)) < me) ? 1 : 0;
+			r1 += ((((unsigned long long)v.y << 8) | (unsigned)(q + 1)) < me) ? 1 : 0;
+			r2 += ((((unsigned long long)v.z << 8) | (unsigned)(q + 2)) < me) ? 1 : 0;
+			r3 += ((((unsigned long long)v.w << 8) | (unsigned)(q + 3)) < me) ? 1 : 0;
+		}
+		sm.samp[(r0 + r1) + (r2 + r3)] = mine;
+	}
+	__syncthreads();
+	MOSS_TD(4);
+	// Steps 2, 4 and 5 handle SORT_ILP keys per thread at a time so their global loads, binary searches and
+	// bucket scans overlap (each step is a chain of dependent shared-memory reads per key).
+	constexpr int SORT_ILP = 8;
+	// 2. bucket = number of splitters below the key (0..255); bucket sizes
+	for (int c0 = 0; c0 < n; c0 += SORT_ILP * TILE_PIX) {
+		unsigned long long key[SORT_ILP];
+		int pos[SORT_ILP];
+#pragma unroll
+		for (int u = 0; u < SORT_ILP; u++) {
+			const int i = c0 + u * TILE_PIX + tid;
+			key[u] = i < n ? gk[i] : ~0ull;
+			pos[u] = 0;
+		}
+#pragma unroll
+		for (int st = 128; st > 0; st >>= 1) {
+#pragma unroll
+			for (int u = 0; u < SORT_ILP; u++)
+				pos[u] += (sm.samp[pos[u] + st - 1] < (uint32_t)(key[u] >> 32)) ? st : 0;
+		}
+#pragma unroll
+		for (int u = 0; u < SORT_ILP; u++) {
+			const int i = c0 + u * TILE_PIX + tid;
+			if (i < n) { sm.bucket[i] = (uint8_t)pos[u]; atomicAdd(&sm.cur[pos[u]], 1u); }
+		}
+	}
+	__syncthreads();
+	MOSS_TD(5);
+	// 3. exclusive scan over the 256 bucket sizes
+	{
+		const int lane = tid & 31, warp = tid >> 5;
+		const uint32_t c = sm.cur[tid];
+		uint32_t v = c;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint32_t nb = __shfl_up_sync(0xffffffffu, v, o);
+			if (lane >= o) v += nb;
+		}
+		if (lane == 31) sm.wsum[warp] = v;
+		__syncthreads();
+		uint32_t off = 0;
+#pragma unroll
+		for (int w = 0; w < 8; w++) off += (w < warp) ? sm.wsum[w] : 0u;
+		const uint32_t excl = off + v - c;
+		sm.start[tid] = excl;
+		sm.cur[tid] = excl;
+		if (tid == 255) sm.start[256] = (uint32_t)n;
+	}
+	__syncthreads();
+	// 4. counting-sort scatter into the buckets
+	for (int c0 = 0; c0 < n; c0 += SORT_ILP * TILE_PIX) {
+#pragma unroll
+		for (int u = 0; u < SORT_ILP; u++) {
+			const int i = c0 + u * TILE_PIX + tid;
+			if (i < n) {
+				const uint8_t bk = sm.bucket[i];
+				const uint32_t slot = atomicAdd(&sm.cur[bk], 1u);
+				sm.keys[slot] = gk[i];
+				sm.bslot[slot] = bk;
+			}
+		}
+	}
+	__syncthreads();
+	MOSS_TD(6);
+	// 5. final position = bucket start + rank inside the bucket.  Slot-centric: consecutive lanes hold
+	//    consecutive slots, i.e. mostly the same bucket, so the scan reads are near-broadcast (a key-centric
+	//    scan issues random-address LDS.64 and saturates the shared-memory pipe with bank conflicts).
+	for (int c0 = 0; c0 < n; c0 += SORT_ILP * TILE_PIX) {
+		unsigned long long key[SORT_ILP];
+		uint32_t st[SORT_ILP], len[SORT_ILP], r[SORT_ILP];
+		uint32_t maxlen = 0;
+#pragma unroll
+		for (int u = 0; u < SORT_ILP; u++) {
+			const int p = c0 + u * TILE_PIX + tid;
+			key[u] = 0ull; st[u] = 0u; len[u] = 0u; r[u] = 0u;
+			if (p < n) {
+				key[u] = sm.keys[p];
+				const int bk = sm.bslot[p];
+				st[u] = sm.start[bk];
+				len[u] = sm.start[bk + 1] - st[u];
+			}
+			maxlen = max(maxlen, len[u]);
+		}
+		for (uint32_t q = 0; q < maxlen; q++) {
+#pragma unroll
+			for (int u = 0; u < SORT_ILP; u++) {
+				// branch-free: read a clamped slot, mask the result (a guarded read compiles to a divergent
+				// branch per u and exposes one shared-memory latency each: ~800 cycles per q in the first version)
+				const unsigned long long other = lds_u64(&sm.keys[min(st[u] + q, (uint32_t)n - 1u)]);
+				r[u] += ((q < len[u]) & (other < key[u])) ? 1u : 0u;
+			}
+		}
+#pragma unroll
+		for (int u = 0; u < SORT_ILP; u++) {
+			const int p = c0 + u * TILE_PIX + tid;
+			if (p < n) emit_sorted(b, range.x + st[u] + r[u], tile, key[u]);
+		}
+	}
+	MOSS_TD(9);
+}
+
+// One block per tile, in tile_order (deepest first).
+__global__ void __launch_bounds__(TILE_PIX)
+tile_sort_kernel(ImageWS im, BinWS b)
+{
+	__shared__ SortSmem ss;
+	if (im.counters[1]) return;   // binning overflow: the host re-runs with a larger buffer
+	if (blockIdx.x >= im.counters[3]) return;                 // only non-empty tiles have work
+	const int tile = (int)im.tile_order[blockIdx.x];
+	const uint2 range = im.ranges[tile];
+	const int n = (int)(range.y - range.x);
+	MOSS_TT(0);
+	if (n > 0) tile_sort(ss, b, range, n, tile);
+	MOSS_TT(1);
+}
+
+} // namespace moss
