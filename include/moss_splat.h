@@ -100,9 +100,12 @@ int moss_rasterize_forward(void* stream, const MossScene* scene, unsigned flags,
 /* Backward.  Replaces CudaRasterizer::Rasterizer::backward (DGR/cuda_rasterizer/rasterizer.h:62-98,
  * rasterizer_impl.cu:345-447) and RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:121-206).
  * The workspaces must be the ones the forward call filled.
- * dL_dmean2D [P,3], dL_dconic [P,4], dL_dopacity [P], dL_dcolor [P,3] are ACCUMULATED into and must be
- * zero on entry (one packed, zero-filled buffer is the intended use); dL_dmean3D [P,3], dL_dcov3D [P,6],
- * dL_dsh [P,M,3] (if shs), dL_dscale [P,3] and dL_drot [P,4] (if scales) are fully written. */
+ * EVERY output is fully written (rows of culled Gaussians with zeros): dL_dmean2D [P,3], dL_dconic [P,4],
+ * dL_dopacity [P], dL_dcolor [P,3], dL_dmean3D [P,3], dL_dcov3D [P,6], dL_dsh [P,M,3] (if shs), dL_dscale [P,3]
+ * and dL_drot [P,4] (if scales).  Nothing needs zero-filling beforehand (the reference zero-fills nine tensors,
+ * DGR/rasterize_points.cu:158-166): the atomically accumulated blend gradients live in a scratch area of the
+ * geometry workspace that the forward clears and the backward leaves cleared, so the backward may be repeated
+ * on the same forward state. */
 int moss_rasterize_backward(void* stream, const MossScene* scene, unsigned flags, const int* radii,
                             const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
                             float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,

@@ -309,7 +309,7 @@ struct BwdSmem {
 	float4 co[BWD_BATCH];
 	float4 feat[BWD_BATCH];
 	uint8_t mask[BWD_BATCH];
-	uint32_t written[BWD_BATCH];                      // bit w: warp w stored a gradient row for this slot
+	uint8_t written[NW][BWD_BATCH];                   // warp w stored a gradient row for this slot (plain byte stores)
 	__align__(8) uint8_t hits[NW][BWD_BATCH + 8];
 	uint32_t warp_last[NW];
 	float grad[NW * BWD_BATCH * NGRAD];               // [warp][slot][component]: each (warp, slot) is written at
@@ -319,9 +319,7 @@ struct BwdSmem {
 template <int NW>
 __global__ void __launch_bounds__(32 * NW)
 blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b,
-	const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas,
-	float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dopacity,
-	float* __restrict__ dL_dcolor)
+	const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas)
 {
 	constexpr int NT = 32 * NW;
 	constexpr int SPLIT = NPATCH / NW;
@@ -399,7 +397,8 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 					hit = patch_hit_mask<NW>(nxy[u], nco[u], tile_px0, tile_py0, sub);
 				}
 				sm.mask[s] = (uint8_t)hit;
-				sm.written[s] = 0u;
+#pragma unroll
+				for (int w = 0; w < NW; w++) sm.written[w][s] = 0;
 			}
 		}
 		__syncthreads();
@@ -505,42 +504,34 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 				if (h + k < nh) {
 					float* row = sm.grad + (warp * BWD_BATCH + jj[k]) * NGRAD;
 					if ((lane & 3) == 0) row[lane >> 2] = s8;
-					if (lane == 1 + 16 * k) { row[8] = so; atomicOr(&sm.written[jj[k]], 1u << warp); }
+					if (lane == 1 + 16 * k) { row[8] = so; sm.written[warp][jj[k]] = 1; }
 				}
 			}
 		}
 		__syncthreads();
 
-		// flush the batch: the rows of the warps that hit a slot are summed in warp order, then ONE global atomic per
-		// (instance, component); a thread takes one slot and one of the component groups {0-4}, {5-8}
+		// flush the batch: the rows of the warps that hit a slot are summed in warp order and added to the Gaussian's
+		// accumulators with VECTOR atomics (red.global.add.v4.f32): a thread takes one slot and either
+		// (colour rgb, opacity) or (mean2D xy, conic xy) + conic w -- 3 atomic instructions per (instance, block)
+		// instead of 9
 		for (int t = threadIdx.x; t < 2 * BWD_BATCH; t += NT) {
 			const int j = t & (BWD_BATCH - 1);
-			const uint32_t wmask = sm.written[j];
-			if (wmask) {
-				const int k0 = (t < BWD_BATCH) ? 0 : 5;
-				float r[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+			const bool second = t >= BWD_BATCH;
+			float r[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+			bool any = false;
 #pragma unroll
-				for (int w = 0; w < NW; w++) {
-					if (wmask & (1u << w)) {
-						const float* row = sm.grad + (w * BWD_BATCH + j) * NGRAD + k0;
-#pragma unroll
-						for (int k = 0; k < 4; k++) r[k] += row[k];
-						if (k0 == 0) r[4] += row[4];
-					}
+			for (int w = 0; w < NW; w++) {
+				if (sm.written[w][j]) {
+					any = true;
+					const float* row = sm.grad + (w * BWD_BATCH + j) * NGRAD;
+					if (!second) { r[0] += row[0]; r[1] += row[1]; r[2] += row[2]; r[3] += row[8]; }
+					else { r[0] += row[3]; r[1] += row[4]; r[2] += row[5]; r[3] += row[6]; r[4] += row[7]; }
 				}
-				const size_t id = sm.id[j];
-				if (k0 == 0) {
-					atomicAdd(dL_dcolor + 3 * id + 0, r[0]);
-					atomicAdd(dL_dcolor + 3 * id + 1, r[1]);
-					atomicAdd(dL_dcolor + 3 * id + 2, r[2]);
-					atomicAdd(dL_dmean2D + 3 * id + 0, r[3]);
-					atomicAdd(dL_dmean2D + 3 * id + 1, r[4]);
-				} else {
-					atomicAdd(dL_dconic + 4 * id + 0, r[0]);
-					atomicAdd(dL_dconic + 4 * id + 1, r[1]);
-					atomicAdd(dL_dconic + 4 * id + 3, r[2]);
-					atomicAdd(dL_dopacity + id, r[3]);
-				}
+			}
+			if (any) {
+				float4* acc = g.grad_acc + 3 * (size_t)sm.id[j];
+				if (!second) atomicAdd(acc, make_float4(r[0], r[1], r[2], r[3]));
+				else { atomicAdd(acc + 1, make_float4(r[0], r[1], r[2], r[3])); atomicAdd(&acc[2].x, r[4]); }
 			}
 		}
 	}

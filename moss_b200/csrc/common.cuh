@@ -50,6 +50,10 @@ struct GeomWS {
 	uint32_t* tiles_touched;  // [P]
 	ushort4*  rect;           // [P]   tile rect (xmin, ymin, xmax, ymax)
 	uint8_t*  clamped;        // [P]   bit c set <=> SH colour channel c was clamped at 0
+	float4*   grad_acc;       // [3P]  blend-backward accumulators, 48 B per Gaussian so they take VECTOR atomics:
+	                          //       [0] = (dL_dcolor rgb, dL_dopacity)  [1] = (dL_dmean2D xy, dL_dconic xy)
+	                          //       [2] = (dL_dconic w, -, -, -).  Zeroed by the forward preprocess, consumed and
+	                          //       re-zeroed by the backward preprocess: no memset launch anywhere.
 };
 struct ImageWS {
 	float*    final_T;        // [N]
@@ -85,6 +89,7 @@ __host__ __device__ inline GeomWS carve_geom(char* base, size_t P, size_t* bytes
 	g.tiles_touched = carve<uint32_t>(p, P);
 	g.rect = carve<ushort4>(p, P);
 	g.clamped = carve<uint8_t>(p, P);
+	g.grad_acc = carve<float4>(p, 3 * P);
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return g;
 }

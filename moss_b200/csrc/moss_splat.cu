@@ -355,18 +355,15 @@ int moss_rasterize_backward(void* stream_, const MossScene* sc, unsigned flags, 
 
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_BWD, stream);
 	switch (blend_split(flags, T)) {
-	case 1: blend_backward_kernel<8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha,
-		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor); break;
-	case 2: blend_backward_kernel<4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha,
-		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor); break;
-	default: blend_backward_kernel<2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha,
-		dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor); break;
+	case 1: blend_backward_kernel<8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha); break;
+	case 2: blend_backward_kernel<4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha); break;
+	default: blend_backward_kernel<2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha); break;
 	} }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_PREPROCESS_BWD, stream);
 	preprocess_backward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
 		P, vp, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
-		dL_dmean2D, dL_dconic, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot); }
+		dL_dmean2D, dL_dconic, dL_dcolor, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	return MOSS_OK;
 }

@@ -193,6 +193,8 @@ preprocess_forward_kernel(int P, ViewParams vp,
 
 	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
 	if (idx >= P) return;
+#pragma unroll
+	for (int k = 0; k < 3; k++) g.grad_acc[3 * (size_t)idx + k] = make_float4(0.f, 0.f, 0.f, 0.f);
 
 	int my_radius = 0;
 	uint32_t touched = 0;

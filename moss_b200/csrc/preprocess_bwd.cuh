@@ -15,8 +15,8 @@ preprocess_backward_kernel(int P, ViewParams vp,
 	const float* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
 	const float* __restrict__ scales, const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
 	GeomWS g,
-	const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconic, const float* __restrict__ dL_dcolor,
-	float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
+	float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dcolor,
+	float* __restrict__ dL_dopacity, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
 	float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
 {
 	__shared__ float v[16], pr[16], s_cam[3];
@@ -28,6 +28,17 @@ preprocess_backward_kernel(int P, ViewParams vp,
 	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
 	if (idx >= P) return;
 	const int M = vp.M, D = vp.D;
+
+	// The blend backward accumulated into g.grad_acc (vector atomics); unpack it into the caller's tensors, which are
+	// therefore fully written here (no zero-fill beforehand), and leave the accumulators zero for the next backward.
+	const float4 acc0 = g.grad_acc[3 * (size_t)idx], acc1 = g.grad_acc[3 * (size_t)idx + 1];
+	const float acc2 = g.grad_acc[3 * (size_t)idx + 2].x;
+#pragma unroll
+	for (int k = 0; k < 3; k++) g.grad_acc[3 * (size_t)idx + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+	dL_dcolor[3 * idx] = acc0.x; dL_dcolor[3 * idx + 1] = acc0.y; dL_dcolor[3 * idx + 2] = acc0.z;
+	dL_dopacity[idx] = acc0.w;
+	dL_dmean2D[3 * idx] = acc1.x; dL_dmean2D[3 * idx + 1] = acc1.y; dL_dmean2D[3 * idx + 2] = 0.f;
+	dL_dconic[4 * idx] = acc1.z; dL_dconic[4 * idx + 1] = acc1.w; dL_dconic[4 * idx + 2] = 0.f; dL_dconic[4 * idx + 3] = acc2;
 
 	if (!(radii[idx] > 0)) {
 #pragma unroll
@@ -48,7 +59,7 @@ preprocess_backward_kernel(int P, ViewParams vp,
 	const float V0 = c3[0], V1 = c3[1], V2 = c3[2], V3 = c3[3], V4 = c3[4], V5 = c3[5];
 
 	// ---- conic -> cov2D -> cov3D and mean (through J) ----------------------------------------------
-	const float dcx = dL_dconic[4 * idx], dcy = dL_dconic[4 * idx + 1], dcz = dL_dconic[4 * idx + 3];
+	const float dcx = acc1.z, dcy = acc1.w, dcz = acc2;
 	float tx = v[0] * mx + v[4] * my + v[8] * mz + v[12];
 	float ty = v[1] * mx + v[5] * my + v[9] * mz + v[13];
 	const float tz = v[2] * mx + v[6] * my + v[10] * mz + v[14];
@@ -118,7 +129,7 @@ preprocess_backward_kernel(int P, ViewParams vp,
 		const float m_w = 1.0f / ((pr[3] * mx + pr[7] * my + pr[11] * mz + pr[15]) + 0.0000001f);
 		const float mul1 = (pr[0] * mx + pr[4] * my + pr[8] * mz + pr[12]) * m_w * m_w;
 		const float mul2 = (pr[1] * mx + pr[5] * my + pr[9] * mz + pr[13]) * m_w * m_w;
-		const float d2x = dL_dmean2D[3 * idx], d2y = dL_dmean2D[3 * idx + 1];
+		const float d2x = acc1.x, d2y = acc1.y;
 		gmx += (pr[0] * m_w - pr[3] * mul1) * d2x + (pr[1] * m_w - pr[3] * mul2) * d2y;
 		gmy += (pr[4] * m_w - pr[7] * mul1) * d2x + (pr[5] * m_w - pr[7] * mul2) * d2y;
 		gmz += (pr[8] * m_w - pr[11] * mul1) * d2x + (pr[9] * m_w - pr[11] * mul2) * d2y;
@@ -134,7 +145,7 @@ preprocess_backward_kernel(int P, ViewParams vp,
 		const uint8_t cl = g.clamped[idx];
 		float dRGB[3];
 #pragma unroll
-		for (int ch = 0; ch < 3; ch++) dRGB[ch] = ((cl >> ch) & 1) ? 0.f : dL_dcolor[3 * idx + ch];
+		for (int ch = 0; ch < 3; ch++) dRGB[ch] = ((cl >> ch) & 1) ? 0.f : (ch == 0 ? acc0.x : (ch == 1 ? acc0.y : acc0.z));
 
 		float basis[16];
 #pragma unroll

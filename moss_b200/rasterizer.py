@@ -177,8 +177,10 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
         has_sh = sc.shs is not None
         has_sr = sc.scales is not None
         lay, param_numel, zero_from, total = grad_layout(P, M, has_sh, has_sr)
+        # every row of every output is written by the backward preprocess kernel: nothing is zero-filled here
+        # (the reference fills 9 tensors, DGR/rasterize_points.cu:158-166); the atomically accumulated blend
+        # gradients live in a self-cleaning scratch inside the geometry workspace
         buf = out if out is not None else torch.empty((total,), dtype=torch.float32, device=dev)
-        buf[zero_from:].zero_()        # K7 fully writes the rest (no 9-tensor zero fill as DGR/rasterize_points.cu:158-166)
 
         def v(name, *shape):
             o, n = lay[name]
