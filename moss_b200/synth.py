@@ -234,3 +234,28 @@ def settings_kwargs(cam: Camera, bg, sh_degree=3, scale_modifier=1.0, device=Non
                 tanfovy=cam.tanfovy, bg=to(bg), scale_modifier=scale_modifier, viewmatrix=to(cam.world_view_transform),
                 projmatrix=to(cam.full_proj_transform), sh_degree=sh_degree, campos=to(cam.camera_center),
                 prefiltered=False, debug=False)
+
+
+class Frame(NamedTuple):
+    params: dict       # target pose: poses [1,72], shapes [1,10], R [3,3], Th [1,3]  (scene/dataset_readers.py:420-426)
+    big_params: dict   # canonical "big pose" (scene/dataset_readers.py:583-590)
+
+
+def frame_params(seed=0) -> Frame:
+    """Random SMPL frame parameters shaped like the reference's `smpl_param` / `big_pose_smpl_param` dicts."""
+    rng = np.random.default_rng(SEED + 17 + seed)
+    poses = 0.35 * rng.standard_normal((1, 72))
+    poses[0, :3] = 0.2 * rng.standard_normal(3)
+    rh = 0.4 * rng.standard_normal(3)
+    ang = np.linalg.norm(rh)
+    k = rh / ang
+    K = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
+    Rg = np.eye(3) + math.sin(ang) * K + (1 - math.cos(ang)) * (K @ K)      # cv2.Rodrigues(Rh)
+    f = lambda a: torch.from_numpy(np.ascontiguousarray(a)).float()  # noqa: E731
+    params = dict(poses=f(poses), shapes=f(0.5 * rng.standard_normal((1, 10))), R=f(Rg),
+                  Th=f(0.3 * rng.standard_normal((1, 3))))
+    big = np.zeros((1, 72))
+    big[0, 5] = 45 / 180 * math.pi; big[0, 8] = -45 / 180 * math.pi
+    big[0, 23] = -30 / 180 * math.pi; big[0, 26] = 30 / 180 * math.pi
+    big_params = dict(poses=f(big), shapes=torch.zeros(1, 10), R=torch.eye(3), Th=torch.zeros(1, 3))
+    return Frame(params, big_params)

@@ -1,0 +1,47 @@
+"""CPU: the LBS / covariance oracle restatement reproduces what the REAL reference functions computed
+(tests/golden/lbs_*.npz, made by tests/golden/make_lbs_golden.py in the build container)."""
+import pytest
+import torch
+
+from oracle import lbs_oracle as L
+from tests.lbs_cases import LBS_CASES, load_case
+
+TOL = 2e-6      # fp32; both sides are the same torch ops up to matmul association
+
+
+def _close(a, b, tol=TOL):
+    scale = max(float(b.abs().max()), 1.0)
+    assert float((a - b).abs().max()) <= tol * scale, float((a - b).abs().max()) / scale
+
+
+@pytest.mark.parametrize("name", LBS_CASES)
+def test_forward_matches_reference(name):
+    d, ft, body = load_case(name)
+    vid = L.nearest_vertex(body.verts, d["xyz"])
+    assert torch.equal(vid.int(), d["vert_ids"])
+    sk, cov = L.skin_and_covariance(d["xyz"], vid, body.weights, ft, d["scaling"], d["rotation"], float(d["mod"]),
+                                    d.get("lbs_delta"), return_transl=True)
+    _close(sk.bweights, d["bweights"])
+    _close(sk.smpl_pts, d["smpl_pts"])
+    _close(sk.world_pts, d["world"])
+    _close(sk.transforms, d["transforms"])
+    _close(sk.translation, d["translation"])
+    _close(cov, d["cov3D"], 1e-5)
+
+
+@pytest.mark.parametrize("name", LBS_CASES)
+def test_backward_matches_reference(name):
+    d, ft, body = load_case(name)
+    xyz = d["xyz"].clone().requires_grad_(True)
+    sc = d["scaling"].clone().requires_grad_(True)
+    rot = d["rotation"].clone().requires_grad_(True)
+    leaves = [xyz, sc, rot]
+    delta = None
+    if "lbs_delta" in d:
+        delta = d["lbs_delta"].clone().requires_grad_(True)
+        leaves.append(delta)
+    sk, cov = L.skin_and_covariance(xyz, d["vert_ids"].long(), body.weights, ft, sc, rot, float(d["mod"]), delta)
+    g = torch.autograd.grad([sk.world_pts, cov], leaves, [d["g_world"], d["g_cov"]])
+    for got, key in zip(g, ["d_xyz", "d_scaling", "d_rotation", "d_lbs_delta"]):
+        rel = float((got - d[key]).norm() / d[key].norm())
+        assert rel < 1e-4, (key, rel)
