@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MOSS_ABI_VERSION 2
+#define MOSS_ABI_VERSION 3
 
 /* status codes */
 #define MOSS_OK                  0
@@ -116,6 +116,41 @@ int moss_rasterize_backward(void* stream, const MossScene* scene, unsigned flags
 int moss_mark_visible(void* stream, int P, const float* means3D, const float* viewmatrix,
                       const float* projmatrix, uint8_t* present);
 
+/* Fused skinning + covariance front end (optional entry points).  Replaces, per render()
+ * call, the per-Gaussian half of GaussianModel.coarse_deform_c2source (scene/gaussian_model.py:829-846, 857-868,
+ * 889-921) and GaussianModel.get_covariance(scaling_modifier, transforms) (scene/gaussian_model.py:37-44,168-169;
+ * utils/general_utils.py:62-118) as gaussian_renderer/__init__.py:57-85 calls them: ONE kernel instead of ~60 torch
+ * launches.  The per-frame, Gaussian-independent tables (joint transforms A, blend-shape offsets) are inputs. */
+typedef struct MossSkin {
+    int P;                      /* Gaussians */
+    int V;                      /* rows of the per-vertex tables (6890 for SMPL) */
+    const float* xyz;           /* [P,3] canonical centres (pc.get_xyz) */
+    const int*   vert_ids;      /* [P] nearest SMPL vertex, 0 <= id < V (the KNN result, scene/gaussian_model.py:827) */
+    const float* weights;       /* [V,24] SMPL_NEUTRAL['weights'], 16-byte aligned */
+    const float* lbs_delta;     /* [P,24] or NULL: bw = softmax(log(w + 1e-9) + delta) (:831-833), 16-byte aligned */
+    const float* A_big;         /* [24,16] joint transforms of the big pose, row-major 4x4 (:838) */
+    const float* A_tgt;         /* [24,16] joint transforms of the target pose (:895) */
+    const float* poseoff_big;   /* [V,3] or NULL (:849-857) */
+    const float* shapeoff;      /* [V,3] or NULL (:862-866) */
+    const float* poseoff_tgt;   /* [V,3] or NULL (:872-889) */
+    const float* Rg;            /* [9] params['R'] */
+    const float* Th;            /* [3] params['Th'] */
+    const float* scaling;       /* [P,3] pc.get_scaling, or NULL: no covariance */
+    const float* rotation;      /* [P,4] pc._rotation (raw; normalised inside like build_rotation) or NULL */
+    float scale_modifier;
+} MossSkin;
+/* means3D [P,3] is always written; cov3D [P,6] (needs scaling+rotation), transforms [P,9], bweights [P,24],
+ * translation [P,3] (return_transl) are optional (NULL to skip). */
+int moss_skin_forward(void* stream, const MossSkin* skin, float* means3D, float* cov3D, float* transforms,
+                      float* bweights, float* translation);
+/* Backward (the reference's is torch autograd through the python ops).  g_means3D [P,3], g_cov3D [P,6] or NULL.
+ * Fully written: d_xyz [P,3], d_scaling [P,3], d_rotation [P,4] (NULL allowed without scaling), d_lbs_delta [P,24]
+ * (NULL allowed).  Optional accumulators, cleared by this call: d_A_tgt [24,16], d_poseoff_tgt [V,3]. */
+int moss_skin_backward(void* stream, const MossSkin* skin, const float* g_means3D, const float* g_cov3D,
+                       float* d_xyz, float* d_scaling, float* d_rotation, float* d_lbs_delta,
+                       float* d_A_tgt, float* d_poseoff_tgt);
+size_t moss_sizeof_skin(void);
+
 /* Internal-state export for parity tests (the reference needs a C++ shim over fromChunk for this,
  * DGR/cuda_rasterizer/rasterizer_impl.cu:155-194).  Copies one state array into `dst` (device) on
  * `stream`; returns the byte count or a negative MOSS_ERR_*. */
@@ -148,7 +183,9 @@ long long moss_export_state(void* stream, const MossScene* scene, int which, voi
 #define MOSS_STAGE_PREPROCESS_BWD  5
 #define MOSS_STAGE_OTHER           6
 #define MOSS_STAGE_TILE_SORT       7
-#define MOSS_STAGE_COUNT           8
+#define MOSS_STAGE_SKIN            8
+#define MOSS_STAGE_SKIN_BWD        9
+#define MOSS_STAGE_COUNT           10
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

@@ -34,8 +34,9 @@ SYMBOLS = [
     "moss_rasterize_backward", "moss_mark_visible", "moss_export_state", "moss_abi_version",
     "moss_error_string", "moss_last_cuda_error", "moss_sizeof_scene", "moss_kernel_launches",
     "moss_profile_enable", "moss_profile_read", "moss_stage_name",
+    "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin",
 ]
-STAGE_COUNT = 8
+STAGE_COUNT = 10
 
 
 class MossScene(C.Structure):
@@ -50,6 +51,16 @@ class MossScene(C.Structure):
         ("geom_ws", C.c_void_p), ("geom_bytes", C.c_size_t),
         ("image_ws", C.c_void_p), ("image_bytes", C.c_size_t),
         ("binning_ws", C.c_void_p), ("binning_bytes", C.c_size_t),
+    ]
+
+
+class MossSkin(C.Structure):
+    _fields_ = [
+        ("P", C.c_int), ("V", C.c_int),
+        ("xyz", C.c_void_p), ("vert_ids", C.c_void_p), ("weights", C.c_void_p), ("lbs_delta", C.c_void_p),
+        ("A_big", C.c_void_p), ("A_tgt", C.c_void_p), ("poseoff_big", C.c_void_p), ("shapeoff", C.c_void_p),
+        ("poseoff_tgt", C.c_void_p), ("Rg", C.c_void_p), ("Th", C.c_void_p), ("scaling", C.c_void_p),
+        ("rotation", C.c_void_p), ("scale_modifier", C.c_float),
     ]
 
 
@@ -100,6 +111,13 @@ def load():
     lib.moss_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
     lib.moss_stage_name.restype = C.c_char_p
     lib.moss_stage_name.argtypes = [C.c_int]
+    lib.moss_sizeof_skin.restype = C.c_size_t
+    lib.moss_skin_forward.restype = C.c_int
+    lib.moss_skin_forward.argtypes = [vp, C.POINTER(MossSkin)] + [vp] * 5
+    lib.moss_skin_backward.restype = C.c_int
+    lib.moss_skin_backward.argtypes = [vp, C.POINTER(MossSkin)] + [vp] * 8
+    if lib.moss_sizeof_skin() != C.sizeof(MossSkin):
+        raise RuntimeError("moss_b200: MossSkin layout mismatch between _abi.py and the library; rebuild")
     if lib.moss_sizeof_scene() != C.sizeof(MossScene):
         raise RuntimeError("moss_b200: MossScene layout mismatch between _abi.py and the library; rebuild")
     _lib = lib

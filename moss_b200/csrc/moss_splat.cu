@@ -18,6 +18,7 @@
 #include "preprocess_bwd.cuh"
 #include "binning.cuh"
 #include "blend.cuh"
+#include "skin.cuh"
 
 using namespace moss;
 
@@ -189,7 +190,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -453,6 +454,60 @@ long long moss_export_state(void* stream_, const MossScene* sc, int which, void*
 	if (n > max_bytes) return -MOSS_ERR_WORKSPACE_TOO_SMALL;
 	if (n > 0 && cudaMemcpyAsync(dst, src, (size_t)n, cudaMemcpyDeviceToDevice, stream) != cudaSuccess) return -MOSS_ERR_CUDA;
 	return n;
+}
+
+// ---- fused skinning + covariance front end ---------------------------------------------------------------
+static inline bool skin_valid(const MossSkin* k)
+{
+	if (!k || k->P < 0 || k->V <= 0) return false;
+	if (k->P == 0) return true;
+	if (!k->xyz || !k->vert_ids || !k->weights || !k->A_big || !k->A_tgt || !k->Rg || !k->Th) return false;
+	if ((k->scaling != nullptr) != (k->rotation != nullptr)) return false;
+	if (((uintptr_t)k->weights & 15) || ((uintptr_t)k->lbs_delta & 15)) return false;
+	return true;
+}
+static inline SkinArgs make_skin(const MossSkin* k)
+{
+	SkinArgs a;
+	a.P = k->P; a.xyz = k->xyz; a.vert_ids = k->vert_ids; a.weights = k->weights; a.lbs_delta = k->lbs_delta;
+	a.A_big = k->A_big; a.A_tgt = k->A_tgt; a.poseoff_big = k->poseoff_big; a.shapeoff = k->shapeoff;
+	a.poseoff_tgt = k->poseoff_tgt; a.Rg = k->Rg; a.Th = k->Th; a.scaling = k->scaling; a.rotation = k->rotation;
+	a.scale_modifier = k->scale_modifier;
+	return a;
+}
+size_t moss_sizeof_skin(void) { return sizeof(MossSkin); }
+
+int moss_skin_forward(void* stream_, const MossSkin* k, float* means3D, float* cov3D, float* transforms,
+	float* bweights, float* translation)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!skin_valid(k)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (k->P == 0) return MOSS_OK;
+	if (!means3D || (cov3D && !k->scaling) || ((uintptr_t)bweights & 15)) return MOSS_ERR_INVALID_ARGUMENT;
+	{ MOSS_STAGE(MOSS_STAGE_SKIN, stream);
+		skin_forward_kernel<<<(k->P + SKIN_THREADS - 1) / SKIN_THREADS, SKIN_THREADS, 0, stream>>>(
+			make_skin(k), means3D, cov3D, transforms, bweights, translation); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+int moss_skin_backward(void* stream_, const MossSkin* k, const float* g_means3D, const float* g_cov3D,
+	float* d_xyz, float* d_scaling, float* d_rotation, float* d_lbs_delta, float* d_A_tgt, float* d_poseoff_tgt)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!skin_valid(k)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (d_A_tgt) MOSS_CUDA_TRY(cudaMemsetAsync(d_A_tgt, 0, sizeof(float) * NJ * 16, stream));
+	if (d_poseoff_tgt) MOSS_CUDA_TRY(cudaMemsetAsync(d_poseoff_tgt, 0, sizeof(float) * 3 * (size_t)k->V, stream));
+	if (k->P == 0) return MOSS_OK;
+	if (!g_means3D || !d_xyz) return MOSS_ERR_INVALID_ARGUMENT;
+	if (k->scaling && (!d_scaling || !d_rotation)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (d_lbs_delta && !k->lbs_delta) return MOSS_ERR_INVALID_ARGUMENT;
+	if (((uintptr_t)d_rotation & 15) || ((uintptr_t)d_lbs_delta & 15)) return MOSS_ERR_INVALID_ARGUMENT;
+	{ MOSS_STAGE(MOSS_STAGE_SKIN_BWD, stream);
+		skin_backward_kernel<<<(k->P + SKIN_THREADS - 1) / SKIN_THREADS, SKIN_THREADS, 0, stream>>>(
+			make_skin(k), g_means3D, g_cov3D, d_xyz, d_scaling, d_rotation, d_lbs_delta, d_A_tgt, d_poseoff_tgt); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
 }
 
 #ifdef MOSS_TILE_TIMING

@@ -1,0 +1,255 @@
+"""Host-side mirror of MOSS's skinning + covariance front end, over the fused sm_100a kernel.
+
+What render() does between ``pc.get_xyz`` and the rasterizer call (gaussian_renderer/__init__.py:57-85):
+
+    _, means3D, bweights, transforms, translation = pc.coarse_deform_c2source(xyz[None], smpl_param,
+                                                        big_pose_smpl_param, big_pose_world_vertex[None], ...)
+    cov3D_precomp = pc.get_covariance(scaling_modifier, transforms.squeeze())
+
+becomes
+
+    ft = frame_tables(smpl, smpl_param, big_pose_smpl_param, correct_Rs)          # per frame, Gaussian-independent
+    means3D, cov3D_precomp, transforms, bweights, translation = skin_and_covariance(
+        xyz, vert_ids, smpl.weights, ft, pc.get_scaling, pc._rotation, scaling_modifier, lbs_delta)
+
+``skin_and_covariance`` is ONE kernel forward and ONE backward through the C ABI (``moss_skin_forward`` /
+``moss_skin_backward``, include/moss_splat.h); there is no torch fallback.  ``frame_tables`` is the 24-joint
+kinematic chain and the blend-shape offset tables (scene/gaussian_model.py:838-892, 965-1064) -- O(24) work per
+frame, kept as differentiable torch ops on the device (the next row to go native);
+its big-pose half is constant over a run and is cached by ``FrameCache``.
+"""
+import ctypes as C
+from typing import NamedTuple, Optional
+
+import torch
+
+from . import _abi
+
+
+class Smpl(NamedTuple):
+    """The entries of GaussianModel.SMPL_NEUTRAL the path reads (scene/gaussian_model.py:88-104), on the device."""
+    v_template: torch.Tensor   # [V,3]
+    shapedirs: torch.Tensor    # [V,3,10]
+    posedirs: torch.Tensor     # [V,3,207]
+    J_regressor: torch.Tensor  # [24,V]
+    weights: torch.Tensor      # [V,24]
+    parents: torch.Tensor      # [24] int64 (kintree_table[0])
+
+
+class FrameTables(NamedTuple):
+    A_big: torch.Tensor        # [24,4,4]
+    A_tgt: torch.Tensor        # [24,4,4]
+    poseoff_big: torch.Tensor  # [V,3]
+    shapeoff: torch.Tensor     # [V,3]
+    poseoff_tgt: torch.Tensor  # [V,3]
+    R: torch.Tensor            # [3,3]
+    Th: torch.Tensor           # [3]
+
+
+def batch_rodrigues(rot_vecs):
+    """scene/gaussian_model.py:1033-1064 ([N,3] -> [N,3,3]; the +1e-8 sits inside the norm as in the reference)."""
+    n = rot_vecs.shape[0]
+    angle = torch.norm(rot_vecs + 1e-8, dim=1, keepdim=True)
+    rot_dir = rot_vecs / angle
+    cos = torch.cos(angle)[:, None]
+    sin = torch.sin(angle)[:, None]
+    rx, ry, rz = torch.split(rot_dir, 1, dim=1)
+    zeros = torch.zeros((n, 1), dtype=rot_vecs.dtype, device=rot_vecs.device)
+    K = torch.cat([zeros, -rz, ry, rz, zeros, -rx, -ry, rx, zeros], dim=1).view(n, 3, 3)
+    ident = torch.eye(3, dtype=rot_vecs.dtype, device=rot_vecs.device)[None]
+    return ident + sin * K + (1 - cos) * torch.bmm(K, K)
+
+
+def _rigid_chain(rot_mats, joints, parents):
+    """scene/gaussian_model.py:965-995 for one frame: [24,3,3], [24,3] -> A [24,4,4]."""
+    nj = joints.shape[0]
+    plist = [int(p) for p in parents.tolist()]
+    rel = torch.cat([joints[:1], joints[1:] - joints[plist[1:]]], dim=0)
+    tm = torch.cat([rot_mats, rel[..., None]], dim=-1)
+    pad = torch.zeros((nj, 1, 4), dtype=rot_mats.dtype, device=rot_mats.device)
+    pad[..., 3] = 1
+    tm = torch.cat([tm, pad], dim=-2)
+    chain = [tm[0]]
+    for i in range(1, nj):
+        chain.append(chain[plist[i]] @ tm[i])
+    tr = torch.stack(chain, dim=0)
+    jh = torch.cat([joints, torch.zeros((nj, 1), dtype=joints.dtype, device=joints.device)], dim=-1)
+    relj = torch.sum(tr * jh[:, None], dim=2)
+    return torch.cat([tr[..., :3], (tr[..., 3] - relj)[..., None]], dim=-1)
+
+
+def _joint_transforms(smpl: Smpl, shapes, rot_mats):
+    """get_transform_params_torch (scene/gaussian_model.py:998-1031) for one frame."""
+    v_shaped = smpl.v_template + torch.sum(smpl.shapedirs[..., :shapes.shape[-1]] * shapes.reshape(1, 1, -1), dim=-1)
+    joints = smpl.J_regressor @ v_shaped
+    return _rigid_chain(rot_mats, joints, smpl.parents)
+
+
+def _pose_offsets(smpl: Smpl, rot_mats):
+    """scene/gaussian_model.py:849-856 / :872-888: [24,3,3] -> [V,3]."""
+    nv = smpl.posedirs.shape[0]
+    ident = torch.eye(3, dtype=rot_mats.dtype, device=rot_mats.device)
+    pf = (rot_mats[1:] - ident).reshape(1, -1)
+    return (pf @ smpl.posedirs.reshape(nv * 3, -1).t()).view(nv, 3)
+
+
+class FrameCache:
+    """The big-pose half of the tables never changes during a run (scene/dataset_readers.py:583-590)."""
+
+    def __init__(self):
+        self.key = None
+        self.val = None
+
+    def get(self, smpl, t_params):
+        key = (t_params["poses"].data_ptr(), t_params["shapes"].data_ptr(), smpl.v_template.data_ptr())
+        if self.key != key:
+            with torch.no_grad():
+                rm = batch_rodrigues(t_params["poses"].reshape(-1, 3))
+                self.val = (_joint_transforms(smpl, t_params["shapes"], rm).contiguous(), _pose_offsets(smpl, rm).contiguous())
+            self.key = key
+        return self.val
+
+
+def frame_tables(smpl: Smpl, params, t_params, correct_Rs=None, cache: Optional[FrameCache] = None) -> FrameTables:
+    """Per-frame half of coarse_deform_c2source (scene/gaussian_model.py:838-892).  ``params`` / ``t_params`` are the
+    reference's ``smpl_param`` / ``big_pose_smpl_param`` dicts (poses [1,72], shapes [1,10], R [3,3], Th [1,3])."""
+    if cache is not None:
+        A_big, po_big = cache.get(smpl, t_params)
+    else:
+        rm_big = batch_rodrigues(t_params["poses"].reshape(-1, 3))
+        A_big, po_big = _joint_transforms(smpl, t_params["shapes"], rm_big), _pose_offsets(smpl, rm_big)
+    nsh = params["shapes"].shape[-1]
+    so = (smpl.shapedirs[..., :nsh] @ params["shapes"].reshape(-1, 1)).squeeze(-1)
+    rm = batch_rodrigues(params["poses"].reshape(-1, 3))
+    if correct_Rs is not None:
+        rm = torch.cat([rm[0:1], torch.matmul(rm[1:], correct_Rs.reshape(-1, 3, 3))], dim=0)
+    po = _pose_offsets(smpl, rm)
+    A = _joint_transforms(smpl, params["shapes"], rm)
+    return FrameTables(A_big, A, po_big, so, po, params["R"].reshape(3, 3), params["Th"].reshape(-1))
+
+
+def _dev_f32(t, name):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (moss_b200 has no CPU path)")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32")
+    return t.contiguous()
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def _fill_skin(xyz, vert_ids, weights, lbs_delta, A_big, A_tgt, po_big, so, po_tgt, R, Th, scaling, rotation, mod):
+    k = _abi.MossSkin()
+    k.P, k.V = xyz.shape[0], weights.shape[0]
+    k.xyz, k.vert_ids, k.weights, k.lbs_delta = _p(xyz), _p(vert_ids), _p(weights), _p(lbs_delta)
+    k.A_big, k.A_tgt = _p(A_big), _p(A_tgt)
+    k.poseoff_big, k.shapeoff, k.poseoff_tgt = _p(po_big), _p(so), _p(po_tgt)
+    k.Rg, k.Th, k.scaling, k.rotation = _p(R), _p(Th), _p(scaling), _p(rotation)
+    k.scale_modifier = float(mod)
+    return k
+
+
+class _SkinCovariance(torch.autograd.Function):
+    """inputs: xyz, scaling, rotation, lbs_delta, A_tgt, poseoff_tgt are differentiable; the rest are constants."""
+
+    @staticmethod
+    def forward(ctx, xyz, scaling, rotation, lbs_delta, A_tgt, poseoff_tgt, vert_ids, weights, A_big, poseoff_big,
+                shapeoff, R, Th, scaling_modifier, return_transl):
+        lib = _abi.load()
+        xyz = _dev_f32(xyz, "xyz")
+        if xyz.ndim != 2 or xyz.shape[1] != 3:
+            raise RuntimeError("xyz must have dimensions (num_points, 3)")
+        dev = xyz.device
+        P = xyz.shape[0]
+        scaling, rotation = _dev_f32(scaling, "scaling"), _dev_f32(rotation, "rotation")
+        lbs_delta = _dev_f32(lbs_delta, "lbs_delta")
+        if lbs_delta is not None:
+            lbs_delta = lbs_delta.reshape(P, 24)
+        A_tgt, A_big = _dev_f32(A_tgt, "A_tgt"), _dev_f32(A_big, "A_big")
+        poseoff_tgt, poseoff_big, shapeoff = (_dev_f32(poseoff_tgt, "poseoff_tgt"), _dev_f32(poseoff_big, "poseoff_big"),
+                                              _dev_f32(shapeoff, "shapeoff"))
+        weights, R, Th = _dev_f32(weights, "weights"), _dev_f32(R, "R"), _dev_f32(Th, "Th")
+        if vert_ids.dtype != torch.int32:
+            vert_ids = vert_ids.to(torch.int32)
+        vert_ids = vert_ids.reshape(-1).contiguous()
+        if not vert_ids.is_cuda or vert_ids.shape[0] != P:
+            raise RuntimeError("vert_ids must be a CUDA tensor with one entry per Gaussian")
+        with torch.cuda.device(dev):
+            means3D = torch.empty((P, 3), dtype=torch.float32, device=dev)
+            has_cov = scaling is not None and rotation is not None
+            cov3D = torch.empty((P, 6), dtype=torch.float32, device=dev) if has_cov else None
+            transforms = torch.empty((P, 3, 3), dtype=torch.float32, device=dev)
+            bweights = torch.empty((P, 24), dtype=torch.float32, device=dev)
+            translation = torch.empty((P, 3), dtype=torch.float32, device=dev) if return_transl else None
+            k = _fill_skin(xyz, vert_ids, weights, lbs_delta, A_big, A_tgt, poseoff_big, shapeoff, poseoff_tgt, R, Th,
+                           scaling, rotation, scaling_modifier)
+            st = lib.moss_skin_forward(torch.cuda.current_stream(dev).cuda_stream, C.byref(k), _p(means3D), _p(cov3D),
+                                       _p(transforms), _p(bweights), _p(translation))
+        _abi.check(st, "moss_skin_forward")
+        ctx.mod = float(scaling_modifier)
+        ctx.has = (scaling is not None, lbs_delta is not None, poseoff_big is not None, shapeoff is not None,
+                   poseoff_tgt is not None)
+        saved = [xyz, vert_ids, weights, A_big, A_tgt, R, Th]
+        for t in (scaling, rotation, lbs_delta, poseoff_big, shapeoff, poseoff_tgt):
+            if t is not None:
+                saved.append(t)
+        ctx.save_for_backward(*saved)
+        outs = (means3D, cov3D if has_cov else torch.empty(0, device=dev), transforms, bweights,
+                translation if return_transl else torch.empty(0, device=dev))
+        ctx.mark_non_differentiable(outs[2], outs[3], outs[4])
+        return outs
+
+    @staticmethod
+    def backward(ctx, g_means3D, g_cov3D, _gt, _gb, _gtr):
+        lib = _abi.load()
+        sv = list(ctx.saved_tensors)
+        xyz, vert_ids, weights, A_big, A_tgt, R, Th = sv[:7]
+        rest = sv[7:]
+        has_cov, has_delta, has_pb, has_so, has_pt = ctx.has
+        scaling = rotation = lbs_delta = po_big = so = po_tgt = None
+        if has_cov:
+            scaling, rotation = rest[0], rest[1]; rest = rest[2:]
+        if has_delta:
+            lbs_delta = rest[0]; rest = rest[1:]
+        if has_pb:
+            po_big = rest[0]; rest = rest[1:]
+        if has_so:
+            so = rest[0]; rest = rest[1:]
+        if has_pt:
+            po_tgt = rest[0]; rest = rest[1:]
+        dev = xyz.device
+        P, V = xyz.shape[0], weights.shape[0]
+        need = ctx.needs_input_grad        # xyz, scaling, rotation, lbs_delta, A_tgt, poseoff_tgt
+        with torch.cuda.device(dev):
+            g_means3D = (torch.zeros((P, 3), dtype=torch.float32, device=dev) if g_means3D is None
+                         else _dev_f32(g_means3D, "grad means3D"))
+            g_cov3D = _dev_f32(g_cov3D, "grad cov3D") if (has_cov and g_cov3D is not None and g_cov3D.numel()) else None
+            d_xyz = torch.empty((P, 3), dtype=torch.float32, device=dev)
+            d_scaling = torch.empty((P, 3), dtype=torch.float32, device=dev) if has_cov else None
+            d_rotation = torch.empty((P, 4), dtype=torch.float32, device=dev) if has_cov else None
+            d_delta = torch.empty((P, 24), dtype=torch.float32, device=dev) if (has_delta and need[3]) else None
+            d_A = torch.empty((24, 4, 4), dtype=torch.float32, device=dev) if need[4] else None
+            d_po = torch.empty((V, 3), dtype=torch.float32, device=dev) if (has_pt and need[5]) else None
+            k = _fill_skin(xyz, vert_ids, weights, lbs_delta, A_big, A_tgt, po_big, so, po_tgt, R, Th, scaling, rotation,
+                           ctx.mod)
+            st = lib.moss_skin_backward(torch.cuda.current_stream(dev).cuda_stream, C.byref(k), _p(g_means3D), _p(g_cov3D),
+                                        _p(d_xyz), _p(d_scaling), _p(d_rotation), _p(d_delta), _p(d_A), _p(d_po))
+        _abi.check(st, "moss_skin_backward")
+        return (d_xyz, d_scaling, d_rotation, d_delta, d_A, d_po) + (None,) * 9
+
+
+def skin_and_covariance(xyz, vert_ids, weights, ft: FrameTables, scaling=None, rotation=None, scaling_modifier=1.0,
+                        lbs_delta=None, return_transl=False):
+    """-> (means3D [P,3], cov3D_precomp [P,6] or None, transforms [P,3,3], bweights [P,24], translation [P,3] or None).
+
+    Same values as ``coarse_deform_c2source(...)[1:]`` + ``get_covariance(scaling_modifier, transforms)``
+    (scene/gaussian_model.py:820-923, 37-44).  ``vert_ids`` is the nearest-vertex lookup the reference recomputes with
+    knn_cuda every call (:827); ``lbs_delta`` is its ``lbs_weights`` argument."""
+    m, c, tr, bw, tl = _SkinCovariance.apply(xyz, scaling, rotation, lbs_delta, ft.A_tgt, ft.poseoff_tgt, vert_ids,
+                                             weights, ft.A_big, ft.poseoff_big, ft.shapeoff, ft.R, ft.Th,
+                                             scaling_modifier, return_transl)
+    return m, (c if c.numel() else None), tr, bw, (tl if return_transl else None)

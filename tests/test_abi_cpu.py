@@ -28,7 +28,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_versions_and_strings(lib):
-    assert lib.moss_abi_version() == 2
+    assert lib.moss_abi_version() == 3
     assert lib.moss_error_string(0) == b"ok"
     assert b"binning" in lib.moss_error_string(_abi.MOSS_ERR_BINNING_OVERFLOW)
 
@@ -56,6 +56,37 @@ def test_invalid_arguments_are_rejected_without_a_gpu(lib):
 def test_scene_struct_layout_matches_header(lib):
     # ctypes mirror must have the same size as the C struct (checked through the library)
     assert lib.moss_sizeof_scene() == C.sizeof(_abi.MossScene)
+    assert lib.moss_sizeof_skin() == C.sizeof(_abi.MossSkin)
+
+
+def test_skin_entry_points_validate_without_a_gpu(lib):
+    k = _abi.MossSkin()
+    k.P, k.V = 4, 0
+    assert lib.moss_skin_forward(None, C.byref(k), None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    assert lib.moss_skin_backward(None, C.byref(k), *([None] * 8)) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    k.P, k.V = 0, 6890       # empty input: nothing to launch, no accumulators requested
+    assert lib.moss_skin_forward(None, C.byref(k), None, None, None, None, None) == _abi.MOSS_OK
+
+
+def test_skinning_host_tables_match_oracle_and_refuse_cpu_compute():
+    """frame_tables (host logic, torch) == the oracle's restatement of the reference; the per-Gaussian kernel has no
+    CPU path."""
+    from moss_b200 import skinning as K, synth
+    from oracle import lbs_oracle as L
+    from tests.lbs_cases import oracle_smpl
+    body = synth.body()
+    V = body.verts.shape[0]
+    smpl = K.Smpl(body.verts, body.shapedirs, body.posedirs.t().reshape(V, 3, 207).contiguous(), body.J_regressor,
+                  body.weights, body.parents)
+    fr = synth.frame_params(3)
+    cr = L.batch_rodrigues(0.05 * torch.randn(23, 3, generator=torch.Generator().manual_seed(1))).reshape(1, 23, 3, 3)
+    a = K.frame_tables(smpl, fr.params, fr.big_params, cr, cache=K.FrameCache())
+    b = L.frame_tables(oracle_smpl(body), fr.params, fr.big_params, cr)
+    for x, y in zip(a, b):
+        assert float((x - y.reshape(x.shape)).abs().max()) <= 2e-6 * max(1.0, float(y.abs().max()))
+    g = synth.gaussians(64, body)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        K.skin_and_covariance(g.xyz, g.vert_ids, body.weights, a, g.scales, g.rotations)
 
 
 def test_api_validation_and_no_cpu_fallback():
