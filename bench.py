@@ -115,7 +115,7 @@ def algorithmic_bytes(P, V, R, N, T, M, D, has_sr):
 
 def run_ours(args, rank, world, dev):
     import moss_b200 as M
-    from moss_b200 import _abi, synth
+    from moss_b200 import _abi, parallel, synth
     lib = _abi.load()
     d, cams = build_inputs(args.workload, rank, world)
     W, H = cams[0].image_width, cams[0].image_height
@@ -138,7 +138,7 @@ def run_ours(args, rank, world, dev):
                                                        devt["scales"], devt["rotations"], devt["cov3D_precomp"], rs)
         M.backward_raw(st, radii, gc, gd, ga)
         if world > 1:
-            dist.all_reduce(st.grad_buf[:st.param_grad_numel])
+            parallel.allreduce_param_grads(st.grad_buf, st.param_grad_numel)
         state["st"], state["radii"] = st, radii
         return st
 
