@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MOSS_ABI_VERSION 3
+#define MOSS_ABI_VERSION 4
 
 /* status codes */
 #define MOSS_OK                  0
@@ -58,6 +58,7 @@ size_t moss_geom_workspace_bytes(int P);
 size_t moss_image_workspace_bytes(int W, int H);
 size_t moss_binning_workspace_bytes(long long capacity);
 size_t moss_binning_workspace_bytes_ex(long long capacity, int export_keys);
+size_t moss_ckpt_workspace_bytes(long long capacity, int W, int H);
 /* largest instance count a binning workspace of `bytes` can hold */
 long long moss_binning_capacity(size_t bytes, int export_keys);
 
@@ -87,6 +88,12 @@ typedef struct MossScene {
     void* geom_ws;   size_t geom_bytes;    /* >= moss_geom_workspace_bytes(P) */
     void* image_ws;  size_t image_bytes;   /* >= moss_image_workspace_bytes(W,H) */
     void* binning_ws; size_t binning_bytes; /* capacity derived with moss_binning_capacity() */
+    void* ckpt_ws;   size_t ckpt_bytes;    /* optional (NULL/0 = off), >= moss_ckpt_workspace_bytes(capacity, W, H): the
+                                              forward stores per-pixel blend state every 256 instances of a tile so that
+                                              the backward walks a deep tile as independent 256-instance segments
+                                              (shorter critical path at ZJU/MonoCap shapes).  Forward outputs are
+                                              unaffected; gradients agree with the unsegmented walk to fp32 rounding.
+                                              Must be the same buffer in the forward and the backward call. */
 } MossScene;
 
 /* Forward.  Replaces CudaRasterizer::Rasterizer::forward (DGR/cuda_rasterizer/rasterizer.h:33-60,

@@ -30,7 +30,7 @@ STATE = dict(depths=0, clamped=1, means2D=2, cov3D=3, conic_opacity=4, rgb=5, ti
 # every symbol include/moss_splat.h declares
 SYMBOLS = [
     "moss_geom_workspace_bytes", "moss_image_workspace_bytes", "moss_binning_workspace_bytes",
-    "moss_binning_workspace_bytes_ex", "moss_binning_capacity", "moss_rasterize_forward",
+    "moss_binning_workspace_bytes_ex", "moss_binning_capacity", "moss_ckpt_workspace_bytes", "moss_rasterize_forward",
     "moss_rasterize_backward", "moss_mark_visible", "moss_export_state", "moss_abi_version",
     "moss_error_string", "moss_last_cuda_error", "moss_sizeof_scene", "moss_kernel_launches",
     "moss_profile_enable", "moss_profile_read", "moss_stage_name",
@@ -51,6 +51,7 @@ class MossScene(C.Structure):
         ("geom_ws", C.c_void_p), ("geom_bytes", C.c_size_t),
         ("image_ws", C.c_void_p), ("image_bytes", C.c_size_t),
         ("binning_ws", C.c_void_p), ("binning_bytes", C.c_size_t),
+        ("ckpt_ws", C.c_void_p), ("ckpt_bytes", C.c_size_t),
     ]
 
 
@@ -89,6 +90,8 @@ def load():
     lib.moss_binning_workspace_bytes.argtypes = [C.c_longlong]
     lib.moss_binning_workspace_bytes_ex.restype = C.c_size_t
     lib.moss_binning_workspace_bytes_ex.argtypes = [C.c_longlong, C.c_int]
+    lib.moss_ckpt_workspace_bytes.restype = C.c_size_t
+    lib.moss_ckpt_workspace_bytes.argtypes = [C.c_longlong, C.c_int, C.c_int]
     lib.moss_binning_capacity.restype = C.c_longlong
     lib.moss_binning_capacity.argtypes = [C.c_size_t, C.c_int]
     lib.moss_rasterize_forward.restype = C.c_int

@@ -108,28 +108,61 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint2* __restrict__ r
 		counters[1] = (R > capacity) ? 1u : 0u;
 		counters[2] = capacity;
 		counters[3] = busy;
+		counters[4] = 0u;       // backward segments / checkpoint records: handed out by tile_sort_kernel
+		counters[5] = 0u;
 		if (host_R) { *host_R = (int)R; __threadfence_system(); }
 	}
 }
 
-// The exclusive start of tile t: ranges[t].x is only meaningful for non-empty tiles, which is all the
-// scatter ever asks for.
+// K3.  A warp flattens the tile lists of its 32 Gaussians into one index space and every lane takes one
+// (Gaussian, tile) instance per round: the cursor atomics of one large splat (dozens of tiles) are issued by many
+// lanes at once instead of one lane waiting for each returned slot in turn -- that serial chain of L2 round trips
+// of the LARGEST splat used to set this launch's duration (22 us at ZJU shape).
+// The exclusive start of tile t (ranges[t].x) is only meaningful for non-empty tiles, which is all the scatter asks for.
 __global__ void __launch_bounds__(256)
 scatter_keys_kernel(int P, int grid_x, const int* __restrict__ radii, GeomWS g,
 	const uint2* __restrict__ ranges, uint32_t* __restrict__ cursor, const uint32_t* __restrict__ counters,
 	unsigned long long* __restrict__ keys)
 {
+	const unsigned full = 0xffffffffu;
 	const int idx = blockIdx.x * 256 + threadIdx.x;
-	if (idx >= P) return;
-	if (counters[1]) return;          // binning buffer too small: host re-runs with a larger one
-	if (!(radii[idx] > 0)) return;
-	const ushort4 r = g.rect[idx];
-	const unsigned long long key = ((unsigned long long)__float_as_uint(g.depths[idx]) << 32) | (uint32_t)idx;
-	for (uint32_t y = r.y; y < r.w; y++) {
-		for (uint32_t x = r.x; x < r.z; x++) {
-			const uint32_t t = y * grid_x + x;
+	const int lane = threadIdx.x & 31;
+	if (counters[1]) return;          // binning buffer too small: host re-runs with a larger one (uniform exit)
+	const bool vis = idx < P && radii[idx] > 0;
+	ushort4 r = make_ushort4(0, 0, 0, 0);
+	uint32_t depth_bits = 0;
+	if (vis) { r = g.rect[idx]; depth_bits = __float_as_uint(g.depths[idx]); }
+	const uint32_t w = (uint32_t)r.z - (uint32_t)r.x;
+	const uint32_t cnt = vis ? w * ((uint32_t)r.w - (uint32_t)r.y) : 0u;
+	uint32_t incl = cnt;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint32_t nb = __shfl_up_sync(full, incl, o);
+		if (lane >= o) incl += nb;
+	}
+	const uint32_t total = __shfl_sync(full, incl, 31);
+	const uint32_t origin = (uint32_t)r.x | ((uint32_t)r.y << 16);
+	for (uint32_t base = 0; base < total; base += 32) {
+		const uint32_t k = base + lane;
+		// owner = first lane whose inclusive count exceeds k (branch-free binary search over the lanes)
+		int lo = 0;
+#pragma unroll
+		for (int step = 16; step > 0; step >>= 1) {
+			const uint32_t v = __shfl_sync(full, incl, lo + step - 1);
+			if (v <= k) lo += step;
+		}
+		const int owner = min(lo, 31);
+		const uint32_t o_incl = __shfl_sync(full, incl, owner);
+		const uint32_t o_cnt = __shfl_sync(full, cnt, owner);
+		const uint32_t o_w = __shfl_sync(full, w, owner);
+		const uint32_t o_origin = __shfl_sync(full, origin, owner);
+		const uint32_t o_depth = __shfl_sync(full, depth_bits, owner);
+		if (k < total) {
+			const uint32_t local = k - (o_incl - o_cnt);
+			const uint32_t ty = local / o_w, tx = local - ty * o_w;
+			const uint32_t t = ((o_origin >> 16) + ty) * (uint32_t)grid_x + (o_origin & 0xffffu) + tx;
 			const uint32_t slot = ranges[t].x + atomicAdd(&cursor[t], 1u);
-			keys[slot] = key;
+			keys[slot] = ((unsigned long long)o_depth << 32) | (uint32_t)(idx - lane + owner);
 		}
 	}
 }

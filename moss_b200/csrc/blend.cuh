@@ -116,7 +116,7 @@ __device__ __forceinline__ int compact_hits(const uint8_t* mask, uint8_t* hits, 
 
 template <bool CULL, int NW>
 __global__ void __launch_bounds__(32 * NW)
-blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b,
+blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b, CkptWS ck,
 	float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha)
 {
 	constexpr int NT = BlendCfg<NW>::NT;          // threads per block
@@ -159,8 +159,17 @@ blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Geo
 		}
 	}
 
+	// boundary records of this tile (nullptr: no checkpointing); pixel slot = patch * 32 + lane, whatever NW is
+	float* ck_rec = ck.rec ? ck.rec + (size_t)ck.seg_base[tile] * CKPT_REC_FLOATS + (sub * NW + warp) * 32 + lane : nullptr;
+
 	for (int base = 0; base < n; base += BLEND_BATCH) {
 		if (__syncthreads_count(done) == NT) break;
+		if (ck_rec && base > 0 && (base % CKPT_SEG) == 0) {
+			// state in front of position `base`; a pixel that is already done never has it read back
+			// (its last contributor lies in front of the boundary)
+			float* r = ck_rec + (size_t)(base / CKPT_SEG - 1) * CKPT_REC_FLOATS;
+			r[0] = T; r[TILE_PIX] = C0; r[2 * TILE_PIX] = C1; r[3 * TILE_PIX] = C2; r[4 * TILE_PIX] = Dp;
+		}
 #pragma unroll
 		for (int u = 0; u < PER; u++) {
 			const int s = u * NT + (int)threadIdx.x;
@@ -257,6 +266,7 @@ blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Geo
 		out_color[2 * HW + pix] = ffma(T, bg[2], C2);
 		out_alpha[pix] = weight;   // sum of alpha*T, DGR forward.cu:380
 		out_depth[pix] = Dp;
+		if (ck.fin) ck.fin[pix] = make_float4(C0, C1, C2, Dp);
 	}
 }
 
@@ -298,9 +308,68 @@ __device__ __forceinline__ float warp_reduce2(float a, float b)
 	return s;
 }
 
+// Transpose-reduce: sum v[0..31] over the 32 lanes with recursive halving; afterwards lane l holds the total of
+// value l.  31 shuffles for 32 values (a butterfly per value would need 160), 5 dependent stages.
+__device__ __forceinline__ float warp_reduce32(const float (&v)[32])
+{
+	const unsigned full = 0xffffffffu;
+	const int lane = threadIdx.x & 31;
+	const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
+	float a[16], c[8], d[4], e[2];
+#pragma unroll
+	for (int i = 0; i < 16; i++) {
+		const float send = b4 ? v[i] : v[i + 16];
+		const float keep = b4 ? v[i + 16] : v[i];
+		a[i] = keep + __shfl_xor_sync(full, send, 16);
+	}
+#pragma unroll
+	for (int i = 0; i < 8; i++) {
+		const float send = b3 ? a[i] : a[i + 8];
+		const float keep = b3 ? a[i + 8] : a[i];
+		c[i] = keep + __shfl_xor_sync(full, send, 8);
+	}
+#pragma unroll
+	for (int i = 0; i < 4; i++) {
+		const float send = b2 ? c[i] : c[i + 4];
+		const float keep = b2 ? c[i + 4] : c[i];
+		d[i] = keep + __shfl_xor_sync(full, send, 4);
+	}
+#pragma unroll
+	for (int i = 0; i < 2; i++) {
+		const float send = b1 ? d[i] : d[i + 2];
+		const float keep = b1 ? d[i + 2] : d[i];
+		e[i] = keep + __shfl_xor_sync(full, send, 2);
+	}
+	const float send = b0 ? e[0] : e[1];
+	const float keep = b0 ? e[1] : e[0];
+	return keep + __shfl_xor_sync(full, send, 1);
+}
+// Sum v[0..3] over the warp: the 8 lanes sharing (lane>>3) end with the total of value (lane>>3).  6 shuffles.
+__device__ __forceinline__ float warp_reduce4(const float (&v)[4])
+{
+	const unsigned full = 0xffffffffu;
+	const int lane = threadIdx.x & 31;
+	const bool b4 = lane & 16, b3 = lane & 8;
+	float a[2];
+#pragma unroll
+	for (int i = 0; i < 2; i++) {
+		const float send = b4 ? v[i] : v[i + 2];
+		const float keep = b4 ? v[i + 2] : v[i];
+		a[i] = keep + __shfl_xor_sync(full, send, 16);
+	}
+	const float send = b3 ? a[0] : a[1];
+	const float keep = b3 ? a[1] : a[0];
+	float s = keep + __shfl_xor_sync(full, send, 8);
+	s += __shfl_xor_sync(full, s, 4);
+	s += __shfl_xor_sync(full, s, 2);
+	s += __shfl_xor_sync(full, s, 1);
+	return s;
+}
+
 constexpr int NGRAD = 9;          // dcolor[3], dmean2D.xy, dconic.{x,y,w}, dopacity
 constexpr int BWD_BATCH = 128;    // instances staged per round of the backward
-constexpr int BWD_GROUP = 2;      // hits processed together (their independent halves interleave)
+constexpr int BWD_GROUP = 4;      // hits processed together: their independent halves interleave and their 4 x 8
+                                  // gradient terms go through ONE 32-value transpose-reduce (5 dependent shuffle stages per 4 hits)
 
 template <int NW>
 struct BwdSmem {
@@ -318,7 +387,7 @@ struct BwdSmem {
 
 template <int NW>
 __global__ void __launch_bounds__(32 * NW)
-blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b,
+blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b, CkptWS ck,
 	const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas)
 {
 	constexpr int NT = 32 * NW;
@@ -326,12 +395,23 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 	constexpr int PER = (BWD_BATCH + NT - 1) / NT;
 	__shared__ BwdSmem<NW> sm;
 
-	const int tile = (int)im.tile_order[blockIdx.x / SPLIT];   // deepest tiles first (binning.cuh)
+	// Unit of work: a whole tile, or -- with a checkpoint workspace -- one CKPT_SEG-long segment [seg_lo, seg_hi) of
+	// its instance list, so that the segments of a deep tile run as independent blocks.
+	int tile, seg = 0;
+	if (ck.rec) {
+		if (blockIdx.x / SPLIT >= im.counters[4]) return;
+		const uint2 ts = ck.seg_map[blockIdx.x / SPLIT];
+		tile = (int)ts.x; seg = (int)ts.y;
+	} else {
+		tile = (int)im.tile_order[blockIdx.x / SPLIT];         // deepest tiles first (binning.cuh)
+	}
 	const int sub = blockIdx.x % SPLIT;
 	const int tile_y = tile / grid_x, tile_x = tile - tile_y * grid_x;
 	const uint2 range = im.ranges[tile];
 	const int n = (int)(range.y - range.x);
 	if (n == 0) return;
+	const uint32_t seg_lo = ck.rec ? (uint32_t)seg * CKPT_SEG : 0u;
+	const uint32_t seg_hi = ck.rec ? min((uint32_t)n, seg_lo + CKPT_SEG) : (uint32_t)n;
 
 	int px, py;
 	pixel_of_thread<NW>(tile_x, tile_y, sub, px, py);
@@ -344,7 +424,9 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 
 	const float T_final = inside ? im.final_T[pix] : 0.f;
 	float T = T_final;
-	const uint32_t last_contributor = inside ? im.n_contrib[pix] : 0u;
+	const uint32_t n_contrib = inside ? im.n_contrib[pix] : 0u;
+	// positions [seg_lo, last_contributor) of this unit can receive gradient from this pixel
+	const uint32_t last_contributor = n_contrib > seg_lo ? min(n_contrib, seg_hi) : seg_lo;
 	float dpix[3] = {0.f, 0.f, 0.f}, ddepth = 0.f, dalpha = 0.f;
 	if (inside) {
 		const int HW = H * W;
@@ -361,14 +443,29 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 	uint32_t block_last = 0;
 #pragma unroll
 	for (int w = 0; w < NW; w++) block_last = max(block_last, sm.warp_last[w]);
-	if (block_last == 0) return;
+	if (block_last <= seg_lo) return;
 #ifdef MOSS_TILE_TIMING
 	if (sub == 0) MOSS_TT(4);
 #endif
 
 	float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
 	float accum_depth_rec = 0.f, last_depth = 0.f, accum_alpha_rec = 0.f, last_alpha = 0.f;
+	if (ck.rec && n_contrib > seg_hi) {
+		// the pixel kept blending behind this segment: start from the forward's state in front of position seg_hi.
+		// With P = that prefix state and F the final sums, the reference's running "what lies behind" values are
+		// (F - P) / T_P  (DGR backward.cu:531-551 unrolled over the instances behind the boundary).
+		const float* r = ck.rec + ((size_t)ck.seg_base[tile] + seg) * CKPT_REC_FLOATS + (sub * NW + warp) * 32 + lane;
+		const float Tp = r[0];
+		const float4 F = ck.fin[pix];
+		const float inv = __fdividef(1.0f, Tp);
+		accum_rec[0] = (F.x - r[TILE_PIX]) * inv; accum_rec[1] = (F.y - r[2 * TILE_PIX]) * inv;
+		accum_rec[2] = (F.z - r[3 * TILE_PIX]) * inv;
+		accum_depth_rec = (F.w - r[4 * TILE_PIX]) * inv;
+		accum_alpha_rec = (Tp - T_final) * inv;
+		T = Tp;
+	}
 	const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+	const int n_walk = (int)(block_last - seg_lo);      // positions block_last-1 ... seg_lo, back to front
 
 	// batch slot s holds forward position (0-based) block_last-1-(base+s): the walk is back to front.
 	// Software pipeline as in the forward: the gathers of the next batch are issued before this one is processed.
@@ -379,20 +476,20 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 	for (int u = 0; u < PER; u++) {
 		const int i = u * NT + (int)threadIdx.x;
 		nid[u] = 0u; nxy[u] = make_float2(0.f, 0.f); nco[u] = make_float4(0.f, 0.f, 0.f, 0.f); nfeat[u] = nco[u];
-		if (u * NT + (int)threadIdx.x < BWD_BATCH && i < (int)block_last) {
+		if (u * NT + (int)threadIdx.x < BWD_BATCH && i < n_walk) {
 			nid[u] = b.point_list[range.x + block_last - 1 - i];
 			nxy[u] = g.means2D[nid[u]]; nco[u] = g.conic_opacity[nid[u]]; nfeat[u] = g.feat[nid[u]];
 		}
 	}
 
-	for (int base = 0; base < (int)block_last; base += BWD_BATCH) {
+	for (int base = 0; base < n_walk; base += BWD_BATCH) {
 		__syncthreads();
 #pragma unroll
 		for (int u = 0; u < PER; u++) {
 			const int s = u * NT + (int)threadIdx.x;
 			if (s < BWD_BATCH) {
 				uint32_t hit = 0;
-				if (base + s < (int)block_last) {
+				if (base + s < n_walk) {
 					sm.id[s] = nid[u]; sm.xy[s] = nxy[u]; sm.co[s] = nco[u]; sm.feat[s] = nfeat[u];
 					hit = patch_hit_mask<NW>(nxy[u], nco[u], tile_px0, tile_py0, sub);
 				}
@@ -406,14 +503,14 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 		for (int u = 0; u < PER; u++) {
 			const int s = u * NT + (int)threadIdx.x;
 			const int i = base + BWD_BATCH + s;
-			if (s < BWD_BATCH && i < (int)block_last) {
+			if (s < BWD_BATCH && i < n_walk) {
 				nid[u] = b.point_list[range.x + block_last - 1 - i];
 				nxy[u] = g.means2D[nid[u]]; nco[u] = g.conic_opacity[nid[u]]; nfeat[u] = g.feat[nid[u]];
 			}
 		}
 
 		// compact the slots that can reach this warp's patch AND lie in front of the warp's last contributor
-		const int cnt = min(BWD_BATCH, (int)block_last - base);
+		const int cnt = min(BWD_BATCH, n_walk - base);
 		int nh = 0;
 #pragma unroll
 		for (int sb = 0; sb < BWD_BATCH; sb += 32) {
@@ -453,7 +550,7 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 			if (!__any_sync(full, any_valid)) continue;
 
 			// ---- recurrences (serial over the hits, predicated) and gradient terms ------------------------
-			float v[BWD_GROUP][8], v_opa[BWD_GROUP];
+			float v[BWD_GROUP * 8], v_opa[BWD_GROUP];
 #pragma unroll
 			for (int k = 0; k < BWD_GROUP; k++) {
 				const bool ok = valid[k];
@@ -469,7 +566,7 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 				for (int ch = 0; ch < 3; ch++) {
 					const float arc = last_alpha * last_color[ch] + omla * accum_rec[ch];
 					dL_dopa += (c[ch] - arc) * dpix[ch];
-					v[k][ch] = ok ? dchannel_dcolor * dpix[ch] : 0.f;
+					v[k * 8 + ch] = ok ? dchannel_dcolor * dpix[ch] : 0.f;
 					accum_rec[ch] = ok ? arc : accum_rec[ch];
 					last_color[ch] = ok ? c[ch] : last_color[ch];
 				}
@@ -489,23 +586,23 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 				const float gdx = Gs[k] * dx[k], gdy = Gs[k] * dy[k];
 				const float dG_ddelx = -gdx * co.x - gdy * co.y;
 				const float dG_ddely = -gdy * co.z - gdx * co.y;
-				v[k][3] = ok ? dL_dG * dG_ddelx * ddelx_dx : 0.f;
-				v[k][4] = ok ? dL_dG * dG_ddely * ddely_dy : 0.f;
-				v[k][5] = ok ? -0.5f * gdx * dx[k] * dL_dG : 0.f;
-				v[k][6] = ok ? -0.5f * gdx * dy[k] * dL_dG : 0.f;
-				v[k][7] = ok ? -0.5f * gdy * dy[k] * dL_dG : 0.f;
+				v[k * 8 + 3] = ok ? dL_dG * dG_ddelx * ddelx_dx : 0.f;
+				v[k * 8 + 4] = ok ? dL_dG * dG_ddely * ddely_dy : 0.f;
+				v[k * 8 + 5] = ok ? -0.5f * gdx * dx[k] * dL_dG : 0.f;
+				v[k * 8 + 6] = ok ? -0.5f * gdx * dy[k] * dL_dG : 0.f;
+				v[k * 8 + 7] = ok ? -0.5f * gdy * dy[k] * dL_dG : 0.f;
 				v_opa[k] = ok ? Gs[k] * dL_dopa : 0.f;
 			}
-			// ---- warp reduction, one row per (warp, slot) ---------------------------------------------------
-			const float so = warp_reduce2(v_opa[0], v_opa[1]);
-#pragma unroll
-			for (int k = 0; k < BWD_GROUP; k++) {
-				const float s8 = warp_reduce8(v[k]);
-				if (h + k < nh) {
-					float* row = sm.grad + (warp * BWD_BATCH + jj[k]) * NGRAD;
-					if ((lane & 3) == 0) row[lane >> 2] = s8;
-					if (lane == 1 + 16 * k) { row[8] = so; sm.written[warp][jj[k]] = 1; }
-				}
+			// ---- warp reduction, one row per (warp, slot): lane l ends with component l&7 of hit l>>3 ------------
+			static_assert(BWD_GROUP == 4, "the transpose-reduce below is laid out for 4 hits x 8 components");
+			const float s32 = warp_reduce32(v);
+			const float so = warp_reduce4(v_opa);
+			const int kk = lane >> 3;
+			const int jsel = kk == 0 ? jj[0] : (kk == 1 ? jj[1] : (kk == 2 ? jj[2] : jj[3]));
+			if (h + kk < nh) {
+				float* row = sm.grad + (warp * BWD_BATCH + jsel) * NGRAD;
+				row[lane & 7] = s32;
+				if ((lane & 7) == 0) { row[8] = so; sm.written[warp][jsel] = 1; }
 			}
 		}
 		__syncthreads();

@@ -61,7 +61,7 @@ struct ImageWS {
 	uint32_t* tile_count;     // [T]  per-tile instance count, then scatter cursor
 	uint2*    ranges;         // [T]  [first, last) into the sorted list
 	uint32_t* tile_order;     // [T]  launch order of the blend kernels: tiles by descending instance count
-	uint32_t* counters;       // [4]  num_rendered, overflow, capacity, non-empty tiles
+	uint32_t* counters;       // [8]  num_rendered, overflow, capacity, non-empty tiles, backward segments, checkpoint records
 };
 struct BinWS {
 	unsigned long long* keys; // [cap] (depth_bits << 32 | gaussian id), grouped per tile, sorted in place
@@ -102,7 +102,7 @@ __host__ __device__ inline ImageWS carve_image(char* base, size_t N, size_t T, s
 	s.tile_count = carve<uint32_t>(p, T);
 	s.ranges = carve<uint2>(p, T);
 	s.tile_order = carve<uint32_t>(p, T);
-	s.counters = carve<uint32_t>(p, 4);
+	s.counters = carve<uint32_t>(p, 8);
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return s;
 }
@@ -115,6 +115,38 @@ __host__ __device__ inline BinWS carve_bin(char* base, size_t cap, bool export_k
 	b.keys_sorted = export_keys ? carve<unsigned long long>(p, cap) : nullptr;
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return b;
+}
+
+// Optional checkpoint workspace (moss_ckpt_workspace_bytes): lets the blend backward split a deep tile's instance
+// list into segments of CKPT_SEG that run as independent blocks.  The forward stores every pixel's running state
+// (T, C rgb, D) at the segment boundaries and its final sums; a backward segment starts from the boundary state
+// instead of walking everything behind it (blend.cuh).
+constexpr int CKPT_SEG = 256;
+constexpr int CKPT_REC_FLOATS = 5 * TILE_PIX;   // one boundary record of one tile: [component][pixel slot]
+struct CkptWS {
+	float4*   fin;        // [N]  final (C0, C1, C2, D) of every pixel, without background
+	uint32_t* seg_base;   // [T]  first boundary record of the tile
+	uint2*    seg_map;    // [max_segs]  (tile, segment) of backward block group k, deep tiles first (roughly)
+	float*    rec;        // [max_recs][5][256]
+	uint32_t  max_segs, max_recs;
+};
+__host__ __device__ inline CkptWS carve_ckpt(char* base, size_t N, size_t T, size_t cap, size_t* bytes = nullptr)
+{
+	char* p = base;
+	CkptWS c;
+	c.max_recs = (uint32_t)(cap / CKPT_SEG);
+	c.max_segs = (uint32_t)(cap / CKPT_SEG + T);
+	c.fin = carve<float4>(p, N);
+	c.seg_base = carve<uint32_t>(p, T);
+	c.seg_map = carve<uint2>(p, c.max_segs);
+	c.rec = carve<float>(p, (size_t)c.max_recs * CKPT_REC_FLOATS);
+	if (bytes) *bytes = (size_t)(p - base) + 256;
+	return c;
+}
+__host__ __device__ inline CkptWS no_ckpt()
+{
+	CkptWS c; c.fin = nullptr; c.seg_base = nullptr; c.seg_map = nullptr; c.rec = nullptr; c.max_segs = 0; c.max_recs = 0;
+	return c;
 }
 
 // Per-view parameters.  The matrices live in device memory (they are torch tensors in the reference

@@ -138,6 +138,13 @@ inline ViewParams make_view(const MossScene* sc)
 	return vp;
 }
 
+// The optional checkpoint workspace is used when it is large enough for this call's binning capacity.
+inline CkptWS scene_ckpt(const MossScene* sc, uint32_t capacity, int N, int T)
+{
+	if (!sc->ckpt_ws || sc->ckpt_bytes < moss_ckpt_workspace_bytes((long long)capacity, sc->W, sc->H)) return no_ckpt();
+	return carve_ckpt((char*)sc->ckpt_ws, (size_t)N, (size_t)T, (size_t)capacity);
+}
+
 // Blend block shape (1 whole tile / 2 half / 3 quarter).  Small images have few busy tiles and the deepest one sets
 // the launch time, so its patches are spread over more SMs; large images have enough tiles to fill the machine
 // and prefer fewer, larger blocks (less duplicated staging).
@@ -152,6 +159,7 @@ __global__ void reset_overflow_kernel(uint32_t* counters, uint32_t capacity)
 {
 	counters[1] = counters[0] > capacity ? 1u : 0u;
 	counters[2] = capacity;
+	counters[4] = 0u; counters[5] = 0u;
 }
 
 __global__ void fill_background_kernel(int N, const float* __restrict__ bg, float* __restrict__ color,
@@ -227,6 +235,13 @@ size_t moss_binning_workspace_bytes_ex(long long capacity, int export_keys)
 	return b;
 }
 size_t moss_binning_workspace_bytes(long long capacity) { return moss_binning_workspace_bytes_ex(capacity, 0); }
+size_t moss_ckpt_workspace_bytes(long long capacity, int W, int H)
+{
+	size_t b = 0;
+	const size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+	carve_ckpt(nullptr, (size_t)W * H, T, (size_t)(capacity > 0 ? capacity : 0), &b);
+	return b;
+}
 long long moss_binning_capacity(size_t bytes, int export_keys)
 {
 	const size_t per = export_keys ? 20 : 12;
@@ -264,6 +279,7 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 	const uint32_t capacity = (uint32_t)(cap_ll > 0xfffffff0ll ? 0xfffffff0ll : cap_ll);
 	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P);
 	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
+	const CkptWS ck = scene_ckpt(sc, capacity, N, T);
 
 	int slot = -1;
 	if (!(flags & MOSS_FLAG_ASYNC)) {
@@ -295,22 +311,22 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 		im.counters, b.keys); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_TILE_SORT, stream);
-	tile_sort_kernel<<<T, TILE_PIX, 0, stream>>>(im, b); }
+	tile_sort_kernel<<<T, TILE_PIX, 0, stream>>>(im, b, ck); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_FWD, stream);
 	const bool cull = !(flags & MOSS_FLAG_NO_CULL);
 	switch (blend_split(flags, T)) {
 	case 1:
-		if (cull) blend_forward_kernel<true, 8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
-		else blend_forward_kernel<false, 8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+		if (cull) blend_forward_kernel<true, 8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
+		else blend_forward_kernel<false, 8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
 		break;
 	case 2:
-		if (cull) blend_forward_kernel<true, 4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
-		else blend_forward_kernel<false, 4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+		if (cull) blend_forward_kernel<true, 4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
+		else blend_forward_kernel<false, 4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
 		break;
 	default:
-		if (cull) blend_forward_kernel<true, 2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
-		else blend_forward_kernel<false, 2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, out_color, out_depth, out_alpha);
+		if (cull) blend_forward_kernel<true, 2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
+		else blend_forward_kernel<false, 2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
 		break;
 	} }
 	MOSS_CHECK_LAUNCH(stream, flags);
@@ -353,12 +369,15 @@ int moss_rasterize_backward(void* stream_, const MossScene* sc, unsigned flags, 
 	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P);
 	ImageWS im = carve_image((char*)sc->image_ws, (size_t)N, (size_t)T);
 	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
+	const CkptWS ck = scene_ckpt(sc, capacity, N, T);
+	// work units: tiles, or (with checkpoints) at most capacity/CKPT_SEG + T segments; surplus blocks exit at once
+	const unsigned units = ck.rec ? ck.max_segs : (unsigned)T;
 
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_BWD, stream);
 	switch (blend_split(flags, T)) {
-	case 1: blend_backward_kernel<8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha); break;
-	case 2: blend_backward_kernel<4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha); break;
-	default: blend_backward_kernel<2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, dL_dpix, dL_ddepth, dL_dalpha); break;
+	case 1: blend_backward_kernel<8><<<units, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha); break;
+	case 2: blend_backward_kernel<4><<<2 * units, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha); break;
+	default: blend_backward_kernel<2><<<4 * units, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha); break;
 	} }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_PREPROCESS_BWD, stream);

@@ -248,14 +248,27 @@ __device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 ra
 
 // One block per tile, in tile_order (deepest first).
 __global__ void __launch_bounds__(TILE_PIX)
-tile_sort_kernel(ImageWS im, BinWS b)
+tile_sort_kernel(ImageWS im, BinWS b, CkptWS ck)
 {
 	__shared__ SortSmem ss;
+	__shared__ uint32_t seg_off;
 	if (im.counters[1]) return;   // binning overflow: the host re-runs with a larger buffer
 	if (blockIdx.x >= im.counters[3]) return;                 // only non-empty tiles have work
 	const int tile = (int)im.tile_order[blockIdx.x];
 	const uint2 range = im.ranges[tile];
 	const int n = (int)(range.y - range.x);
+	if (ck.rec && n > 0) {
+		// hand the tile its backward segments and boundary records.  Blocks start in tile_order (deepest first), so
+		// the deep tiles' segments land at the front of seg_map; the exact order only affects scheduling.
+		const uint32_t nseg = ((uint32_t)n + CKPT_SEG - 1) / CKPT_SEG;
+		if (threadIdx.x == 0) {
+			seg_off = atomicAdd(&im.counters[4], nseg);
+			ck.seg_base[tile] = atomicAdd(&im.counters[5], nseg - 1u);
+		}
+		__syncthreads();
+		for (uint32_t i = threadIdx.x; i < nseg; i += TILE_PIX)
+			if (seg_off + i < ck.max_segs) ck.seg_map[seg_off + i] = make_uint2((uint32_t)tile, i);
+	}
 	MOSS_TT(0);
 	if (n > 0) tile_sort(ss, b, range, n, tile);
 	MOSS_TT(1);

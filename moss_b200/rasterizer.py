@@ -59,15 +59,36 @@ def _f32c(t, name):
 # remembered instance counts so that the binning workspace is right-sized without a host sync
 _capacity_hint = {}
 
+# Segmented backward (checkpoint workspace, include/moss_splat.h MossScene.ckpt_ws): "auto" turns it on for images of
+# up to 4096 tiles, where a few deep tiles set the backward's duration; larger images have enough tiles to fill the
+# GPU and skip the extra checkpoint traffic.  True / False force it (tests compare both).
+_segmented_backward = "auto"
+
+
+def set_segmented_backward(mode):
+    """mode: "auto" | True | False.  Returns the previous setting."""
+    global _segmented_backward
+    if mode not in ("auto", True, False):
+        raise ValueError("mode must be 'auto', True or False")
+    prev, _segmented_backward = _segmented_backward, mode
+    return prev
+
+
+def _want_ckpt(W, H):
+    if _segmented_backward == "auto":
+        return ((W + 15) // 16) * ((H + 15) // 16) <= 4096
+    return bool(_segmented_backward)
+
 
 class RasterState:
     """Workspaces + scene descriptor of one forward call (kept alive for the backward)."""
-    __slots__ = ("scene", "ws", "binning", "flags", "num_rendered", "keep", "grad_buf", "param_grad_numel")
+    __slots__ = ("scene", "ws", "binning", "ckpt", "flags", "num_rendered", "keep", "grad_buf", "param_grad_numel")
 
     def __init__(self):
         self.scene = _abi.MossScene()
         self.ws = None
         self.binning = None
+        self.ckpt = None
         self.flags = 0
         self.num_rendered = 0
         self.keep = None
@@ -123,10 +144,16 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
         nr = C.c_int(0)
         color, depth, alpha = out[0:3], out[3:4], out[4:5]
         call_flags = flags
+        want_ckpt = _want_ckpt(W, H)
         while True:
             bbytes = lib.moss_binning_workspace_bytes_ex(cap, export)
             binning = torch.empty((bbytes,), dtype=torch.uint8, device=dev)
             sc.binning_ws = binning.data_ptr(); sc.binning_bytes = bbytes
+            ckpt = None
+            if want_ckpt:
+                cbytes = lib.moss_ckpt_workspace_bytes(lib.moss_binning_capacity(bbytes, export), W, H)
+                ckpt = torch.empty((cbytes,), dtype=torch.uint8, device=dev)
+                sc.ckpt_ws = ckpt.data_ptr(); sc.ckpt_bytes = cbytes
             status = lib.moss_rasterize_forward(stream, C.byref(sc), call_flags, color.data_ptr(), depth.data_ptr(),
                                                 alpha.data_ptr(), _ptr(radii), C.byref(nr))
             if status == _abi.MOSS_ERR_BINNING_OVERFLOW:
@@ -137,7 +164,7 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
             break
         if nr.value >= 0:
             _capacity_hint[key] = nr.value
-        st.ws, st.binning, st.flags, st.num_rendered = ws, binning, flags, nr.value
+        st.ws, st.binning, st.ckpt, st.flags, st.num_rendered = ws, binning, ckpt, flags, nr.value
         # tensors whose device pointers sit in the scene struct must outlive the backward
         st.keep = (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, bg, view, proj, campos)
     return color, radii, depth, alpha, st
@@ -222,8 +249,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         # The workspaces and the inputs whose device pointers sit in st.scene go through save_for_backward, like
         # the reference's three state tensors (DGR/diff_gaussian_rasterization/__init__.py:97): autograd frees
         # them right after the backward unless retain_graph is set.
-        ctx.save_for_backward(radii, st.ws, st.binning, *st.keep)
-        st.ws = st.binning = st.keep = None
+        ctx.save_for_backward(radii, st.ws, st.binning, *st.keep, *([st.ckpt] if st.ckpt is not None else []))
+        st.ws = st.binning = st.keep = st.ckpt = None
         ctx.state = st
         return color, radii, depth, alpha
 
