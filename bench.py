@@ -132,12 +132,12 @@ def run_ours(args, rank, world, dev):
 
     state = {}
 
-    def step(i):
+    def step(i, collective=True):
         rs = settings[i % len(settings)]
         color, radii, depth, alpha, st = M.forward_raw(devt["means3D"], devt["shs"], devt["colors_precomp"], devt["opacities"],
                                                        devt["scales"], devt["rotations"], devt["cov3D_precomp"], rs)
         M.backward_raw(st, radii, gc, gd, ga)
-        if world > 1:
+        if world > 1 and collective:
             parallel.allreduce_param_grads(st.grad_buf, st.param_grad_numel)
         state["st"], state["radii"] = st, radii
         return st
@@ -178,7 +178,7 @@ def run_ours(args, rank, world, dev):
     t_ext = time.perf_counter()
     i = 0
     while rank == 0 and not args.quick and time.perf_counter() - t0 < 1.2 and time.perf_counter() - t_ext < 3.0:
-        step(i); i += 1
+        step(i, collective=False); i += 1      # rank 0 only: must not issue a collective the other ranks do not match
         if i % 64 == 0:
             torch.cuda.synchronize(dev)
     torch.cuda.synchronize(dev)

@@ -36,7 +36,7 @@ __device__ __forceinline__ int order_bucket(uint32_t c)
 // with the natural order several deep tiles of the body's centre column land on one SM and the launch waits
 // for that SM while the others idle (ncu: sm__cycles_active.avg 37% of elapsed).
 __global__ void __launch_bounds__(SCAN_THREADS)
-tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint2* __restrict__ ranges,
+tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_total, uint2* __restrict__ ranges,
 	uint32_t* __restrict__ counters, uint32_t capacity, volatile int* host_R, uint32_t* __restrict__ tile_order)
 {
 	__shared__ uint32_t warp_sums[32];
@@ -46,8 +46,20 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint2* __restrict__ r
 	if (threadIdx.x == 0) carry_s = 0;
 	if (threadIdx.x < ORDER_BUCKETS) bucket_n[threadIdx.x] = 0;
 	__syncthreads();
-	// size-class histogram (counts are still intact here)
-	for (int t = threadIdx.x; t < T; t += SCAN_THREADS) atomicAdd(&bucket_n[order_bucket(tile_count[t])], 1u);
+	// per-tile totals; the sub-counters become the scatter cursors (exclusive prefix inside the tile's segment);
+	// size-class histogram
+	for (int t = threadIdx.x; t < T; t += SCAN_THREADS) {
+		uint4* sub = reinterpret_cast<uint4*>(tile_count + (size_t)t * TILE_SUB);
+		static_assert(TILE_SUB == 8, "two uint4 per tile");
+		const uint4 a = sub[0], b = sub[1];
+		uint4 pa, pb;
+		pa.x = 0u; pa.y = a.x; pa.z = pa.y + a.y; pa.w = pa.z + a.z;
+		pb.x = pa.w + a.w; pb.y = pb.x + b.x; pb.z = pb.y + b.y; pb.w = pb.z + b.z;
+		const uint32_t c = pb.w + b.w;
+		sub[0] = pa; sub[1] = pb;
+		tile_total[t] = c;
+		atomicAdd(&bucket_n[order_bucket(c)], 1u);
+	}
 	__syncthreads();
 	if (warp == 0) {
 		// descending exclusive offsets: class 131 first ... class 0 (empty) last
@@ -67,13 +79,13 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint2* __restrict__ r
 	}
 	__syncthreads();
 	for (int t = threadIdx.x; t < T; t += SCAN_THREADS)
-		tile_order[atomicAdd(&bucket_n[order_bucket(tile_count[t])], 1u)] = (uint32_t)t;
+		tile_order[atomicAdd(&bucket_n[order_bucket(tile_total[t])], 1u)] = (uint32_t)t;
 	__syncthreads();
 	// classes 1..3 never occur (count 1 maps to class 4), so the offset of class 1 is the number of non-empty tiles
 	const uint32_t busy = bucket_n[1];
 	for (int base = 0; base < T; base += SCAN_THREADS) {
 		const int t = base + threadIdx.x;
-		const uint32_t c = (t < T) ? tile_count[t] : 0u;
+		const uint32_t c = (t < T) ? tile_total[t] : 0u;
 		uint32_t v = c;
 #pragma unroll
 		for (int o = 1; o < 32; o <<= 1) {
@@ -96,7 +108,6 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint2* __restrict__ r
 		const uint32_t incl = v + (warp > 0 ? warp_sums[warp - 1] : 0u) + carry;
 		if (t < T) {
 			ranges[t] = c ? make_uint2(incl - c, incl) : make_uint2(0u, 0u);
-			tile_count[t] = 0u;
 		}
 		__syncthreads();
 		if (threadIdx.x == SCAN_THREADS - 1) carry_s = incl;
@@ -161,7 +172,9 @@ scatter_keys_kernel(int P, int grid_x, const int* __restrict__ radii, GeomWS g,
 			const uint32_t local = k - (o_incl - o_cnt);
 			const uint32_t ty = local / o_w, tx = local - ty * o_w;
 			const uint32_t t = ((o_origin >> 16) + ty) * (uint32_t)grid_x + (o_origin & 0xffffu) + tx;
-			const uint32_t slot = ranges[t].x + atomicAdd(&cursor[t], 1u);
+			// the cursor of the sub-counter this warp counted into (preprocess: same warp <-> same 32 Gaussians)
+			const uint32_t sub = ((uint32_t)idx >> 5) & (TILE_SUB - 1);
+			const uint32_t slot = ranges[t].x + atomicAdd(&cursor[t * TILE_SUB + sub], 1u);
 			keys[slot] = ((unsigned long long)o_depth << 32) | (uint32_t)(idx - lane + owner);
 		}
 	}

@@ -388,7 +388,8 @@ struct BwdSmem {
 template <int NW>
 __global__ void __launch_bounds__(32 * NW)
 blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b, CkptWS ck,
-	const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas)
+	const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas,
+	int deterministic)
 {
 	constexpr int NT = 32 * NW;
 	constexpr int SPLIT = NPATCH / NW;
@@ -625,16 +626,41 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 					else { r[0] += row[3]; r[1] += row[4]; r[2] += row[5]; r[3] += row[6]; r[4] += row[7]; }
 				}
 			}
-			if (any) {
-				float4* acc = g.grad_acc + 3 * (size_t)sm.id[j];
+			if (any && !deterministic) {
+				float4* acc = g.grad_acc + GRAD_ACC_VEC * (size_t)sm.id[j];
 				if (!second) atomicAdd(acc, make_float4(r[0], r[1], r[2], r[3]));
 				else { atomicAdd(acc + 1, make_float4(r[0], r[1], r[2], r[3])); atomicAdd(&acc[2].x, r[4]); }
+			} else if (any) {
+				// order-independent accumulation: the block's partial sums (themselves computed in a fixed order)
+				// are added as 64-bit fixed-point integers
+				const float S = det_scale_from_bits(im.counters[6], false);
+				unsigned long long* acc = reinterpret_cast<unsigned long long*>(g.grad_acc + GRAD_ACC_VEC * (size_t)sm.id[j]);
+				const int first = second ? 4 : 0, cnt = second ? 5 : 4;
+#pragma unroll
+				for (int i = 0; i < 5; i++)
+					if (i < cnt) atomicAdd(acc + first + i, (unsigned long long)__float2ll_rn(r[i] * S));
 			}
 		}
 	}
 #ifdef MOSS_TILE_TIMING
 	if (sub == 0) { MOSS_TT(5); if (threadIdx.x == 0) { g_tile_timing[tile * 8 + 6] = (long long)block_last; g_tile_timing[tile * 8 + 7] = (long long)n; } }
 #endif
+}
+
+// max |upstream gradient| over dL_dpix [3N], dL_ddepth [N], dL_dalpha [N] -> *out (float bits, caller-zeroed).
+// max is order-independent, so the fixed-point scale derived from it is reproducible.
+__global__ void __launch_bounds__(256)
+upstream_maxabs_kernel(int N, const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepth,
+	const float* __restrict__ dL_dalpha, uint32_t* __restrict__ out)
+{
+	float m = 0.f;
+	for (int i = blockIdx.x * 256 + threadIdx.x; i < N; i += gridDim.x * 256) {
+		m = fmaxf(m, fmaxf(fmaxf(fabsf(dL_dpix[i]), fabsf(dL_dpix[N + i])), fabsf(dL_dpix[2 * N + i])));
+		m = fmaxf(m, fmaxf(fabsf(dL_ddepth[i]), fabsf(dL_dalpha[i])));
+	}
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+	if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out, __float_as_uint(m));   // non-negative floats order like their bits
 }
 
 } // namespace moss

@@ -41,6 +41,9 @@ __host__ __device__ __forceinline__ size_t align_up(size_t v, size_t a) { return
 // ---------------------------------------------------------------------------------------------
 // Workspace carving (caller-owned memory; layout private to this library).
 // ---------------------------------------------------------------------------------------------
+constexpr int TILE_SUB = 8;        // sub-counters per tile (ImageWS::tile_count)
+constexpr int GRAD_ACC_VEC = 5;    // float4 slots per Gaussian in GeomWS::grad_acc
+
 struct GeomWS {
 	float*    depths;         // [P]   view-space z (sort key low bits)
 	float2*   means2D;        // [P]   pixel-space centre
@@ -50,18 +53,25 @@ struct GeomWS {
 	uint32_t* tiles_touched;  // [P]
 	ushort4*  rect;           // [P]   tile rect (xmin, ymin, xmax, ymax)
 	uint8_t*  clamped;        // [P]   bit c set <=> SH colour channel c was clamped at 0
-	float4*   grad_acc;       // [3P]  blend-backward accumulators, 48 B per Gaussian so they take VECTOR atomics:
+	float4*   grad_acc;       // [5P]  blend-backward accumulators, 80 B per Gaussian; the first 48 B take VECTOR atomics:
 	                          //       [0] = (dL_dcolor rgb, dL_dopacity)  [1] = (dL_dmean2D xy, dL_dconic xy)
 	                          //       [2] = (dL_dconic w, -, -, -).  Zeroed by the forward preprocess, consumed and
 	                          //       re-zeroed by the backward preprocess: no memset launch anywhere.
+	                          //       MOSS_FLAG_DETERMINISTIC views the 80 B as nine int64 fixed-point sums instead
+	                          //       (colour rgb, opacity, mean2D xy, conic x y w): integer adds commute, so the
+	                          //       result does not depend on the order in which blocks arrive.
 };
 struct ImageWS {
 	float*    final_T;        // [N]
 	uint32_t* n_contrib;      // [N]
-	uint32_t* tile_count;     // [T]  per-tile instance count, then scatter cursor
+	uint32_t* tile_count;     // [T][TILE_SUB]  per-tile instance counts, split over TILE_SUB sub-counters picked by the
+	                          //      counting warp (a busy tile's single counter is a serialisation point in L2: ~1700
+	                          //      same-address atomics took ~9 us at ZJU shape); after the scan: the scatter cursors
+	uint32_t* tile_total;     // [T]  instances per tile
 	uint2*    ranges;         // [T]  [first, last) into the sorted list
 	uint32_t* tile_order;     // [T]  launch order of the blend kernels: tiles by descending instance count
-	uint32_t* counters;       // [8]  num_rendered, overflow, capacity, non-empty tiles, backward segments, checkpoint records
+	uint32_t* counters;       // [8]  num_rendered, overflow, capacity, non-empty tiles, backward segments, checkpoint records,
+	                          //      bits of max|upstream gradient| (deterministic backward), reserved
 };
 struct BinWS {
 	unsigned long long* keys; // [cap] (depth_bits << 32 | gaussian id), grouped per tile, sorted in place
@@ -89,7 +99,7 @@ __host__ __device__ inline GeomWS carve_geom(char* base, size_t P, size_t* bytes
 	g.tiles_touched = carve<uint32_t>(p, P);
 	g.rect = carve<ushort4>(p, P);
 	g.clamped = carve<uint8_t>(p, P);
-	g.grad_acc = carve<float4>(p, 3 * P);
+	g.grad_acc = carve<float4>(p, GRAD_ACC_VEC * P);
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return g;
 }
@@ -99,7 +109,8 @@ __host__ __device__ inline ImageWS carve_image(char* base, size_t N, size_t T, s
 	ImageWS s;
 	s.final_T = carve<float>(p, N);
 	s.n_contrib = carve<uint32_t>(p, N);
-	s.tile_count = carve<uint32_t>(p, T);
+	s.tile_count = carve<uint32_t>(p, T * TILE_SUB);
+	s.tile_total = carve<uint32_t>(p, T);
 	s.ranges = carve<uint2>(p, T);
 	s.tile_order = carve<uint32_t>(p, T);
 	s.counters = carve<uint32_t>(p, 8);
@@ -115,6 +126,18 @@ __host__ __device__ inline BinWS carve_bin(char* base, size_t cap, bool export_k
 	b.keys_sorted = export_keys ? carve<unsigned long long>(p, cap) : nullptr;
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return b;
+}
+
+// MOSS_FLAG_DETERMINISTIC: fixed-point scale of the blend-backward accumulators, a power of two derived from the
+// largest |upstream gradient| m of the call (bits in counters[6]).  A Gaussian's sums are bounded by about
+// 2^17 (largest per-pixel factor: 0.5*W*|d|*conic) x 2^12 pixels x m, so S = 2^(31 - ceil(log2 m)) keeps S*sum below
+// 2^62 while resolving 2^-31 m, finer than fp32 at m.
+__device__ __forceinline__ float det_scale_from_bits(uint32_t bits, bool inverse)
+{
+	const float m = __uint_as_float(bits);
+	int e = 0;
+	if (m > 0.f && m < 3.0e38f) frexpf(m, &e);
+	return ldexpf(1.0f, inverse ? (e - 31) : (31 - e));
 }
 
 // Optional checkpoint workspace (moss_ckpt_workspace_bytes): lets the blend backward split a deep tile's instance

@@ -288,7 +288,7 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 	}
 
 	if (!(flags & MOSS_FLAG_REBIN)) {
-		MOSS_CUDA_TRY(cudaMemsetAsync(im.tile_count, 0, (size_t)T * sizeof(uint32_t), stream));
+		MOSS_CUDA_TRY(cudaMemsetAsync(im.tile_count, 0, (size_t)T * TILE_SUB * sizeof(uint32_t), stream));
 		{ MOSS_STAGE(MOSS_STAGE_PREPROCESS, stream);
 		preprocess_forward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
 			P, vp, sc->means3D, sc->shs, sc->colors_precomp, sc->opacities, sc->scales, sc->rotations,
@@ -297,7 +297,7 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 		int* host_R = nullptr;
 		if (slot >= 0) MOSS_CUDA_TRY(cudaHostGetDevicePointer((void**)&host_R, g_slots.host + slot, 0));
 		{ MOSS_STAGE(MOSS_STAGE_TILE_SCAN, stream);
-		tile_scan_kernel<<<1, SCAN_THREADS, 0, stream>>>(T, im.tile_count, im.ranges, im.counters, capacity, host_R, im.tile_order); }
+		tile_scan_kernel<<<1, SCAN_THREADS, 0, stream>>>(T, im.tile_count, im.tile_total, im.ranges, im.counters, capacity, host_R, im.tile_order); }
 		MOSS_CHECK_LAUNCH(stream, flags);
 		if (slot >= 0) MOSS_CUDA_TRY(cudaEventRecord(g_slots.ev[slot], stream));
 	} else {
@@ -372,18 +372,25 @@ int moss_rasterize_backward(void* stream_, const MossScene* sc, unsigned flags, 
 	const CkptWS ck = scene_ckpt(sc, capacity, N, T);
 	// work units: tiles, or (with checkpoints) at most capacity/CKPT_SEG + T segments; surplus blocks exit at once
 	const unsigned units = ck.rec ? ck.max_segs : (unsigned)T;
+	const int det = (flags & MOSS_FLAG_DETERMINISTIC) ? 1 : 0;
+	if (det) {
+		MOSS_CUDA_TRY(cudaMemsetAsync(im.counters + 6, 0, sizeof(uint32_t), stream));
+		{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
+		upstream_maxabs_kernel<<<min((N + 255) / 256, 592), 256, 0, stream>>>(N, dL_dpix, dL_ddepth, dL_dalpha, im.counters + 6); }
+		MOSS_CHECK_LAUNCH(stream, flags);
+	}
 
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_BWD, stream);
 	switch (blend_split(flags, T)) {
-	case 1: blend_backward_kernel<8><<<units, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha); break;
-	case 2: blend_backward_kernel<4><<<2 * units, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha); break;
-	default: blend_backward_kernel<2><<<4 * units, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha); break;
+	case 1: blend_backward_kernel<8><<<units, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
+	case 2: blend_backward_kernel<4><<<2 * units, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
+	default: blend_backward_kernel<2><<<4 * units, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
 	} }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_PREPROCESS_BWD, stream);
 	preprocess_backward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
 		P, vp, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
-		dL_dmean2D, dL_dconic, dL_dcolor, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot); }
+		dL_dmean2D, dL_dconic, dL_dcolor, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, det, im.counters); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	return MOSS_OK;
 }

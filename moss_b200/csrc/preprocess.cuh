@@ -106,22 +106,23 @@ __device__ __forceinline__ Float3 cov2d_ewa(float tx, float ty, float tz, const 
 	return r;
 }
 
-// SH (degree D) -> rgb, DGR forward.cu:20-71.  sh points at this Gaussian's [M,3] block.
-__device__ __forceinline__ void sh_to_rgb(int D, const float* __restrict__ sh, float dx, float dy, float dz,
+// SH (degree D) -> rgb, DGR forward.cu:20-71.  sh holds this Gaussian's coefficients (registers: every index below is a
+// compile-time constant), loaded up front by sh_load.
+__device__ __forceinline__ void sh_to_rgb(int D, const float (&sh)[48], float dx, float dy, float dz,
 	float* rgb)
 {
 	const float len = fsqrt(ffma(dz, dz, ffma(dx, dx, fmul(dy, dy))));
 	const float x = fdiv(dx, len), y = fdiv(dy, len), z = fdiv(dz, len);
 #pragma unroll
 	for (int c = 0; c < 3; c++)
-		rgb[c] = fmul(__ldg(sh + c), MOSS_SH_C0);
+		rgb[c] = fmul(sh[c], MOSS_SH_C0);
 	if (D > 0) {
 		const float a1 = fmul(y, MOSS_SH_C1), a2 = fmul(z, MOSS_SH_C1), a3 = fmul(x, MOSS_SH_C1);
 #pragma unroll
 		for (int c = 0; c < 3; c++) {
-			float r = ffma(-a1, __ldg(sh + 3 + c), rgb[c]);
-			r = ffma(a2, __ldg(sh + 6 + c), r);
-			rgb[c] = ffma(-a3, __ldg(sh + 9 + c), r);
+			float r = ffma(-a1, sh[3 + c], rgb[c]);
+			r = ffma(a2, sh[6 + c], r);
+			rgb[c] = ffma(-a3, sh[9 + c], r);
 		}
 		if (D > 1) {
 			const float xx = fmul(x, x), yy = fmul(y, y), zz = fmul(z, z);
@@ -135,11 +136,11 @@ __device__ __forceinline__ void sh_to_rgb(int D, const float* __restrict__ sh, f
 			const float b8 = fmul(xx_yy, MOSS_SH_C2_4);
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
-				float r = ffma(b4, __ldg(sh + 12 + c), rgb[c]);
-				r = ffma(b5, __ldg(sh + 15 + c), r);
-				r = ffma(b6, __ldg(sh + 18 + c), r);
-				r = ffma(b7, __ldg(sh + 21 + c), r);
-				rgb[c] = ffma(b8, __ldg(sh + 24 + c), r);
+				float r = ffma(b4, sh[12 + c], rgb[c]);
+				r = ffma(b5, sh[15 + c], r);
+				r = ffma(b6, sh[18 + c], r);
+				r = ffma(b7, sh[21 + c], r);
+				rgb[c] = ffma(b8, sh[24 + c], r);
 			}
 			if (D > 2) {
 				// fused forms as in the reference's SASS: 3xx-yy = fma(xx,3,-yy); 4zz-xx-yy = fma(zz,4,-xx)-yy;
@@ -154,13 +155,13 @@ __device__ __forceinline__ void sh_to_rgb(int D, const float* __restrict__ sh, f
 				const float c15 = fmul(fmul(x, MOSS_SH_C3_6), ffma(yy, -3.f, xx));
 #pragma unroll
 				for (int c = 0; c < 3; c++) {
-					float r = ffma(c9, __ldg(sh + 27 + c), rgb[c]);
-					r = ffma(c10, __ldg(sh + 30 + c), r);
-					r = ffma(c11, __ldg(sh + 33 + c), r);
-					r = ffma(c12, __ldg(sh + 36 + c), r);
-					r = ffma(c13, __ldg(sh + 39 + c), r);
-					r = ffma(c14, __ldg(sh + 42 + c), r);
-					rgb[c] = ffma(c15, __ldg(sh + 45 + c), r);
+					float r = ffma(c9, sh[27 + c], rgb[c]);
+					r = ffma(c10, sh[30 + c], r);
+					r = ffma(c11, sh[33 + c], r);
+					r = ffma(c12, sh[36 + c], r);
+					r = ffma(c13, sh[39 + c], r);
+					r = ffma(c14, sh[42 + c], r);
+					rgb[c] = ffma(c15, sh[45 + c], r);
 				}
 			}
 		}
@@ -168,6 +169,27 @@ __device__ __forceinline__ void sh_to_rgb(int D, const float* __restrict__ sh, f
 #pragma unroll
 	for (int c = 0; c < 3; c++)
 		rgb[c] = fadd(rgb[c], 0.5f);
+}
+
+// The 3(D+1)^2 coefficients of one Gaussian as 16 B vector loads (the [M,3] block is 192 B for M = 16): 12 load
+// instructions per thread instead of 48 scalar ones -- every lane touches its own sectors, so the LSU cost is per
+// instruction.  Unaligned views fall back to scalar loads.
+__device__ __forceinline__ void sh_load(int D, int M, const float* __restrict__ row, bool vec_ok, float (&sh)[48])
+{
+	const int nfl = 3 * (D + 1) * (D + 1);
+	if (vec_ok) {
+		const float4* r4 = reinterpret_cast<const float4*>(row);
+		const int nvec = (nfl + 3) >> 2;      // never past the row: 3M floats with 3M % 4 == 0 and nfl <= 3M
+#pragma unroll
+		for (int k = 0; k < 12; k++) {
+			float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+			if (k < nvec) v = __ldg(r4 + k);
+			sh[4 * k] = v.x; sh[4 * k + 1] = v.y; sh[4 * k + 2] = v.z; sh[4 * k + 3] = v.w;
+		}
+	} else {
+#pragma unroll
+		for (int k = 0; k < 48; k++) sh[k] = k < nfl ? __ldg(row + k) : 0.f;
+	}
 }
 
 // ndc -> pixel, evaluated in fp64 like the reference (DGR auxiliary.h:41-44).
@@ -185,20 +207,45 @@ preprocess_forward_kernel(int P, ViewParams vp,
 	const float* __restrict__ cov3D_precomp, int prefiltered,
 	GeomWS g, uint32_t* __restrict__ tile_count, int* __restrict__ radii)
 {
+	// Every global read of the Gaussian is issued here, before the first data-dependent branch, so the kernel pays
+	// ONE DRAM round trip instead of a chain of four (position -> covariance -> SH -> opacity); with a cold L2 and
+	// one block per SM that chain was most of the launch's duration.  Culled Gaussians read a little more than needed.
+	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
+	const bool active = idx < P;
+	const int li = active ? idx : 0;
+	const float px = means3D[3 * li], py = means3D[3 * li + 1], pz = means3D[3 * li + 2];
+	const float opac = opacities[li];
+	float c3[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+	float4 quat = make_float4(0.f, 0.f, 0.f, 0.f);
+	float sc3[3] = {0.f, 0.f, 0.f};
+	if (cov3D_precomp != nullptr) {
+#pragma unroll
+		for (int k = 0; k < 6; k++) c3[k] = cov3D_precomp[6 * li + k];
+	} else {
+		quat = reinterpret_cast<const float4*>(rotations)[li];
+		sc3[0] = scales[3 * li]; sc3[1] = scales[3 * li + 1]; sc3[2] = scales[3 * li + 2];
+	}
+	float shl[48];
+	float rgb_in[3] = {0.f, 0.f, 0.f};
+	if (colors_precomp == nullptr) {
+		const bool vec_ok = ((reinterpret_cast<uintptr_t>(shs) & 15) == 0) && ((3 * vp.M) % 4 == 0);
+		sh_load(vp.D, vp.M, shs + (size_t)li * vp.M * 3, vec_ok, shl);
+	} else {
+#pragma unroll
+		for (int c = 0; c < 3; c++) rgb_in[c] = colors_precomp[3 * li + c];
+	}
+
 	__shared__ float s_view[16], s_proj[16], s_cam[3];
 	if (threadIdx.x < 16) s_view[threadIdx.x] = vp.view[threadIdx.x];
 	else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
 	else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
 	__syncthreads();
-
-	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
-	if (idx >= P) return;
+	if (!active) return;
 #pragma unroll
-	for (int k = 0; k < 3; k++) g.grad_acc[3 * (size_t)idx + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+	for (int k = 0; k < GRAD_ACC_VEC; k++) g.grad_acc[GRAD_ACC_VEC * (size_t)idx + k] = make_float4(0.f, 0.f, 0.f, 0.f);
 
 	int my_radius = 0;
 	uint32_t touched = 0;
-	const float px = means3D[3 * idx], py = means3D[3 * idx + 1], pz = means3D[3 * idx + 2];
 	const float vz = affine_row(px, py, pz, s_view[2], s_view[6], s_view[10], s_view[14]);
 
 	do {
@@ -215,14 +262,8 @@ preprocess_forward_kernel(int P, ViewParams vp,
 		const float p_w = frcp(fadd(hw, 0.0000001f));
 		const float ndc_x = fmul(hx, p_w), ndc_y = fmul(hy, p_w);
 
-		float c3[6];
-		if (cov3D_precomp != nullptr) {
-#pragma unroll
-			for (int k = 0; k < 6; k++) c3[k] = cov3D_precomp[6 * idx + k];
-		} else {
-			const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
-			cov3d_from_scale_rot(scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2], vp.scale_modifier,
-				q.x, q.y, q.z, q.w, c3);
+		if (cov3D_precomp == nullptr) {
+			cov3d_from_scale_rot(sc3[0], sc3[1], sc3[2], vp.scale_modifier, quat.x, quat.y, quat.z, quat.w, c3);
 #pragma unroll
 			for (int k = 0; k < 6; k++) g.cov3D[6 * idx + k] = c3[k];
 		}
@@ -256,28 +297,29 @@ preprocess_forward_kernel(int P, ViewParams vp,
 		float rgb[3];
 		uint8_t clamp_bits = 0;
 		if (colors_precomp == nullptr) {
-			sh_to_rgb(vp.D, shs + (size_t)idx * vp.M * 3, fsub(px, s_cam[0]), fsub(py, s_cam[1]), fsub(pz, s_cam[2]), rgb);
+			sh_to_rgb(vp.D, shl, fsub(px, s_cam[0]), fsub(py, s_cam[1]), fsub(pz, s_cam[2]), rgb);
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
 				if (rgb[c] < 0.f) { clamp_bits |= (1u << c); rgb[c] = 0.f; }
 			}
 		} else {
 #pragma unroll
-			for (int c = 0; c < 3; c++) rgb[c] = colors_precomp[3 * idx + c];
+			for (int c = 0; c < 3; c++) rgb[c] = rgb_in[c];
 		}
 
 		g.depths[idx] = vz;
 		g.means2D[idx] = make_float2(pix_x, pix_y);
-		g.conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, opacities[idx]);
+		g.conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, opac);
 		g.feat[idx] = make_float4(rgb[0], rgb[1], rgb[2], vz);
 		g.clamped[idx] = clamp_bits;
 		g.rect[idx] = make_ushort4((unsigned short)rminx, (unsigned short)rminy, (unsigned short)rmaxx, (unsigned short)rmaxy);
 		my_radius = ri;
 		touched = area;
 		// bin: one counter per tile (replaces the per-Gaussian scan + key duplication + global sort)
+		const uint32_t sub = ((uint32_t)idx >> 5) & (TILE_SUB - 1);      // one sub-counter per counting warp
 		for (uint32_t y = rminy; y < rmaxy; y++)
 			for (uint32_t x = rminx; x < rmaxx; x++)
-				atomicAdd(&tile_count[y * gx + x], 1u);
+				atomicAdd(&tile_count[(y * gx + x) * TILE_SUB + sub], 1u);
 	} while (false);
 
 	radii[idx] = my_radius;

@@ -17,35 +17,73 @@ preprocess_backward_kernel(int P, ViewParams vp,
 	GeomWS g,
 	float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dcolor,
 	float* __restrict__ dL_dopacity, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-	float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
+	float* __restrict__ dL_dscale, float* __restrict__ dL_drot, int deterministic, const uint32_t* __restrict__ counters)
 {
+	// All global reads of the Gaussian are issued before the first data-dependent branch (one DRAM round trip instead
+	// of a chain; see preprocess_forward_kernel).
+	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
+	const bool active = idx < P;
+	const int li = active ? idx : 0;
+	const int M = vp.M, D = vp.D;
+	const int radius = radii[li];
+	float4 acc0, acc1;
+	float acc2;
+	if (!deterministic) {
+		acc0 = g.grad_acc[GRAD_ACC_VEC * (size_t)li]; acc1 = g.grad_acc[GRAD_ACC_VEC * (size_t)li + 1];
+		acc2 = g.grad_acc[GRAD_ACC_VEC * (size_t)li + 2].x;
+	} else {
+		// nine int64 fixed-point sums (blend.cuh) -> float
+		const float inv = det_scale_from_bits(counters[6], true);
+		const long long* a = reinterpret_cast<const long long*>(g.grad_acc + GRAD_ACC_VEC * (size_t)li);
+		acc0 = make_float4((float)a[0] * inv, (float)a[1] * inv, (float)a[2] * inv, (float)a[3] * inv);
+		acc1 = make_float4((float)a[4] * inv, (float)a[5] * inv, (float)a[6] * inv, (float)a[7] * inv);
+		acc2 = (float)a[8] * inv;
+	}
+	const float mx = means3D[3 * li], my = means3D[3 * li + 1], mz = means3D[3 * li + 2];
+	const float* c3 = cov3D_precomp ? (cov3D_precomp + 6 * (size_t)li) : (g.cov3D + 6 * (size_t)li);
+	const float V0 = c3[0], V1 = c3[1], V2 = c3[2], V3 = c3[3], V4 = c3[4], V5 = c3[5];
+	const uint8_t cl = g.clamped[li];
+	const bool sh_vec = shs && ((reinterpret_cast<uintptr_t>(shs) & 15) == 0) && ((3 * M) % 4 == 0);
+	const bool dsh_vec = shs && M == 16 && ((reinterpret_cast<uintptr_t>(dL_dsh) & 15) == 0);
+	float sh[48];
+	if (shs) sh_load(D, M, shs + (size_t)li * 3 * M, sh_vec, sh);
+	float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+	float sc_in[3] = {0.f, 0.f, 0.f};
+	if (scales) {
+		q = reinterpret_cast<const float4*>(rotations)[li];
+		sc_in[0] = scales[3 * li]; sc_in[1] = scales[3 * li + 1]; sc_in[2] = scales[3 * li + 2];
+	}
+
 	__shared__ float v[16], pr[16], s_cam[3];
 	if (threadIdx.x < 16) v[threadIdx.x] = vp.view[threadIdx.x];
 	else if (threadIdx.x < 32) pr[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
 	else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
 	__syncthreads();
-
-	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
-	if (idx >= P) return;
-	const int M = vp.M, D = vp.D;
+	if (!active) return;
 
 	// The blend backward accumulated into g.grad_acc (vector atomics); unpack it into the caller's tensors, which are
 	// therefore fully written here (no zero-fill beforehand), and leave the accumulators zero for the next backward.
-	const float4 acc0 = g.grad_acc[3 * (size_t)idx], acc1 = g.grad_acc[3 * (size_t)idx + 1];
-	const float acc2 = g.grad_acc[3 * (size_t)idx + 2].x;
 #pragma unroll
-	for (int k = 0; k < 3; k++) g.grad_acc[3 * (size_t)idx + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+	for (int k = 0; k < GRAD_ACC_VEC; k++) g.grad_acc[GRAD_ACC_VEC * (size_t)idx + k] = make_float4(0.f, 0.f, 0.f, 0.f);
 	dL_dcolor[3 * idx] = acc0.x; dL_dcolor[3 * idx + 1] = acc0.y; dL_dcolor[3 * idx + 2] = acc0.z;
 	dL_dopacity[idx] = acc0.w;
 	dL_dmean2D[3 * idx] = acc1.x; dL_dmean2D[3 * idx + 1] = acc1.y; dL_dmean2D[3 * idx + 2] = 0.f;
 	dL_dconic[4 * idx] = acc1.z; dL_dconic[4 * idx + 1] = acc1.w; dL_dconic[4 * idx + 2] = 0.f; dL_dconic[4 * idx + 3] = acc2;
 
-	if (!(radii[idx] > 0)) {
+	if (!(radius > 0)) {
 #pragma unroll
 		for (int k = 0; k < 3; k++) dL_dmean3D[3 * idx + k] = 0.f;
 #pragma unroll
 		for (int k = 0; k < 6; k++) dL_dcov3D[6 * idx + k] = 0.f;
-		if (shs) for (int k = 0; k < 3 * M; k++) dL_dsh[(size_t)idx * 3 * M + k] = 0.f;
+		if (shs) {
+			if (dsh_vec) {
+				float4* d4 = reinterpret_cast<float4*>(dL_dsh + (size_t)idx * 48);
+#pragma unroll
+				for (int k = 0; k < 12; k++) d4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+			} else {
+				for (int k = 0; k < 3 * M; k++) dL_dsh[(size_t)idx * 3 * M + k] = 0.f;
+			}
+		}
 		if (scales) {
 #pragma unroll
 			for (int k = 0; k < 3; k++) dL_dscale[3 * idx + k] = 0.f;
@@ -53,10 +91,6 @@ preprocess_backward_kernel(int P, ViewParams vp,
 		}
 		return;
 	}
-
-	const float mx = means3D[3 * idx], my = means3D[3 * idx + 1], mz = means3D[3 * idx + 2];
-	const float* c3 = cov3D_precomp ? (cov3D_precomp + 6 * idx) : (g.cov3D + 6 * idx);
-	const float V0 = c3[0], V1 = c3[1], V2 = c3[2], V3 = c3[3], V4 = c3[4], V5 = c3[5];
 
 	// ---- conic -> cov2D -> cov3D and mean (through J) ----------------------------------------------
 	const float dcx = acc1.z, dcy = acc1.w, dcz = acc2;
@@ -137,12 +171,10 @@ preprocess_backward_kernel(int P, ViewParams vp,
 
 	// ---- colour -> SH coefficients and view direction -> mean ---------------------------------------
 	if (shs) {
-		const float* sh = shs + (size_t)idx * 3 * M;
 		float* dsh = dL_dsh + (size_t)idx * 3 * M;
 		const float ox = mx - s_cam[0], oy = my - s_cam[1], oz = mz - s_cam[2];
 		const float ilen = 1.f / sqrtf(ox * ox + oy * oy + oz * oz);
 		const float x = ox * ilen, y = oy * ilen, z = oz * ilen;
-		const uint8_t cl = g.clamped[idx];
 		float dRGB[3];
 #pragma unroll
 		for (int ch = 0; ch < 3; ch++) dRGB[ch] = ((cl >> ch) & 1) ? 0.f : (ch == 0 ? acc0.x : (ch == 1 ? acc0.y : acc0.z));
@@ -198,14 +230,27 @@ preprocess_backward_kernel(int P, ViewParams vp,
 			}
 		}
 		const int ncoef = (D + 1) * (D + 1);
+		if (dsh_vec) {
+			// the 192 B row as 12 vector stores (48 scalar stores cost 4x the LSU time: every lane owns its sectors)
+			float o[48];
 #pragma unroll
-		for (int k = 0; k < 16; k++) {
-			if (k < M) {
+			for (int k = 0; k < 16; k++) {
 				const float bk = (k < ncoef) ? basis[k] : 0.f;
-				dsh[3 * k] = bk * dRGB[0]; dsh[3 * k + 1] = bk * dRGB[1]; dsh[3 * k + 2] = bk * dRGB[2];
+				o[3 * k] = bk * dRGB[0]; o[3 * k + 1] = bk * dRGB[1]; o[3 * k + 2] = bk * dRGB[2];
 			}
+			float4* d4 = reinterpret_cast<float4*>(dsh);
+#pragma unroll
+			for (int k = 0; k < 12; k++) d4[k] = make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+		} else {
+#pragma unroll
+			for (int k = 0; k < 16; k++) {
+				if (k < M) {
+					const float bk = (k < ncoef) ? basis[k] : 0.f;
+					dsh[3 * k] = bk * dRGB[0]; dsh[3 * k + 1] = bk * dRGB[1]; dsh[3 * k + 2] = bk * dRGB[2];
+				}
+			}
+			for (int k = 16; k < M; k++) { dsh[3 * k] = 0.f; dsh[3 * k + 1] = 0.f; dsh[3 * k + 2] = 0.f; }
 		}
-		for (int k = 16; k < M; k++) { dsh[3 * k] = 0.f; dsh[3 * k + 1] = 0.f; dsh[3 * k + 2] = 0.f; }
 
 		const float ddx = dx3[0] * dRGB[0] + dx3[1] * dRGB[1] + dx3[2] * dRGB[2];
 		const float ddy = dy3[0] * dRGB[0] + dy3[1] * dRGB[1] + dy3[2] * dRGB[2];
@@ -221,10 +266,8 @@ preprocess_backward_kernel(int P, ViewParams vp,
 
 	// ---- cov3D -> scale, (un-normalised) quaternion --------------------------------------------------
 	if (scales) {
-		const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
 		const float r = q.x, x = q.y, y = q.z, z = q.w;
-		const float s[3] = {vp.scale_modifier * scales[3 * idx], vp.scale_modifier * scales[3 * idx + 1],
-			vp.scale_modifier * scales[3 * idx + 2]};
+		const float s[3] = {vp.scale_modifier * sc_in[0], vp.scale_modifier * sc_in[1], vp.scale_modifier * sc_in[2]};
 		// R[i][j]: column i, row j (GLM listing of DGR backward.cu:288-292)
 		const float R[3][3] = {
 			{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
