@@ -131,14 +131,36 @@ def run_ours(args, rank, world, dev):
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)   # > 126 MB L2
 
     state = {}
+    # N > 1: the packed parameter gradient is all-reduced by the library's own kernel over NVLink peer memory (the
+    # backward writes straight into the symmetric buffer); NCCL only if symmetric memory cannot be set up here
+    peer, collective_kind = None, "none"
+    if world > 1:
+        from moss_b200.rasterizer import grad_layout
+        total = grad_layout(P, 16 if d["shs"] is not None else 0, d["shs"] is not None, d["scales"] is not None)[3]
+        ok = torch.ones(1, device=dev)
+        if os.environ.get("MOSS_COLLECTIVE", "peer") == "peer":
+            try:
+                peer = parallel.PeerGradBuffer(total, dev)
+            except RuntimeError as e:
+                print(f"[rank {rank}] peer all-reduce unavailable, using NCCL: {e}", file=sys.stderr)
+                ok.zero_()
+        else:
+            ok.zero_()
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)          # all ranks or none
+        if float(ok) == 0.0:
+            peer = None
+        collective_kind = "peer-memory kernel (moss_peer_allreduce)" if peer is not None else "nccl all_reduce"
 
     def step(i, collective=True):
         rs = settings[i % len(settings)]
         color, radii, depth, alpha, st = M.forward_raw(devt["means3D"], devt["shs"], devt["colors_precomp"], devt["opacities"],
                                                        devt["scales"], devt["rotations"], devt["cov3D_precomp"], rs)
-        M.backward_raw(st, radii, gc, gd, ga)
+        M.backward_raw(st, radii, gc, gd, ga, out=peer.tensor if peer is not None else None)
         if world > 1 and collective:
-            parallel.allreduce_param_grads(st.grad_buf, st.param_grad_numel)
+            if peer is not None:
+                peer.allreduce(st.param_grad_numel)
+            else:
+                parallel.allreduce_param_grads(st.grad_buf, st.param_grad_numel)
         state["st"], state["radii"] = st, radii
         return st
 
@@ -236,6 +258,8 @@ def run_ours(args, rank, world, dev):
     d2h = sum(v.numel() * v.element_size() for v in out_host.values())
 
     stop.set()
+    if peer is not None:
+        peer.check()
     st = state["st"]
     R = int(M.export_state(st, "counters")[0])
     V = int((state["radii"] > 0).sum())
@@ -278,7 +302,7 @@ def run_ours(args, rank, world, dev):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOADS[args.workload]["desc"], "gaussians": P, "visible": V, "instances": R,
                    "image": [W, H], "views_per_step": world, "l2": "flushed between steps (256 MiB fill, outside the timed events)",
-                   "parallelism": f"dp{world} (views sharded, packed parameter gradient all-reduced)" if world > 1 else "single GPU"},
+                   "parallelism": f"dp{world} (views sharded, packed parameter gradient all-reduced: {collective_kind})" if world > 1 else "single GPU"},
         "e2e": {"value": round(mpix / (e2e_ms_step * 1e-3), 2), "unit": "Mpix/s", "ms_per_step": round(e2e_ms_step, 5),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps, "device_mallocs": e2e_mallocs},
         "gpu_launches": int(launches_timed),

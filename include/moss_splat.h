@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MOSS_ABI_VERSION 4
+#define MOSS_ABI_VERSION 5
 
 /* status codes */
 #define MOSS_OK                  0
@@ -158,6 +158,19 @@ int moss_skin_backward(void* stream, const MossSkin* skin, const float* g_means3
                        float* d_A_tgt, float* d_poseoff_tgt);
 size_t moss_sizeof_skin(void);
 
+/* Data-parallel exchange step (no reference counterpart: MOSS trains on one GPU).  Sum, in
+ * place and on every rank, `numel` floats starting `offset_floats` (multiple of 4) into a SYMMETRIC buffer: the same
+ * allocation made on each of `world` (<= 8) GPUs of one node and mapped into every process (CUDA IPC / fabric handles,
+ * e.g. torch.distributed._symmetric_memory).  buffer_ptrs_dev[p] / signal_ptrs_dev[p] are DEVICE arrays holding rank
+ * p's buffer and zero-initialised signal pad (>= moss_peer_signal_bytes(world)) as mapped in the calling process.
+ * One kernel per rank: flag barrier, two-shot all-reduce with loads/stores on the peer pointers (rank order, so the
+ * result is bit-identical on every rank and from run to run), flag barrier.  Every rank must call it with the same
+ * numel/offset and the same, strictly increasing, non-zero `epoch`.  *error_word_dev (device uint32, zeroed by the
+ * caller once) becomes non-zero if a peer did not arrive within ~10 s. */
+size_t moss_peer_signal_bytes(int world);
+int moss_peer_allreduce(void* stream, int rank, int world, void* const* buffer_ptrs_dev, void* const* signal_ptrs_dev,
+                        size_t offset_floats, size_t numel, unsigned epoch, unsigned* error_word_dev);
+
 /* Internal-state export for parity tests (the reference needs a C++ shim over fromChunk for this,
  * DGR/cuda_rasterizer/rasterizer_impl.cu:155-194).  Copies one state array into `dst` (device) on
  * `stream`; returns the byte count or a negative MOSS_ERR_*. */
@@ -192,7 +205,8 @@ long long moss_export_state(void* stream, const MossScene* scene, int which, voi
 #define MOSS_STAGE_TILE_SORT       7
 #define MOSS_STAGE_SKIN            8
 #define MOSS_STAGE_SKIN_BWD        9
-#define MOSS_STAGE_COUNT           10
+#define MOSS_STAGE_PEER_REDUCE     10
+#define MOSS_STAGE_COUNT           11
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

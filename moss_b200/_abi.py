@@ -34,9 +34,9 @@ SYMBOLS = [
     "moss_rasterize_backward", "moss_mark_visible", "moss_export_state", "moss_abi_version",
     "moss_error_string", "moss_last_cuda_error", "moss_sizeof_scene", "moss_kernel_launches",
     "moss_profile_enable", "moss_profile_read", "moss_stage_name",
-    "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin",
+    "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_peer_signal_bytes", "moss_peer_allreduce",
 ]
-STAGE_COUNT = 10
+STAGE_COUNT = 11
 
 
 class MossScene(C.Structure):
@@ -114,6 +114,10 @@ def load():
     lib.moss_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
     lib.moss_stage_name.restype = C.c_char_p
     lib.moss_stage_name.argtypes = [C.c_int]
+    lib.moss_peer_signal_bytes.restype = C.c_size_t
+    lib.moss_peer_signal_bytes.argtypes = [C.c_int]
+    lib.moss_peer_allreduce.restype = C.c_int
+    lib.moss_peer_allreduce.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_size_t, C.c_size_t, C.c_uint, vp]
     lib.moss_sizeof_skin.restype = C.c_size_t
     lib.moss_skin_forward.restype = C.c_int
     lib.moss_skin_forward.argtypes = [vp, C.POINTER(MossSkin)] + [vp] * 5

@@ -19,6 +19,7 @@
 #include "binning.cuh"
 #include "blend.cuh"
 #include "skin.cuh"
+#include "peer_reduce.cuh"
 
 using namespace moss;
 
@@ -198,7 +199,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -532,6 +533,26 @@ int moss_skin_backward(void* stream_, const MossSkin* k, const float* g_means3D,
 	{ MOSS_STAGE(MOSS_STAGE_SKIN_BWD, stream);
 		skin_backward_kernel<<<(k->P + SKIN_THREADS - 1) / SKIN_THREADS, SKIN_THREADS, 0, stream>>>(
 			make_skin(k), g_means3D, g_cov3D, d_xyz, d_scaling, d_rotation, d_lbs_delta, d_A_tgt, d_poseoff_tgt); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+// ---- packed-gradient all-reduce over mapped peer memory -------------------------------------------------------
+size_t moss_peer_signal_bytes(int world) { return sizeof(uint32_t) * 2 * PEER_MAX_BLOCKS * (size_t)(world > 0 ? world : 1); }
+
+int moss_peer_allreduce(void* stream_, int rank, int world, void* const* buffer_ptrs_dev, void* const* signal_ptrs_dev,
+	size_t offset_floats, size_t numel, unsigned epoch, unsigned* error_word_dev)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || !buffer_ptrs_dev || !signal_ptrs_dev ||
+		!error_word_dev || epoch == 0 || (offset_floats & 3)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (numel == 0) return MOSS_OK;
+	const size_t per = (numel / 4 + world - 1) / world;
+	int blocks = (int)((per + PEER_THREADS - 1) / PEER_THREADS);
+	blocks = blocks < 1 ? 1 : (blocks > PEER_MAX_BLOCKS ? PEER_MAX_BLOCKS : blocks);
+	{ MOSS_STAGE(MOSS_STAGE_PEER_REDUCE, stream);
+	peer_allreduce_kernel<<<blocks, PEER_THREADS, 0, stream>>>((float* const*)buffer_ptrs_dev, (uint32_t* const*)signal_ptrs_dev,
+		rank, world, offset_floats, numel, epoch, error_word_dev); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }

@@ -1,0 +1,95 @@
+// Packed-gradient all-reduce over NVLink peer memory: the one exchange step of the
+// data-parallel path.  Every rank's backward writes its packed parameter gradient into a SYMMETRIC buffer (same
+// allocation on every GPU, all of them mapped into every process); this kernel then does a two-shot all-reduce with
+// plain loads/stores on the mapped peer pointers:
+//   barrier  -> every peer's gradient is complete (its backward precedes this kernel in stream order)
+//   reduce   -> rank r sums slice r of all `world` buffers in rank order (deterministic) and stores the result into
+//               slice r of EVERY buffer; slice r is read by rank r only, so no buffer is written while it is read
+//   barrier  -> every slice of the local buffer has arrived
+// 4.9 MB at ZJU shape: (world-1)/world of it crosses NVLink once in each direction, versus NCCL's ~50-70 us launch +
+// protocol latency at this size, which is a third of the 0.2 ms step.
+// Flags live in the peers' signal pads: slot ((phase * PEER_MAX_BLOCKS + block) * world + writer), value = the call's
+// epoch (monotonic, never reset).  Spins give up after ~10 s and raise the error word instead of hanging the GPU.
+#pragma once
+#include "common.cuh"
+
+namespace moss {
+
+constexpr int PEER_MAX_BLOCKS = 32;
+constexpr int PEER_MAX_WORLD = 8;
+constexpr int PEER_THREADS = 512;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v)
+{
+	asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p)
+{
+	uint32_t v;
+	asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float4* p)
+{
+	float4 v;
+	asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_peer_f4(float4* p, float4 v)
+{
+	asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// One flag exchange between block b of this rank and block b of every peer.
+__device__ __forceinline__ void peer_barrier(uint32_t* const* pads, int rank, int world, int phase, uint32_t epoch, uint32_t* err)
+{
+	__syncthreads();
+	if ((int)threadIdx.x < world) {
+		const int p = (int)threadIdx.x;
+		const size_t slot = (size_t)(phase * PEER_MAX_BLOCKS + (int)blockIdx.x) * world;
+		__threadfence_system();
+		st_release_sys(pads[p] + slot + rank, epoch);
+		const uint32_t* mine = pads[rank] + slot + p;
+		const long long t0 = clock64();
+		while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+			if (clock64() - t0 > 20000000000ll) { atomicExch(err, 1u); break; }    // ~10 s at 2 GHz: a peer died
+		}
+	}
+	__syncthreads();
+}
+
+__global__ void __launch_bounds__(PEER_THREADS)
+peer_allreduce_kernel(float* const* bufs, uint32_t* const* pads, int rank, int world, size_t offset, size_t numel,
+	uint32_t epoch, uint32_t* err)
+{
+	__shared__ float* s_buf[PEER_MAX_WORLD];
+	if ((int)threadIdx.x < world) s_buf[threadIdx.x] = bufs[threadIdx.x] + offset;
+	peer_barrier(pads, rank, world, 0, epoch, err);
+
+	const size_t n4 = numel / 4;
+	const size_t per = (n4 + world - 1) / world;                 // float4s per rank slice
+	const size_t lo = min(n4, per * rank), hi = min(n4, lo + per);
+	for (size_t i = lo + (size_t)blockIdx.x * PEER_THREADS + threadIdx.x; i < hi; i += (size_t)gridDim.x * PEER_THREADS) {
+		float4 v[PEER_MAX_WORLD];
+#pragma unroll
+		for (int p = 0; p < PEER_MAX_WORLD; p++)
+			if (p < world) v[p] = ld_peer_f4(reinterpret_cast<const float4*>(s_buf[p]) + i);
+		float4 s = v[0];
+#pragma unroll
+		for (int p = 1; p < PEER_MAX_WORLD; p++)
+			if (p < world) { s.x += v[p].x; s.y += v[p].y; s.z += v[p].z; s.w += v[p].w; }
+#pragma unroll
+		for (int p = 0; p < PEER_MAX_WORLD; p++)
+			if (p < world) st_peer_f4(reinterpret_cast<float4*>(s_buf[p]) + i, s);
+	}
+	// scalar tail (numel % 4) by the last rank
+	if (rank == world - 1 && blockIdx.x == 0 && threadIdx.x < (numel & 3)) {
+		const size_t i = n4 * 4 + threadIdx.x;
+		float s = 0.f;
+		for (int p = 0; p < world; p++) s += *((volatile float*)(s_buf[p] + i));
+		for (int p = 0; p < world; p++) *((volatile float*)(s_buf[p] + i)) = s;
+	}
+	peer_barrier(pads, rank, world, 1, epoch, err);
+}
+
+} // namespace moss

@@ -52,3 +52,57 @@ def allreduce_densification_stats(radii, max_radii2D, viewspace_grad_norm, xyz_g
     max_radii2D.copy_(local_max)
     xyz_gradient_accum.add_(add)
     denom.add_(cnt)
+
+
+class PeerGradBuffer:
+    """Symmetric (peer-mapped) packed-gradient buffer + the library's own all-reduce kernel over NVLink peer memory
+    (include/moss_splat.h: moss_peer_allreduce).  Pass ``.tensor`` as ``out=`` to ``rasterizer.backward_raw`` so the
+    backward writes the gradients straight into the mapped buffer, then call ``allreduce(param_grad_numel)``.
+
+    The allocation and the exchange of the IPC handles are plumbing (torch.distributed._symmetric_memory); the data
+    path is this repo's kernel.  Raises RuntimeError when symmetric memory cannot be set up on this machine -- callers
+    that want a library collective instead use ``allreduce_param_grads`` (NCCL)."""
+
+    def __init__(self, numel, device, group=None):
+        import ctypes as C
+        from . import _abi
+        import torch.distributed._symmetric_memory as symm
+        if not dist.is_initialized():
+            raise RuntimeError("PeerGradBuffer needs an initialised process group")
+        self._lib = _abi.load()
+        self._C = C
+        group = group if group is not None else dist.group.WORLD
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if self.world > 8:
+            raise RuntimeError("peer all-reduce supports up to 8 ranks of one node")
+        numel = (int(numel) + 3) // 4 * 4
+        try:
+            self.tensor = symm.empty(numel, dtype=torch.float32, device=device)
+            self.handle = symm.rendezvous(self.tensor, group)
+        except Exception as e:       # no IPC / fabric support on this box
+            raise RuntimeError(f"symmetric memory unavailable: {e}") from e
+        need = self._lib.moss_peer_signal_bytes(self.world)
+        if int(self.handle.signal_pad_size) < need:
+            raise RuntimeError(f"signal pad too small ({self.handle.signal_pad_size} < {need})")
+        self.error = torch.zeros(1, dtype=torch.int32, device=device)
+        self.epoch = 0
+        self.device = device
+        # everyone's pad is zero and mapped before the first kernel spins on it
+        self.tensor.zero_()
+        torch.cuda.synchronize(device)
+        dist.barrier(group)
+
+    def allreduce(self, numel, offset=0):
+        """Sum tensor[offset:offset+numel] over all ranks, in place, on the current stream (no host sync)."""
+        self.epoch += 1
+        st = self._lib.moss_peer_allreduce(torch.cuda.current_stream(self.device).cuda_stream, self.rank, self.world,
+                                           int(self.handle.buffer_ptrs_dev), int(self.handle.signal_pad_ptrs_dev),
+                                           int(offset), int(numel), self.epoch, self.error.data_ptr())
+        from . import _abi
+        _abi.check(st, "moss_peer_allreduce")
+        return self.tensor
+
+    def check(self):
+        """Host-side check (synchronises): did any spin time out?"""
+        if int(self.error.item()) != 0:
+            raise RuntimeError("moss_peer_allreduce: a peer did not arrive (timeout)")
