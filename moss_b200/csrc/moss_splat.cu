@@ -312,7 +312,15 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 		im.counters, b.keys); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_TILE_SORT, stream);
-	tile_sort_kernel<<<T, TILE_PIX, 0, stream>>>(im, b, ck); }
+	// opt in to > 48 KB of dynamic shared memory (the attribute is per device)
+	static int sort_attr_dev = -1;
+	int cur_dev = 0;
+	cudaGetDevice(&cur_dev);
+	if (cur_dev != sort_attr_dev) {
+		MOSS_CUDA_TRY(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
+		sort_attr_dev = cur_dev;
+	}
+	tile_sort_kernel<<<T, TILE_PIX, sizeof(SortSmem), stream>>>(im, b, ck); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_FWD, stream);
 	const bool cull = !(flags & MOSS_FLAG_NO_CULL);

@@ -39,7 +39,8 @@ __device__ __forceinline__ float4 lds_f4(const void* p)
 	return v;
 }
 
-constexpr int SORT_CAP = 4096;   // instances per tile sorted in shared memory (32 KB)
+constexpr int SORT_CAP = 6144;   // instances per tile sorted in shared memory (48 KB of keys + 12 KB of bucket bytes,
+                                 // dynamic shared memory; side views of the ZJU body reach ~4400 per tile)
 constexpr int NPATCH = TILE_PIX / 32;   // 8 warps = 2 (x) by 4 (y) patches of 8x4 pixels
 
 // Ascending bitonic network over a[0..n) with virtual +inf padding up to the next power of two
@@ -250,7 +251,8 @@ __device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 ra
 __global__ void __launch_bounds__(TILE_PIX)
 tile_sort_kernel(ImageWS im, BinWS b, CkptWS ck)
 {
-	__shared__ SortSmem ss;
+	extern __shared__ __align__(16) unsigned char sort_smem_raw[];
+	SortSmem& ss = *reinterpret_cast<SortSmem*>(sort_smem_raw);
 	__shared__ uint32_t seg_off;
 	if (im.counters[1]) return;   // binning overflow: the host re-runs with a larger buffer
 	if (blockIdx.x >= im.counters[3]) return;                 // only non-empty tiles have work
