@@ -96,8 +96,7 @@ def build_inputs(workload, rank, world):
         cams = [cam0]
     else:
         cams = synth.ring_cameras(23, cam0.image_width, cam0.image_height)
-    my_cams = cams[rank::world] if len(cams) >= world else cams
-    return d, my_cams
+    return d, cams
 
 
 def algorithmic_bytes(P, V, R, N, T, M, D, has_sr):
@@ -151,8 +150,18 @@ def run_ours(args, rank, world, dev):
             peer = None
         collective_kind = "peer-memory kernel (moss_peer_allreduce)" if peer is not None else "nccl all_reduce"
 
+    # Which view does this rank render at step i?  N = 1: the ring in order.  N > 1: a cost-balanced schedule
+    # (parallel.balanced_view_schedule) from a short calibration pass, so that the ranks of one step wait for views of
+    # similar cost; every rank still cycles through all views.
+    sched = None
+
+    def view_of(i):
+        if sched is None:
+            return (i * world + rank) % len(settings)
+        return sched[i % len(sched)][rank]
+
     def step(i, collective=True):
-        rs = settings[i % len(settings)]
+        rs = settings[view_of(i)]
         color, radii, depth, alpha, st = M.forward_raw(devt["means3D"], devt["shs"], devt["colors_precomp"], devt["opacities"],
                                                        devt["scales"], devt["rotations"], devt["cov3D_precomp"], rs)
         M.backward_raw(st, radii, gc, gd, ga, out=peer.tensor if peer is not None else None)
@@ -184,6 +193,24 @@ def run_ours(args, rank, world, dev):
         t1 = time.perf_counter()
         ms = sum(a.elapsed_time(b) for a, b in ev)
         return ms, t0, t1
+
+    if world > 1 and len(settings) > 1:
+        costs = torch.zeros(len(settings), device=dev, dtype=torch.float64)
+        for v in range(len(settings)):
+            rs_v = settings[v]
+            evs = []
+            for rep in range(4):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                _c, _r, _d, _a, _st = M.forward_raw(devt["means3D"], devt["shs"], devt["colors_precomp"], devt["opacities"],
+                                                    devt["scales"], devt["rotations"], devt["cov3D_precomp"], rs_v)
+                M.backward_raw(_st, _r, gc, gd, ga)
+                e1.record()
+                evs.append((e0, e1))
+            torch.cuda.synchronize(dev)
+            costs[v] = min(a.elapsed_time(b) for a, b in evs[1:])
+        dist.all_reduce(costs, op=dist.ReduceOp.MAX)            # same numbers, hence the same schedule, on every rank
+        sched = parallel.balanced_view_schedule(costs.tolist(), world)
 
     # clocks
     samples, stop = [], threading.Event()
@@ -223,7 +250,7 @@ def run_ours(args, rank, world, dev):
     def e2e_step(i):
         t = {k: host[k].to(dev, non_blocking=True).requires_grad_(True) for k in lay_names}
         means2D = torch.zeros_like(t["means3D"], requires_grad=True)
-        color, radii, depth, alpha = rast[i % len(rast)](means3D=t["means3D"], means2D=means2D, shs=t.get("shs"),
+        color, radii, depth, alpha = rast[view_of(i)](means3D=t["means3D"], means2D=means2D, shs=t.get("shs"),
                                                          colors_precomp=t.get("colors_precomp"), opacities=t["opacities"],
                                                          scales=t.get("scales"), rotations=t.get("rotations"),
                                                          cov3D_precomp=t.get("cov3D_precomp"))
@@ -376,7 +403,7 @@ def run_reference(args, rank, world, dev):
 
     def call(t, i):
         means2D = torch.zeros_like(t["means3D"], requires_grad=True)
-        color, radii, depth, alpha = rast[i % len(rast)](means3D=t["means3D"], means2D=means2D, shs=t.get("shs"),
+        color, radii, depth, alpha = rast[(i * world + rank) % len(rast)](means3D=t["means3D"], means2D=means2D, shs=t.get("shs"),
                                                          colors_precomp=t.get("colors_precomp"), opacities=t["opacities"],
                                                          scales=t.get("scales"), rotations=t.get("rotations"),
                                                          cov3D_precomp=t.get("cov3D_precomp"))

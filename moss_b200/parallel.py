@@ -106,3 +106,16 @@ class PeerGradBuffer:
         """Host-side check (synchronises): did any spin time out?"""
         if int(self.error.item()) != 0:
             raise RuntimeError("moss_peer_allreduce: a peer did not arrive (timeout)")
+
+
+def balanced_view_schedule(costs, world):
+    """Cost-balanced data-parallel schedule.  A step ends when its SLOWEST rank has finished (the gradient exchange is
+    a barrier), and the views of one body differ by up to 40 % in cost (edge-on views stack thousands of splats in a
+    few tiles).  So the views rendered in the same step should cost about the same: sort the views by cost and let
+    step s give rank r the view at position (s * world + r) of that order (wrapping around).  Every rank still visits
+    every view.  -> list of steps, each a list of `world` view indices; len = number of views."""
+    n = len(costs)
+    if n == 0 or world <= 0:
+        raise ValueError("need at least one view and one rank")
+    order = sorted(range(n), key=lambda i: (costs[i], i))
+    return [[order[(s * world + r) % n] for r in range(world)] for s in range(n)]

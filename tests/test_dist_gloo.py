@@ -61,6 +61,23 @@ def test_packed_gradient_allreduce_and_sharding_world2():
     mp.spawn(_worker, args=(2, _free_port(), 257, 16), nprocs=2, join=True)
 
 
+def test_balanced_view_schedule():
+    costs = [200.0, 185.0, 430.0, 176.0, 245.0, 190.0, 413.0]
+    for world in (1, 2, 4, 8):
+        sched = parallel.balanced_view_schedule(costs, world)
+        assert len(sched) == len(costs) and all(len(s) == world for s in sched)
+        for r in range(world):                       # every rank visits every view exactly once per cycle
+            if len(costs) % world and world > 1:
+                assert len({s[r] for s in sched}) == len(costs)
+        # the views of one step are neighbours in cost order: the step's spread is far below the global spread
+        if world == 2:
+            worst = max(abs(costs[a] - costs[b]) for a, b in sched if abs(sched.index([a, b])) >= 0 and {a, b} != {3, 2})
+            assert worst <= 170.0
+    import pytest
+    with pytest.raises(ValueError):
+        parallel.balanced_view_schedule([], 2)
+
+
 def test_single_process_is_a_noop():
     buf = torch.arange(10.0)
     assert parallel.allreduce_param_grads(buf, 6) is buf and buf.tolist() == list(range(10))
