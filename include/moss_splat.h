@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MOSS_ABI_VERSION 5
+#define MOSS_ABI_VERSION 6
 
 /* status codes */
 #define MOSS_OK                  0
@@ -162,14 +162,16 @@ size_t moss_sizeof_skin(void);
  * place and on every rank, `numel` floats starting `offset_floats` (multiple of 4) into a SYMMETRIC buffer: the same
  * allocation made on each of `world` (<= 8) GPUs of one node and mapped into every process (CUDA IPC / fabric handles,
  * e.g. torch.distributed._symmetric_memory).  buffer_ptrs_dev[p] / signal_ptrs_dev[p] are DEVICE arrays holding rank
- * p's buffer and zero-initialised signal pad (>= moss_peer_signal_bytes(world)) as mapped in the calling process.
+ * p's buffer and zero-initialised signal pad (signal_pad_bytes each, >= moss_peer_signal_bytes(world); a larger pad
+ * allows more blocks) as mapped in the calling process.
  * One kernel per rank: flag barrier, two-shot all-reduce with loads/stores on the peer pointers (rank order, so the
  * result is bit-identical on every rank and from run to run), flag barrier.  Every rank must call it with the same
  * numel/offset and the same, strictly increasing, non-zero `epoch`.  *error_word_dev (device uint32, zeroed by the
  * caller once) becomes non-zero if a peer did not arrive within ~10 s. */
 size_t moss_peer_signal_bytes(int world);
 int moss_peer_allreduce(void* stream, int rank, int world, void* const* buffer_ptrs_dev, void* const* signal_ptrs_dev,
-                        size_t offset_floats, size_t numel, unsigned epoch, unsigned* error_word_dev);
+                        size_t signal_pad_bytes, size_t offset_floats, size_t numel, unsigned epoch,
+                        unsigned* error_word_dev);
 
 /* Internal-state export for parity tests (the reference needs a C++ shim over fromChunk for this,
  * DGR/cuda_rasterizer/rasterizer_impl.cu:155-194).  Copies one state array into `dst` (device) on

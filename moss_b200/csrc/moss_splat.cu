@@ -546,20 +546,25 @@ int moss_skin_backward(void* stream_, const MossSkin* k, const float* g_means3D,
 }
 
 // ---- packed-gradient all-reduce over mapped peer memory -------------------------------------------------------
-size_t moss_peer_signal_bytes(int world) { return sizeof(uint32_t) * 2 * PEER_MAX_BLOCKS * (size_t)(world > 0 ? world : 1); }
+size_t moss_peer_signal_bytes(int world) { return sizeof(uint32_t) * 2 * 8 * (size_t)(world > 0 ? world : 1); }   // minimum: 8 blocks
 
 int moss_peer_allreduce(void* stream_, int rank, int world, void* const* buffer_ptrs_dev, void* const* signal_ptrs_dev,
-	size_t offset_floats, size_t numel, unsigned epoch, unsigned* error_word_dev)
+	size_t signal_pad_bytes, size_t offset_floats, size_t numel, unsigned epoch, unsigned* error_word_dev)
 {
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || !buffer_ptrs_dev || !signal_ptrs_dev ||
-		!error_word_dev || epoch == 0 || (offset_floats & 3)) return MOSS_ERR_INVALID_ARGUMENT;
+		!error_word_dev || epoch == 0 || (offset_floats & 3) || signal_pad_bytes < moss_peer_signal_bytes(world))
+		return MOSS_ERR_INVALID_ARGUMENT;
 	if (numel == 0) return MOSS_OK;
+	// every rank derives the same grid from (numel, world, pad size): the flag slots are indexed by it
 	const size_t per = (numel / 4 + world - 1) / world;
-	int blocks = (int)((per + PEER_THREADS - 1) / PEER_THREADS);
-	blocks = blocks < 1 ? 1 : (blocks > PEER_MAX_BLOCKS ? PEER_MAX_BLOCKS : blocks);
+	size_t blocks = (per + (size_t)PEER_THREADS * PEER_ILP - 1) / ((size_t)PEER_THREADS * PEER_ILP);
+	const size_t pad_blocks = signal_pad_bytes / (sizeof(uint32_t) * 2 * (size_t)world);
+	if (blocks > pad_blocks) blocks = pad_blocks;
+	if (blocks > PEER_MAX_BLOCKS) blocks = PEER_MAX_BLOCKS;
+	if (blocks < 1) blocks = 1;
 	{ MOSS_STAGE(MOSS_STAGE_PEER_REDUCE, stream);
-	peer_allreduce_kernel<<<blocks, PEER_THREADS, 0, stream>>>((float* const*)buffer_ptrs_dev, (uint32_t* const*)signal_ptrs_dev,
+	peer_allreduce_kernel<<<(unsigned)blocks, PEER_THREADS, 0, stream>>>((float* const*)buffer_ptrs_dev, (uint32_t* const*)signal_ptrs_dev,
 		rank, world, offset_floats, numel, epoch, error_word_dev); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;

@@ -8,16 +8,17 @@
 //   barrier  -> every slice of the local buffer has arrived
 // 4.9 MB at ZJU shape: (world-1)/world of it crosses NVLink once in each direction, versus NCCL's ~50-70 us launch +
 // protocol latency at this size, which is a third of the 0.2 ms step.
-// Flags live in the peers' signal pads: slot ((phase * PEER_MAX_BLOCKS + block) * world + writer), value = the call's
+// Flags live in the peers' signal pads: slot ((phase * gridDim.x + block) * world + writer), value = the call's
 // epoch (monotonic, never reset).  Spins give up after ~10 s and raise the error word instead of hanging the GPU.
 #pragma once
 #include "common.cuh"
 
 namespace moss {
 
-constexpr int PEER_MAX_BLOCKS = 32;
+constexpr int PEER_MAX_BLOCKS = 128;   // upper bound; the launch uses what the signal pads can hold
+constexpr int PEER_ILP = 4;            // float4 per thread in flight: an NVLink round trip is ~2 us, so the loop must not serialise them
 constexpr int PEER_MAX_WORLD = 8;
-constexpr int PEER_THREADS = 512;
+constexpr int PEER_THREADS = 256;
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v)
 {
@@ -46,7 +47,7 @@ __device__ __forceinline__ void peer_barrier(uint32_t* const* pads, int rank, in
 	__syncthreads();
 	if ((int)threadIdx.x < world) {
 		const int p = (int)threadIdx.x;
-		const size_t slot = (size_t)(phase * PEER_MAX_BLOCKS + (int)blockIdx.x) * world;
+		const size_t slot = (size_t)(phase * (int)gridDim.x + (int)blockIdx.x) * world;
 		__threadfence_system();
 		st_release_sys(pads[p] + slot + rank, epoch);
 		const uint32_t* mine = pads[rank] + slot + p;
@@ -69,18 +70,29 @@ peer_allreduce_kernel(float* const* bufs, uint32_t* const* pads, int rank, int w
 	const size_t n4 = numel / 4;
 	const size_t per = (n4 + world - 1) / world;                 // float4s per rank slice
 	const size_t lo = min(n4, per * rank), hi = min(n4, lo + per);
-	for (size_t i = lo + (size_t)blockIdx.x * PEER_THREADS + threadIdx.x; i < hi; i += (size_t)gridDim.x * PEER_THREADS) {
-		float4 v[PEER_MAX_WORLD];
+	const size_t stride = (size_t)gridDim.x * PEER_THREADS;
+	for (size_t i0 = lo + (size_t)blockIdx.x * PEER_THREADS + threadIdx.x; i0 < hi; i0 += stride * PEER_ILP) {
+		float4 v[PEER_ILP][PEER_MAX_WORLD];
 #pragma unroll
-		for (int p = 0; p < PEER_MAX_WORLD; p++)
-			if (p < world) v[p] = ld_peer_f4(reinterpret_cast<const float4*>(s_buf[p]) + i);
-		float4 s = v[0];
+		for (int u = 0; u < PEER_ILP; u++) {
+			const size_t i = i0 + u * stride;
 #pragma unroll
-		for (int p = 1; p < PEER_MAX_WORLD; p++)
-			if (p < world) { s.x += v[p].x; s.y += v[p].y; s.z += v[p].z; s.w += v[p].w; }
+			for (int p = 0; p < PEER_MAX_WORLD; p++)
+				if (p < world && i < hi) v[u][p] = ld_peer_f4(reinterpret_cast<const float4*>(s_buf[p]) + i);
+		}
 #pragma unroll
-		for (int p = 0; p < PEER_MAX_WORLD; p++)
-			if (p < world) st_peer_f4(reinterpret_cast<float4*>(s_buf[p]) + i, s);
+		for (int u = 0; u < PEER_ILP; u++) {
+			const size_t i = i0 + u * stride;
+			if (i < hi) {
+				float4 s = v[u][0];
+#pragma unroll
+				for (int p = 1; p < PEER_MAX_WORLD; p++)
+					if (p < world) { s.x += v[u][p].x; s.y += v[u][p].y; s.z += v[u][p].z; s.w += v[u][p].w; }
+#pragma unroll
+				for (int p = 0; p < PEER_MAX_WORLD; p++)
+					if (p < world) st_peer_f4(reinterpret_cast<float4*>(s_buf[p]) + i, s);
+			}
+		}
 	}
 	// scalar tail (numel % 4) by the last rank
 	if (rank == world - 1 && blockIdx.x == 0 && threadIdx.x < (numel & 3)) {

@@ -97,7 +97,8 @@ class PeerGradBuffer:
         self.epoch += 1
         st = self._lib.moss_peer_allreduce(torch.cuda.current_stream(self.device).cuda_stream, self.rank, self.world,
                                            int(self.handle.buffer_ptrs_dev), int(self.handle.signal_pad_ptrs_dev),
-                                           int(offset), int(numel), self.epoch, self.error.data_ptr())
+                                           int(self.handle.signal_pad_size), int(offset), int(numel), self.epoch,
+                                           self.error.data_ptr())
         from . import _abi
         _abi.check(st, "moss_peer_allreduce")
         return self.tensor
