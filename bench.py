@@ -162,6 +162,24 @@ def run_ours(args, rank, world, dev):
             return (i * world + rank) % len(settings)
         return sched[i % len(sched)][rank]
 
+    # The timed device-resident loop replays one CUDA graph per view (fwd + bwd + gradient exchange captured once,
+    # MOSS_FLAG_ASYNC); --no-graph, the per-kernel profiling pass and rank-local extra steps use stream launches.
+    graphs = {}
+    use_graph = (not args.no_graph) and (world == 1 or peer is not None)
+    inputs = dict(devt)
+
+    def graph_step(i):
+        from moss_b200.graphs import GraphedStep
+        v = view_of(i)
+        gs = graphs.get(v)
+        if gs is None:
+            after = (lambda st_: peer.allreduce(st_.param_grad_numel)) if peer is not None else None
+            gs = graphs[v] = GraphedStep(inputs, settings[v], (gc, gd, ga), grad_out=peer.tensor if peer is not None else None,
+                                         after=after)
+        gs.replay()
+        state["st"], state["radii"] = gs.state, gs.out[1]
+        return gs.state
+
     def step(i, collective=True):
         rs = settings[view_of(i)]
         color, radii, depth, alpha, st = M.forward_raw(devt["means3D"], devt["shs"], devt["colors_precomp"], devt["opacities"],
@@ -221,9 +239,24 @@ def run_ours(args, rank, world, dev):
         th.start()
         time.sleep(0.3)
 
-    launches0 = lib.moss_kernel_launches()
-    ms_total, t0, t1 = timed_loop(step, args.steps, args.warmup)
-    launches_timed = (lib.moss_kernel_launches() - launches0) * args.steps // (args.steps + args.warmup)
+    timed_step = step
+    if use_graph:
+        try:
+            # capture every view this rank will replay BEFORE the timed loop; all ranks capture the same number of
+            # graphs in the same order (each capture runs the exchange a few times)
+            for i in range(len(sched) if sched is not None else len(settings)):
+                graph_step(i)
+            torch.cuda.synchronize(dev)
+            timed_step = graph_step
+        except Exception as e:                       # capture not possible here: say so and time the stream path
+            if world > 1:
+                raise
+            print(f"[bench] CUDA-graph capture failed, timing stream launches: {e}", file=sys.stderr)
+            use_graph = False
+    ms_total, t0, t1 = timed_loop(timed_step, args.steps, args.warmup)
+    if use_graph:
+        for gs in graphs.values():
+            gs.check()
     # keep the same load running until the sampler has seen it for >= 1 s (the timed region may be shorter than
     # nvidia-smi's sampling period); these extra steps are not part of any reported time
     t_ext = time.perf_counter()
@@ -237,10 +270,12 @@ def run_ours(args, rank, world, dev):
 
     # per-kernel times (same steps, events around every kernel launch inside the library, on the launching stream)
     lib.moss_profile_enable(1)
+    launches0 = lib.moss_kernel_launches()
     for i in range(args.steps):
         flush.zero_()
         step(i)
     torch.cuda.synchronize(dev)
+    launches_timed = lib.moss_kernel_launches() - launches0      # kernels of args.steps steps (a replayed graph runs the same ones)
     prof = _abi.profile_read()
     lib.moss_profile_enable(0)
 
@@ -331,6 +366,7 @@ def run_ours(args, rank, world, dev):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOADS[args.workload]["desc"], "gaussians": P, "visible": V, "instances": R,
                    "image": [W, H], "views_per_step": world, "l2": "flushed between steps (256 MiB fill, outside the timed events)",
+                   "launch": "one CUDA graph per view (fwd+bwd+exchange captured once, MOSS_FLAG_ASYNC)" if use_graph else "stream launches",
                    "parallelism": f"dp{world} (views sharded, packed parameter gradient all-reduced: {collective_kind})" if world > 1 else "single GPU"},
         "e2e": {"value": round(mpix / (e2e_ms_step * 1e-3), 2), "unit": "Mpix/s", "ms_per_step": round(e2e_ms_step, 5),
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps, "device_mallocs": e2e_mallocs},
@@ -480,6 +516,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "cpu"])
     ap.add_argument("--workload", default="zju", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="time stream launches instead of replaying captured CUDA graphs")
     ap.add_argument("--quick", action="store_true", help="profiling runs (ncu): no clock extension, 2 e2e steps, no CPU baseline")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

@@ -166,8 +166,10 @@ size_t moss_sizeof_skin(void);
  * allows more blocks) as mapped in the calling process.
  * One kernel per rank: flag barrier, two-shot all-reduce with loads/stores on the peer pointers (rank order, so the
  * result is bit-identical on every rank and from run to run), flag barrier.  Every rank must call it with the same
- * numel/offset and the same, strictly increasing, non-zero `epoch`.  *error_word_dev (device uint32, zeroed by the
- * caller once) becomes non-zero if a peer did not arrive within ~10 s. */
+ * numel/offset and either the same, strictly increasing, non-zero `epoch`, or always epoch 0: the epoch then lives on
+ * the device (error_word_dev[1], bumped by a one-thread kernel before the exchange), which makes the call CUDA-graph
+ * capturable.  error_word_dev: device uint32[2], zeroed by the caller once; [0] becomes non-zero if a peer did not
+ * arrive within ~10 s. */
 size_t moss_peer_signal_bytes(int world);
 int moss_peer_allreduce(void* stream, int rank, int world, void* const* buffer_ptrs_dev, void* const* signal_ptrs_dev,
                         size_t signal_pad_bytes, size_t offset_floats, size_t numel, unsigned epoch,

@@ -553,7 +553,7 @@ int moss_peer_allreduce(void* stream_, int rank, int world, void* const* buffer_
 {
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || !buffer_ptrs_dev || !signal_ptrs_dev ||
-		!error_word_dev || epoch == 0 || (offset_floats & 3) || signal_pad_bytes < moss_peer_signal_bytes(world))
+		!error_word_dev || (offset_floats & 3) || signal_pad_bytes < moss_peer_signal_bytes(world))
 		return MOSS_ERR_INVALID_ARGUMENT;
 	if (numel == 0) return MOSS_OK;
 	// every rank derives the same grid from (numel, world, pad size): the flag slots are indexed by it
@@ -564,6 +564,7 @@ int moss_peer_allreduce(void* stream_, int rank, int world, void* const* buffer_
 	if (blocks > PEER_MAX_BLOCKS) blocks = PEER_MAX_BLOCKS;
 	if (blocks < 1) blocks = 1;
 	{ MOSS_STAGE(MOSS_STAGE_PEER_REDUCE, stream);
+	if (epoch == 0) peer_epoch_kernel<<<1, 1, 0, stream>>>(error_word_dev);
 	peer_allreduce_kernel<<<(unsigned)blocks, PEER_THREADS, 0, stream>>>((float* const*)buffer_ptrs_dev, (uint32_t* const*)signal_ptrs_dev,
 		rank, world, offset_floats, numel, epoch, error_word_dev); }
 	MOSS_CHECK_LAUNCH(stream, 0);

@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(PEER_THREADS)
 peer_allreduce_kernel(float* const* bufs, uint32_t* const* pads, int rank, int world, size_t offset, size_t numel,
 	uint32_t epoch, uint32_t* err)
 {
+	if (epoch == 0) epoch = err[1];       // device-side epoch (bumped by peer_epoch_kernel just before): graph-capturable
 	__shared__ float* s_buf[PEER_MAX_WORLD];
 	if ((int)threadIdx.x < world) s_buf[threadIdx.x] = bufs[threadIdx.x] + offset;
 	peer_barrier(pads, rank, world, 0, epoch, err);
@@ -103,5 +104,8 @@ peer_allreduce_kernel(float* const* bufs, uint32_t* const* pads, int rank, int w
 	}
 	peer_barrier(pads, rank, world, 1, epoch, err);
 }
+
+// err[1] += 1: the epoch of the next peer_allreduce_kernel when the caller passes epoch 0.
+__global__ void peer_epoch_kernel(uint32_t* err) { err[1] += 1u; }
 
 } // namespace moss

@@ -84,8 +84,7 @@ class PeerGradBuffer:
         need = self._lib.moss_peer_signal_bytes(self.world)
         if int(self.handle.signal_pad_size) < need:
             raise RuntimeError(f"signal pad too small ({self.handle.signal_pad_size} < {need})")
-        self.error = torch.zeros(1, dtype=torch.int32, device=device)
-        self.epoch = 0
+        self.error = torch.zeros(2, dtype=torch.int32, device=device)      # [0] timeout flag, [1] device-side epoch
         self.device = device
         # everyone's pad is zero and mapped before the first kernel spins on it
         self.tensor.zero_()
@@ -93,11 +92,11 @@ class PeerGradBuffer:
         dist.barrier(group)
 
     def allreduce(self, numel, offset=0):
-        """Sum tensor[offset:offset+numel] over all ranks, in place, on the current stream (no host sync)."""
-        self.epoch += 1
+        """Sum tensor[offset:offset+numel] over all ranks, in place, on the current stream (no host sync; the epoch
+        lives on the device, so the call can be captured in a CUDA graph)."""
         st = self._lib.moss_peer_allreduce(torch.cuda.current_stream(self.device).cuda_stream, self.rank, self.world,
                                            int(self.handle.buffer_ptrs_dev), int(self.handle.signal_pad_ptrs_dev),
-                                           int(self.handle.signal_pad_size), int(offset), int(numel), self.epoch,
+                                           int(self.handle.signal_pad_size), int(offset), int(numel), 0,
                                            self.error.data_ptr())
         from . import _abi
         _abi.check(st, "moss_peer_allreduce")
@@ -105,7 +104,7 @@ class PeerGradBuffer:
 
     def check(self):
         """Host-side check (synchronises): did any spin time out?"""
-        if int(self.error.item()) != 0:
+        if int(self.error[0].item()) != 0:
             raise RuntimeError("moss_peer_allreduce: a peer did not arrive (timeout)")
 
 

@@ -328,3 +328,8 @@ def export_state(st, name):
     if n < 0:
         raise RuntimeError(f"moss_export_state({name}) failed: {lib.moss_error_string(int(-n)).decode()}")
     return out
+
+
+def export_state_counters(st):
+    """int32[4] on the host side of a sync: num_rendered, overflow flag, capacity, non-empty tiles."""
+    return export_state(st, "counters").cpu()
