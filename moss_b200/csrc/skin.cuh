@@ -167,6 +167,21 @@ __device__ __forceinline__ void load3(const float* base, int row, float v[3])
 	else { v[0] = v[1] = v[2] = 0.f; }
 }
 
+// The Gaussian's own values, read at the top of the kernels together with vert_ids: the weight / offset rows depend on
+// vert_ids (one extra round trip), nothing else should queue up behind them.
+struct SkinOwn { float x[3], qr[4], sc[3]; };
+__device__ __forceinline__ SkinOwn skin_own(const SkinArgs& a, int idx)
+{
+	SkinOwn o;
+#pragma unroll
+	for (int i = 0; i < 3; i++) o.x[i] = __ldg(a.xyz + 3 * (size_t)idx + i);
+#pragma unroll
+	for (int i = 0; i < 4; i++) o.qr[i] = a.rotation ? __ldg(a.rotation + 4 * (size_t)idx + i) : 0.f;
+#pragma unroll
+	for (int i = 0; i < 3; i++) o.sc[i] = a.scaling ? a.scale_modifier * __ldg(a.scaling + 3 * (size_t)idx + i) : 0.f;
+	return o;
+}
+
 // Everything of the forward the backward needs again (recomputed there instead of being stored).
 struct SkinFwd {
 	Mat3 Rbi, Rt, Tr0, Tr;     // inverse big-pose rotation, target rotation, Rt*Rbi, Rg*Rt*Rbi
@@ -174,13 +189,13 @@ struct SkinFwd {
 	float q[3];                // T-pose point after the three offsets
 	float s[3];                // SMPL-space posed point
 };
-__device__ __forceinline__ void skin_point(const SkinShared& sh, const SkinArgs& a, int idx, int vid, const float bw[NJ], SkinFwd& f)
+__device__ __forceinline__ void skin_point(const SkinShared& sh, const SkinArgs& a, const float x[3], int vid, const float bw[NJ], SkinFwd& f)
 {
 	Mat3 Rb; float tb[3];
 	skin_blend(sh.Ab, bw, Rb, tb);
 	f.Rbi = mat3_inverse(Rb);
 #pragma unroll
-	for (int i = 0; i < 3; i++) f.xb[i] = __ldg(a.xyz + 3 * (size_t)idx + i) - tb[i];
+	for (int i = 0; i < 3; i++) f.xb[i] = x[i] - tb[i];
 	float q0[3];
 	mat3_vec(f.Rbi, f.xb, q0);
 	float pb[3], so[3], pt[3];
@@ -218,10 +233,11 @@ skin_forward_kernel(SkinArgs a, float* __restrict__ means3D, float* __restrict__
 	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= a.P) return;
 	const int vid = __ldg(a.vert_ids + idx);
+	const SkinOwn own = skin_own(a, idx);
 	float bw[NJ];
 	skin_weights(a, idx, vid, bw);
 	SkinFwd f;
-	skin_point(sh, a, idx, vid, bw, f);
+	skin_point(sh, a, own.x, vid, bw, f);
 	// world = smpl_pts @ inverse(R) + Th   (scene/gaussian_model.py:911-912)
 #pragma unroll
 	for (int i = 0; i < 3; i++)
@@ -255,11 +271,8 @@ skin_forward_kernel(SkinArgs a, float* __restrict__ means3D, float* __restrict__
 			translation[3 * (size_t)idx + i] = (r2[0] * sh.Rgi[i] + r2[1] * sh.Rgi[3 + i] + r2[2] * sh.Rgi[6 + i]) + sh.Th[i];
 	}
 	if (cov3D && a.scaling) {
-		float qr[4], sc[3];
-#pragma unroll
-		for (int i = 0; i < 4; i++) qr[i] = __ldg(a.rotation + 4 * (size_t)idx + i);
-#pragma unroll
-		for (int i = 0; i < 3; i++) sc[i] = a.scale_modifier * __ldg(a.scaling + 3 * (size_t)idx + i);
+		const float (&qr)[4] = own.qr;
+		const float (&sc)[3] = own.sc;
 		const float inv_norm = 1.0f / sqrtf(qr[0] * qr[0] + qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
 		Mat3 Rq, L;
 		quat_rot(qr, inv_norm, Rq);
@@ -297,20 +310,23 @@ skin_backward_kernel(SkinArgs a, const float* __restrict__ g_means3D, const floa
 	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx < a.P) {
 		const int vid = __ldg(a.vert_ids + idx);
+		const SkinOwn own = skin_own(a, idx);
+		float gw[3], gcv[6];
+#pragma unroll
+		for (int i = 0; i < 3; i++) gw[i] = __ldg(g_means3D + 3 * (size_t)idx + i);
+#pragma unroll
+		for (int i = 0; i < 6; i++) gcv[i] = g_cov3D ? __ldg(g_cov3D + 6 * (size_t)idx + i) : 0.f;
 		float bw[NJ];
 		skin_weights(a, idx, vid, bw);
 		SkinFwd f;
-		skin_point(sh, a, idx, vid, bw, f);
+		skin_point(sh, a, own.x, vid, bw, f);
 
 		Mat3 dTr;
 #pragma unroll
 		for (int i = 0; i < 9; i++) dTr.m[i] = 0.f;
 		if (a.scaling && g_cov3D) {
-			float qr[4], sc[3];
-#pragma unroll
-			for (int i = 0; i < 4; i++) qr[i] = __ldg(a.rotation + 4 * (size_t)idx + i);
-#pragma unroll
-			for (int i = 0; i < 3; i++) sc[i] = a.scale_modifier * __ldg(a.scaling + 3 * (size_t)idx + i);
+			const float (&qr)[4] = own.qr;
+			const float (&sc)[3] = own.sc;
 			const float inv_norm = 1.0f / sqrtf(qr[0] * qr[0] + qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
 			Mat3 Rq, L;
 			quat_rot(qr, inv_norm, Rq);
@@ -319,10 +335,9 @@ skin_backward_kernel(SkinArgs a, const float* __restrict__ g_means3D, const floa
 #pragma unroll
 				for (int k = 0; k < 3; k++) L.m[3 * i + k] = Rq.m[3 * i + k] * sc[k];
 			const Mat3 S = mat3_mul_nt(L, L);
-			const float* g = g_cov3D + 6 * (size_t)idx;
 			Mat3 G;      // gradient w.r.t. the full 3x3 product: only the upper triangle is read (strip_symmetric)
-			G.m[0] = __ldg(g); G.m[1] = __ldg(g + 1); G.m[2] = __ldg(g + 2); G.m[3] = 0.f; G.m[4] = __ldg(g + 3);
-			G.m[5] = __ldg(g + 4); G.m[6] = 0.f; G.m[7] = 0.f; G.m[8] = __ldg(g + 5);
+			G.m[0] = gcv[0]; G.m[1] = gcv[1]; G.m[2] = gcv[2]; G.m[3] = 0.f; G.m[4] = gcv[3];
+			G.m[5] = gcv[4]; G.m[6] = 0.f; G.m[7] = 0.f; G.m[8] = gcv[5];
 			Mat3 Gs;     // G + G^T
 #pragma unroll
 			for (int i = 0; i < 3; i++)
@@ -361,9 +376,7 @@ skin_backward_kernel(SkinArgs a, const float* __restrict__ g_means3D, const floa
 		}
 
 		// ---- skinning chain --------------------------------------------------------------------------------
-		float gw[3], gs[3];
-#pragma unroll
-		for (int i = 0; i < 3; i++) gw[i] = __ldg(g_means3D + 3 * (size_t)idx + i);
+		float gs[3];
 #pragma unroll
 		for (int j = 0; j < 3; j++) gs[j] = sh.Rgi[3 * j] * gw[0] + sh.Rgi[3 * j + 1] * gw[1] + sh.Rgi[3 * j + 2] * gw[2];
 		Mat3 Rg;

@@ -1,0 +1,79 @@
+"""Front-end measurement: skinning + covariance forward+backward for ZJU / MonoCap sized
+Gaussian sets.  ours = the fused sm_100a kernel pair through the C ABI; reference = the reference's python ops
+(oracle/lbs_oracle.py, a line-by-line restatement pinned to the real functions) as torch kernels on the same GPU with
+autograd, i.e. what render() runs today; cpu = the same restatement on the host cores.  Prints one JSON line each.
+    python tools/skin_bench.py [P ...]"""
+import json, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from moss_b200 import skinning as K, synth, _abi
+from oracle import lbs_oracle as L
+from tests.lbs_cases import oracle_smpl
+
+dev = torch.device("cuda:0")
+lib = _abi.load()
+body = synth.body()
+peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json"))) if os.path.exists("MEASURED_PEAKS.json") else {"hbm_gbs": 6650.0}
+for P in [int(a) for a in sys.argv[1:]] or [20000, 100000]:
+    g = synth.gaussians(P, body, seed=synth.SEED + 5)
+    fr = synth.frame_params(7)
+    ft_c = L.frame_tables(oracle_smpl(body), fr.params, fr.big_params)
+    ft = K.FrameTables(*[t.to(dev).contiguous() for t in ft_c])
+    gen = torch.Generator().manual_seed(P)
+    delta = 0.3 * torch.randn(P, 24, generator=gen)
+    gw, gc = torch.randn(P, 3, generator=gen), torch.randn(P, 6, generator=gen)
+    leaf = lambda t, d: t.to(d).requires_grad_(True)  # noqa: E731
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+
+    def make(d, fn):
+        xyz, sc, rot, dl = leaf(g.xyz, d), leaf(g.scales, d), leaf(g.rotations, d), leaf(delta, d)
+        vid, w = g.vert_ids.to(d), body.weights.to(d)
+        gwd, gcd = gw.to(d), gc.to(d)
+        def step():
+            for t in (xyz, sc, rot, dl):
+                t.grad = None
+            m, cov = fn(xyz, vid, w, sc, rot, dl)
+            torch.autograd.backward([m, cov], [gwd, gcd])
+        return step
+    ours = make(dev, lambda x, v, w, s, r, d: K.skin_and_covariance(x, v, w, ft, s, r, 1.0, d)[:2])
+    def ref_fn(ftab):
+        def f(x, v, w, s, r, d):
+            sk, cov = L.skin_and_covariance(x, v.long(), w, ftab, s, r, 1.0, d)
+            return sk.world_pts, cov
+        return f
+    ref = make(dev, ref_fn(L.FrameTables(*ft)))
+    cpu = make("cpu", ref_fn(ft_c))
+
+    def gpu_time(step, n=100):
+        for _ in range(10): step()
+        torch.cuda.synchronize()
+        tot = 0.0
+        for _ in range(n):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); step(); e1.record(); torch.cuda.synchronize()
+            tot += e0.elapsed_time(e1)
+        return tot / n
+    l0 = lib.moss_kernel_launches()
+    t_ours = gpu_time(ours)
+    launches = (lib.moss_kernel_launches() - l0) / 110
+    lib.moss_profile_enable(1)
+    for _ in range(50):
+        flush.zero_(); ours()
+    torch.cuda.synchronize()
+    prof = _abi.profile_read(); lib.moss_profile_enable(0)
+    kf, kb = prof["skin_forward"][0] / prof["skin_forward"][1] * 1e3, prof["skin_backward"][0] / prof["skin_backward"][1] * 1e3
+    t_ref = gpu_time(ref, 30)
+    torch.set_num_threads(os.cpu_count() or 1)
+    cpu(); t0 = time.perf_counter(); cpu(); t_cpu = (time.perf_counter() - t0) * 1e3
+    # algorithmic bytes: fwd reads xyz 12 + vid 4 + weight row 96 + delta 96 + 3 offset rows 36 + scaling 12 + rot 16,
+    # writes means3D 12 + cov 24 + transforms 36 + bweights 96; bwd reads the same inputs + 36 of upstream gradient,
+    # writes d_xyz 12 + d_scaling 12 + d_rot 16 + d_delta 96
+    bytes_f, bytes_b = P * (272 + 168), P * (272 + 36 + 136)
+    print(json.dumps({"metric": "skin+covariance fwd+bwd MGaussians/s", "gaussians": P, "ours_ms": round(t_ours, 4),
+                      "ours_launches_per_step": launches, "kernel_us": {"skin_forward": round(kf, 2), "skin_backward": round(kb, 2)},
+                      "roofline": {"bound": "hbm", "kernel": "skin_backward", "achieved": round(bytes_b / (kb * 1e-6) / 1e9, 1),
+                                   "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": round(bytes_b / (kb * 1e-6) / 1e9 / peaks["hbm_gbs"], 4)},
+                      "value": round(P / 1e6 / (t_ours * 1e-3), 1), "reference_torch_ops_on_gpu_ms": round(t_ref, 4),
+                      "speedup_vs_reference_python_path": round(t_ref / t_ours, 1),
+                      "cpu_baseline": {"ms": round(t_cpu, 2), "cores": os.cpu_count(), "kind": "port"}}))
