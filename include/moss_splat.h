@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MOSS_ABI_VERSION 6
+#define MOSS_ABI_VERSION 7
 
 /* status codes */
 #define MOSS_OK                  0
@@ -167,13 +167,14 @@ size_t moss_sizeof_skin(void);
  * One kernel per rank: flag barrier, two-shot all-reduce with loads/stores on the peer pointers (rank order, so the
  * result is bit-identical on every rank and from run to run), flag barrier.  Every rank must call it with the same
  * numel/offset and either the same, strictly increasing, non-zero `epoch`, or always epoch 0: the epoch then lives on
- * the device (error_word_dev[1], bumped by a one-thread kernel before the exchange), which makes the call CUDA-graph
- * capturable.  error_word_dev: device uint32[2], zeroed by the caller once; [0] becomes non-zero if a peer did not
- * arrive within ~10 s. */
+ * the device (error_word_dev[1] counts completed exchanges; the last block to finish bumps it), which makes the call
+ * CUDA-graph capturable.  error_word_dev: device uint32[4], zeroed by the caller once; [0] becomes non-zero if a peer did not
+ * arrive within ~10 s.  multicast_ptr: the buffer's NVLS multicast mapping or NULL; with it the data phase is one
+ * multimem.ld_reduce + one multimem.st per 16 bytes (reduction inside the NVSwitch) instead of world loads + stores. */
 size_t moss_peer_signal_bytes(int world);
 int moss_peer_allreduce(void* stream, int rank, int world, void* const* buffer_ptrs_dev, void* const* signal_ptrs_dev,
                         size_t signal_pad_bytes, size_t offset_floats, size_t numel, unsigned epoch,
-                        unsigned* error_word_dev);
+                        unsigned* error_word_dev, void* multicast_ptr);
 
 /* Internal-state export for parity tests (the reference needs a C++ shim over fromChunk for this,
  * DGR/cuda_rasterizer/rasterizer_impl.cu:155-194).  Copies one state array into `dst` (device) on

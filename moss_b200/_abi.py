@@ -117,7 +117,7 @@ def load():
     lib.moss_peer_signal_bytes.restype = C.c_size_t
     lib.moss_peer_signal_bytes.argtypes = [C.c_int]
     lib.moss_peer_allreduce.restype = C.c_int
-    lib.moss_peer_allreduce.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, vp]
+    lib.moss_peer_allreduce.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, vp, vp]
     lib.moss_sizeof_skin.restype = C.c_size_t
     lib.moss_skin_forward.restype = C.c_int
     lib.moss_skin_forward.argtypes = [vp, C.POINTER(MossSkin)] + [vp] * 5

@@ -549,7 +549,8 @@ int moss_skin_backward(void* stream_, const MossSkin* k, const float* g_means3D,
 size_t moss_peer_signal_bytes(int world) { return sizeof(uint32_t) * 2 * 8 * (size_t)(world > 0 ? world : 1); }   // minimum: 8 blocks
 
 int moss_peer_allreduce(void* stream_, int rank, int world, void* const* buffer_ptrs_dev, void* const* signal_ptrs_dev,
-	size_t signal_pad_bytes, size_t offset_floats, size_t numel, unsigned epoch, unsigned* error_word_dev)
+	size_t signal_pad_bytes, size_t offset_floats, size_t numel, unsigned epoch, unsigned* error_word_dev,
+	void* multicast_ptr)
 {
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || !buffer_ptrs_dev || !signal_ptrs_dev ||
@@ -564,9 +565,8 @@ int moss_peer_allreduce(void* stream_, int rank, int world, void* const* buffer_
 	if (blocks > PEER_MAX_BLOCKS) blocks = PEER_MAX_BLOCKS;
 	if (blocks < 1) blocks = 1;
 	{ MOSS_STAGE(MOSS_STAGE_PEER_REDUCE, stream);
-	if (epoch == 0) peer_epoch_kernel<<<1, 1, 0, stream>>>(error_word_dev);
 	peer_allreduce_kernel<<<(unsigned)blocks, PEER_THREADS, 0, stream>>>((float* const*)buffer_ptrs_dev, (uint32_t* const*)signal_ptrs_dev,
-		rank, world, offset_floats, numel, epoch, error_word_dev); }
+		rank, world, offset_floats, numel, epoch, error_word_dev, (float*)multicast_ptr); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }

@@ -84,7 +84,18 @@ class PeerGradBuffer:
         need = self._lib.moss_peer_signal_bytes(self.world)
         if int(self.handle.signal_pad_size) < need:
             raise RuntimeError(f"signal pad too small ({self.handle.signal_pad_size} < {need})")
-        self.error = torch.zeros(2, dtype=torch.int32, device=device)      # [0] timeout flag, [1] device-side epoch
+        import os
+        mc = 0
+        # NVLS (reduction inside the switch) moves 1/world of the buffer per GPU; measured on B200 it ties with the
+        # peer-pointer path at 4 and 8 ranks and loses at 2 (tools/peer_probe.py), so it is used from 4 ranks up
+        want = os.environ.get("MOSS_PEER_MULTIMEM", "auto")
+        if want == "1" or (want == "auto" and self.world >= 4):
+            try:
+                mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+            except Exception:
+                mc = 0
+        self.multicast_ptr = mc                 # 0: no NVLS mapping -> loads/stores on the peer pointers
+        self.error = torch.zeros(4, dtype=torch.int32, device=device)      # [0] timeout flag, [1] device-side epoch, [2] block counter
         self.device = device
         # everyone's pad is zero and mapped before the first kernel spins on it
         self.tensor.zero_()
@@ -97,7 +108,7 @@ class PeerGradBuffer:
         st = self._lib.moss_peer_allreduce(torch.cuda.current_stream(self.device).cuda_stream, self.rank, self.world,
                                            int(self.handle.buffer_ptrs_dev), int(self.handle.signal_pad_ptrs_dev),
                                            int(self.handle.signal_pad_size), int(offset), int(numel), 0,
-                                           self.error.data_ptr())
+                                           self.error.data_ptr(), self.multicast_ptr or None)
         from . import _abi
         _abi.check(st, "moss_peer_allreduce")
         return self.tensor

@@ -28,7 +28,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_versions_and_strings(lib):
-    assert lib.moss_abi_version() == 6
+    assert lib.moss_abi_version() == 7
     assert lib.moss_error_string(0) == b"ok"
     assert b"binning" in lib.moss_error_string(_abi.MOSS_ERR_BINNING_OVERFLOW)
 

@@ -29,5 +29,5 @@ for n in (1_220_000, 6_100_000):
     t_graph = timeit(g.replay, 50) / 10
     buf.check()
     if rank == 0:
-        print(f"world {world} numel {n} ({n*4/1e6:.1f} MB): peer {t_peer:.1f} us  peer(graph x10) {t_graph:.1f} us  nccl {t_nccl:.1f} us  pad {buf.handle.signal_pad_size} B")
+        print(f"world {world} numel {n} ({n*4/1e6:.1f} MB): peer {t_peer:.1f} us  peer(graph x10) {t_graph:.1f} us  nccl {t_nccl:.1f} us  pad {buf.handle.signal_pad_size} B  multicast {hex(buf.multicast_ptr)}")
 dist.destroy_process_group()
