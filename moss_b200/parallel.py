@@ -122,11 +122,22 @@ class PeerGradBuffer:
 def balanced_view_schedule(costs, world):
     """Cost-balanced data-parallel schedule.  A step ends when its SLOWEST rank has finished (the gradient exchange is
     a barrier), and the views of one body differ by up to 40 % in cost (edge-on views stack thousands of splats in a
-    few tiles).  So the views rendered in the same step should cost about the same: sort the views by cost and let
-    step s give rank r the view at position (s * world + r) of that order (wrapping around).  Every rank still visits
-    every view.  -> list of steps, each a list of `world` view indices; len = number of views."""
+    few tiles).  So the views rendered in the same step should cost about the same: sort the views by cost and cut
+    the order into consecutive groups of `world` (the last group is the `world` most expensive views, so it may
+    overlap its neighbour instead of wrapping around to the cheapest ones).  One cycle = one step per group; from
+    cycle to cycle the ranks rotate through the positions of a group, so over `world` cycles every rank has rendered
+    every view.  -> list of steps, each a list of `world` view indices (len = groups * world)."""
     n = len(costs)
     if n == 0 or world <= 0:
         raise ValueError("need at least one view and one rank")
     order = sorted(range(n), key=lambda i: (costs[i], i))
-    return [[order[(s * world + r) % n] for r in range(world)] for s in range(n)]
+    if n <= world:
+        groups = [[order[r % n] for r in range(world)]]
+    else:
+        starts = list(range(0, n - world, world)) + [n - world]
+        groups = [order[s:s + world] for s in starts]
+    steps = []
+    for cycle in range(world):
+        for g in groups:
+            steps.append([g[(r + cycle) % world] for r in range(world)])
+    return steps
