@@ -77,6 +77,7 @@ struct BinWS {
 	unsigned long long* keys; // [cap] (depth_bits << 32 | gaussian id), grouped per tile, sorted in place
 	uint32_t* point_list;     // [cap] sorted gaussian ids
 	unsigned long long* keys_sorted; // [cap] (tile << 32 | depth_bits), only with EXPORT_KEYS
+	unsigned long long* keys_tmp;    // [cap] bucketed copy of a tile's keys: tiles deeper than the shared-memory sort holds
 };
 
 template <typename T>
@@ -124,6 +125,7 @@ __host__ __device__ inline BinWS carve_bin(char* base, size_t cap, bool export_k
 	b.keys = carve<unsigned long long>(p, cap);
 	b.point_list = carve<uint32_t>(p, cap);
 	b.keys_sorted = export_keys ? carve<unsigned long long>(p, cap) : nullptr;
+	b.keys_tmp = carve<unsigned long long>(p, cap);
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return b;
 }
@@ -144,7 +146,7 @@ __device__ __forceinline__ float det_scale_from_bits(uint32_t bits, bool inverse
 // list into segments of CKPT_SEG that run as independent blocks.  The forward stores every pixel's running state
 // (T, C rgb, D) at the segment boundaries and its final sums; a backward segment starts from the boundary state
 // instead of walking everything behind it (blend.cuh).
-constexpr int CKPT_SEG = 256;
+constexpr int CKPT_SEG = 128;     // = the blend kernels' staging batch for 2- and 4-warp blocks (whole-tile blocks stage 256: no checkpoints)
 constexpr int CKPT_REC_FLOATS = 5 * TILE_PIX;   // one boundary record of one tile: [component][pixel slot]
 struct CkptWS {
 	float4*   fin;        // [N]  final (C0, C1, C2, D) of every pixel, without background

@@ -139,13 +139,6 @@ inline ViewParams make_view(const MossScene* sc)
 	return vp;
 }
 
-// The optional checkpoint workspace is used when it is large enough for this call's binning capacity.
-inline CkptWS scene_ckpt(const MossScene* sc, uint32_t capacity, int N, int T)
-{
-	if (!sc->ckpt_ws || sc->ckpt_bytes < moss_ckpt_workspace_bytes((long long)capacity, sc->W, sc->H)) return no_ckpt();
-	return carve_ckpt((char*)sc->ckpt_ws, (size_t)N, (size_t)T, (size_t)capacity);
-}
-
 // Blend block shape (1 whole tile / 2 half / 3 quarter).  Small images have few busy tiles and the deepest one sets
 // the launch time, so its patches are spread over more SMs; large images have enough tiles to fill the machine
 // and prefer fewer, larger blocks (less duplicated staging).
@@ -154,6 +147,15 @@ inline int blend_split(unsigned flags, int T)
 	const int f = (int)((flags & MOSS_FLAG_SPLIT_MASK) >> MOSS_FLAG_SPLIT_SHIFT);
 	if (f) return f;
 	return T <= 2048 ? 3 : (T <= 6144 ? 2 : 1);
+}
+
+// The optional checkpoint workspace is used when it is large enough for this call's binning capacity.
+inline CkptWS scene_ckpt(const MossScene* sc, uint32_t capacity, int N, int T, unsigned flags)
+{
+	// whole-tile (8-warp) blocks stage 256 instances per round and would skip every other boundary
+	if (blend_split(flags, T) == 1 && CKPT_SEG < 256) return no_ckpt();
+	if (!sc->ckpt_ws || sc->ckpt_bytes < moss_ckpt_workspace_bytes((long long)capacity, sc->W, sc->H)) return no_ckpt();
+	return carve_ckpt((char*)sc->ckpt_ws, (size_t)N, (size_t)T, (size_t)capacity);
 }
 
 __global__ void reset_overflow_kernel(uint32_t* counters, uint32_t capacity)
@@ -245,7 +247,7 @@ size_t moss_ckpt_workspace_bytes(long long capacity, int W, int H)
 }
 long long moss_binning_capacity(size_t bytes, int export_keys)
 {
-	const size_t per = export_keys ? 20 : 12;
+	const size_t per = export_keys ? 28 : 20;
 	long long lo = 0, hi = (long long)(bytes / per) + 1;   // largest cap with bytes_ex(cap) <= bytes
 	while (lo < hi) {
 		const long long mid = lo + (hi - lo + 1) / 2;
@@ -280,7 +282,7 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 	const uint32_t capacity = (uint32_t)(cap_ll > 0xfffffff0ll ? 0xfffffff0ll : cap_ll);
 	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P);
 	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
-	const CkptWS ck = scene_ckpt(sc, capacity, N, T);
+	const CkptWS ck = scene_ckpt(sc, capacity, N, T, flags);
 
 	int slot = -1;
 	if (!(flags & MOSS_FLAG_ASYNC)) {
@@ -378,7 +380,7 @@ int moss_rasterize_backward(void* stream_, const MossScene* sc, unsigned flags, 
 	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P);
 	ImageWS im = carve_image((char*)sc->image_ws, (size_t)N, (size_t)T);
 	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
-	const CkptWS ck = scene_ckpt(sc, capacity, N, T);
+	const CkptWS ck = scene_ckpt(sc, capacity, N, T, flags);
 	// work units: tiles, or (with checkpoints) at most capacity/CKPT_SEG + T segments; surplus blocks exit at once
 	const unsigned units = ck.rec ? ck.max_segs : (unsigned)T;
 	const int det = (flags & MOSS_FLAG_DETERMINISTIC) ? 1 : 0;

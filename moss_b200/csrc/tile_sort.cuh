@@ -103,6 +103,76 @@ __device__ __forceinline__ void emit_sorted(const BinWS& b, uint32_t dst, int ti
 	if (b.keys_sorted) b.keys_sorted[dst] = ((unsigned long long)tile << 32) | (k >> 32);
 }
 
+// Tiles deeper than SORT_CAP (edge-on views of a 100 k-Gaussian body reach 8-12 k instances in one tile): the same
+// sample sort with the bucketed keys in GLOBAL scratch (BinWS::keys_tmp) and only the per-key bucket bytes in shared
+// memory; every bucket (expected size n/256) is then ranked by one warp.  The in-place global bitonic network this
+// replaces needed ~100 barrier-separated passes over L2 (0.5-0.9 ms for such a tile).
+constexpr int LARGE_SORT_CAP = SORT_CAP * 8;      // one bucket byte per key in the 48 KB key area
+
+__device__ __forceinline__ void tile_sort_large(SortSmem& sm, const BinWS& b, uint2 range, int n, int tile)
+{
+	const unsigned long long* gk = b.keys + range.x;
+	unsigned long long* tmp = b.keys_tmp + range.x;
+	uint8_t* bucket_of = reinterpret_cast<uint8_t*>(sm.keys);          // [n] bytes, n <= 8 * SORT_CAP
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	// 1. splitters (sorted depth words of 255 evenly spaced keys), ranked exactly like the shared-memory version
+	const uint32_t mine = tid < 255 ? (uint32_t)(gk[(int)(((long long)(tid + 1) * n) >> 8)] >> 32) : 0xffffffffu;
+	sm.start[tid] = mine;                                              // scratch until step 3
+	sm.cur[tid] = 0u;
+	__syncthreads();
+	{
+		const unsigned long long me = ((unsigned long long)mine << 8) | (unsigned)tid;
+		int r = 0;
+		for (int q = 0; q < 256; q++) r += ((((unsigned long long)sm.start[q] << 8) | (unsigned)q) < me) ? 1 : 0;
+		sm.samp[r] = mine;
+	}
+	__syncthreads();
+	// 2. bucket of every key, bucket sizes
+	for (int i = tid; i < n; i += TILE_PIX) {
+		const uint32_t d = (uint32_t)(gk[i] >> 32);
+		int pos = 0;
+#pragma unroll
+		for (int st = 128; st > 0; st >>= 1) pos += (sm.samp[pos + st - 1] < d) ? st : 0;
+		bucket_of[i] = (uint8_t)pos;
+		atomicAdd(&sm.cur[pos], 1u);
+	}
+	__syncthreads();
+	// 3. exclusive scan over the 256 bucket sizes
+	{
+		const uint32_t c = sm.cur[tid];
+		uint32_t v = c;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint32_t nb = __shfl_up_sync(0xffffffffu, v, o);
+			if (lane >= o) v += nb;
+		}
+		if (lane == 31) sm.wsum[warp] = v;
+		__syncthreads();
+		uint32_t off = 0;
+#pragma unroll
+		for (int w = 0; w < 8; w++) off += (w < warp) ? sm.wsum[w] : 0u;
+		const uint32_t excl = off + v - c;
+		__syncthreads();                       // everyone has read sm.start as scratch / sm.cur as counts
+		sm.start[tid] = excl;
+		sm.cur[tid] = excl;
+		if (tid == 255) sm.start[256] = (uint32_t)n;
+	}
+	__syncthreads();
+	// 4. scatter into the buckets (global scratch)
+	for (int i = tid; i < n; i += TILE_PIX) tmp[atomicAdd(&sm.cur[bucket_of[i]], 1u)] = gk[i];
+	__syncthreads();
+	// 5. one warp per bucket: final position = bucket start + number of smaller keys in the bucket
+	for (int bk = warp; bk < 256; bk += TILE_PIX / 32) {
+		const uint32_t s0 = sm.start[bk], len = sm.start[bk + 1] - s0;
+		for (uint32_t j = lane; j < len; j += 32) {
+			const unsigned long long key = tmp[s0 + j];
+			uint32_t r = 0;
+			for (uint32_t q = 0; q < len; q++) r += (tmp[s0 + q] < key) ? 1u : 0u;
+			emit_sorted(b, range.x + s0 + r, tile, key);
+		}
+	}
+}
+
 __device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 range, int n, int tile)
 {
 	unsigned long long* gk = b.keys + range.x;
@@ -115,6 +185,7 @@ __device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 ra
 		return;
 	}
 	if (n > SORT_CAP) {
+		if (n <= LARGE_SORT_CAP && b.keys_tmp) { tile_sort_large(sm, b, range, n, tile); return; }
 		__syncthreads();
 		block_bitonic_sort(gk, n);
 		for (int i = tid; i < n; i += TILE_PIX) emit_sorted(b, range.x + i, tile, gk[i]);

@@ -75,6 +75,8 @@ SCENES = {
     "zju": dict(P=20000, W=512, H=512, precomp_cov=True, transforms=True),
     "zju_sr": dict(P=20000, W=512, H=512),
     "monocap": dict(P=100000, W=1024, H=1024, precomp_cov=True, transforms=True),
+    # edge-on view: > 11 000 instances in one tile (beyond the shared-memory sort; exercises tile_sort_large)
+    "monocap_edge": dict(P=100000, W=1024, H=1024, precomp_cov=True, transforms=True, cam=6),
     "stress": dict(P=1000000, W=1920, H=1080, stress=True),
     "stress_small": dict(P=60000, W=480, H=270, stress=True),
 }
