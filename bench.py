@@ -11,7 +11,9 @@ own view of the same (replicated) Gaussians per step and the packed parameter gr
 
   value  : Mpix/s, inputs resident in HBM, CUDA-event timed per step; L2 is flushed between steps (outside the events).
   e2e    : same metric through the public API (GaussianRasterizer + autograd) with HOST buffers: every step copies
-           the step's inputs from pinned host memory and reads image + gradients back.
+           the step's inputs from pinned host memory and reads image + gradients back.  `e2e.value` blocks the host on
+           every call (forward outputs are read back on a side stream during the backward); `e2e.pipelined` keeps two
+           calls in flight.  Both arms run the same two loops (e2e_step / e2e_pipelined).
   roofline / cpu_baseline / clocks / gpu_launches: see DESIGN.md "Measurement".
 
 --impl reference : the UNMODIFIED reference CUDA rasterizer (oracle/_ref/diff_gaussian_rasterization, rebuilt for
@@ -110,6 +112,93 @@ def algorithmic_bytes(P, V, R, N, T, M, D, has_sr):
     b["blend_backward"] = N * (20 + 8) + R * (4 + 40) + V * 44
     b["preprocess_backward"] = P * 4 + V * (12 + 24 + 44 + 12 * (D + 1) ** 2 + 16) + P * (12 + 24 + 12 * M + (28 if has_sr else 0))
     return b
+
+
+def e2e_object(mpix, pipe_ms_step, sync_ms_step, h2d, d2h, steps, **extra):
+    """`value`: one call at a time, the host blocked until the call's results are in host memory (per-step CUDA
+    events).  `pipelined`: the same calls, copies and bytes with two calls in flight (e2e_pipelined)."""
+    o = {"value": round(mpix / (sync_ms_step * 1e-3), 2), "unit": "Mpix/s", "ms_per_step": round(sync_ms_step, 5),
+         "protocol": "synchronous call: pinned-host inputs -> device, fwd+bwd through the public API, image + gradients -> "
+                     "pinned host (forward outputs read back on a side stream during the backward), host sync; L2 flushed "
+                     "between steps outside the events",
+         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": steps,
+         "pipelined": {"value": round(mpix / (pipe_ms_step * 1e-3), 2), "ms_per_step": round(pipe_ms_step, 5),
+                       "note": "two calls in flight (upload / kernels / read-back of consecutive steps overlap), L2 flush inside "
+                               "the loop; host-bound when the kernels are shorter than the Python call path"}}
+    o.update(extra)
+    return o
+
+
+def e2e_pipelined(dev, host, lay_names, fwd_bwd, world, steps, warmup, flush, depth=2):
+    """End-to-end throughput with `depth` calls in flight (both arms run exactly this loop).
+
+    Every step still copies ITS inputs from pinned host memory and reads ITS image + gradients back to pinned host
+    memory; what changes against the synchronous protocol is only that step i+1's upload (copy-in stream) and step
+    i-1's read-back (copy-out stream) run beside step i's kernels.  `fwd_bwd(t, i, after_forward)` runs one
+    forward+backward through the public API, calls `after_forward((color, depth, alpha, radii))` in between and
+    returns the gradient tensors.  Device-timed over the whole loop (events on the compute stream, which joins the
+    copy-out stream before the closing event); the L2 flush runs inside the loop.  Returns ms for `steps` steps."""
+    main = torch.cuda.current_stream(dev)
+    s_in, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    slots = [{"out": {}, "done": torch.cuda.Event(), "in": torch.cuda.Event(), "fwd": torch.cuda.Event(),
+              "bwd": torch.cuda.Event(), "keep": None} for _ in range(depth)]
+
+    def to_host(sl, j, r):
+        if j not in sl["out"]:
+            sl["out"][j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
+        sl["out"][j].copy_(r.detach(), non_blocking=True)
+
+    def one(i):
+        sl = slots[i % depth]
+        sl["done"].synchronize()                 # this slot's previous results are on the host; its buffers are free
+        with torch.cuda.stream(s_in):
+            t = {k: host[k].to(dev, non_blocking=True) for k in lay_names}
+            sl["in"].record(s_in)
+        main.wait_event(sl["in"])
+        t = {k: v.requires_grad_(True) for k, v in t.items()}
+
+        def after_forward(outs):
+            sl["fwd"].record(main)
+            s_out.wait_event(sl["fwd"])
+            with torch.cuda.stream(s_out):
+                for j, r in enumerate(outs):
+                    to_host(sl, j, r)
+            sl["keep_f"] = outs
+
+        grads = fwd_bwd(t, i, after_forward)
+        if world > 1:
+            for g in grads:
+                dist.all_reduce(g)
+        sl["bwd"].record(main)
+        s_out.wait_event(sl["bwd"])
+        with torch.cuda.stream(s_out):
+            for j, r in enumerate(grads):
+                to_host(sl, 4 + j, r)
+            sl["done"].record(s_out)
+        sl["keep"] = (t, grads)                  # device buffers stay referenced until the slot's read-back is done
+
+    def drain():
+        for sl in slots:
+            sl["done"].synchronize()
+        torch.cuda.synchronize(dev)
+
+    for i in range(warmup):
+        one(i)
+    drain()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(main)
+    for i in range(steps):
+        flush.zero_()
+        one(i)
+    main.wait_stream(s_out)
+    e1.record(main)
+    drain()
+    if world > 1:
+        dist.barrier()
+    out_bytes = sum(v.numel() * v.element_size() for v in slots[0]["out"].values())
+    return e0.elapsed_time(e1), out_bytes
 
 
 def run_ours(args, rank, world, dev):
@@ -284,23 +373,41 @@ def run_ours(args, rank, world, dev):
     lay_names = [k for k in names if host[k] is not None]
     out_host = {}
 
-    def e2e_step(i):
-        t = {k: host[k].to(dev, non_blocking=True).requires_grad_(True) for k in lay_names}
+    side = torch.cuda.Stream(dev)          # read-back of the forward outputs runs beside the backward
+
+    def to_host(j, r):
+        if j not in out_host:
+            out_host[j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
+        out_host[j].copy_(r.detach(), non_blocking=True)   # detach: a pinned tensor must not join the autograd graph
+
+    def fwd_bwd(t, i, after_forward):
         means2D = torch.zeros_like(t["means3D"], requires_grad=True)
         color, radii, depth, alpha = rast[view_of(i)](means3D=t["means3D"], means2D=means2D, shs=t.get("shs"),
                                                          colors_precomp=t.get("colors_precomp"), opacities=t["opacities"],
                                                          scales=t.get("scales"), rotations=t.get("rotations"),
                                                          cov3D_precomp=t.get("cov3D_precomp"))
+        after_forward((color, depth, alpha, radii))
         torch.autograd.backward([color, alpha], [gc, ga])
-        res = [color, depth, alpha, radii, means2D.grad] + [t[k].grad for k in lay_names]
+        return [means2D.grad] + [t[k].grad for k in lay_names]
+
+    def e2e_step(i):
+        main = torch.cuda.current_stream(dev)
+        t = {k: host[k].to(dev, non_blocking=True).requires_grad_(True) for k in lay_names}
+
+        def after_forward(outs):
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                for j, r in enumerate(outs):
+                    to_host(j, r)
+
+        res = fwd_bwd(t, i, after_forward)
         if world > 1:
-            for g in res[4:]:
+            for g in res:
                 dist.all_reduce(g)
         for j, r in enumerate(res):
-            if j not in out_host:
-                out_host[j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
-            out_host[j].copy_(r.detach(), non_blocking=True)   # detach: a pinned tensor must not join the autograd graph
-        torch.cuda.current_stream(dev).synchronize()      # the step's result is on the host
+            to_host(4 + j, r)
+        main.synchronize()                                 # the step's result is on the host
+        side.synchronize()
         if os.environ.get("MOSS_TRACE_ALLOC"):
             ms_ = torch.cuda.memory_stats(dev)
             print("alloc-trace", i, ms_["num_device_alloc"], ms_["num_device_free"], ms_["reserved_bytes.all.current"] >> 20,
@@ -312,12 +419,13 @@ def run_ours(args, rank, world, dev):
         pr = cProfile.Profile(); pr.enable()
         timed_loop(e2e_step, e2e_steps, 3)
         pr.disable()
-        pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(14)
+        pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(32)
     def n_malloc():
         return torch.cuda.memory_stats(dev).get("num_device_alloc", 0)
     m0 = n_malloc()
     e2e_ms, _, _ = timed_loop(e2e_step, e2e_steps, max(3, min(args.warmup, 10)) if not args.quick else 1)
     e2e_mallocs = n_malloc() - m0
+    pipe_ms, pipe_out_bytes = e2e_pipelined(dev, host, lay_names, fwd_bwd, world, e2e_steps, 3 if not args.quick else 1, flush)
     h2d = sum(host[k].numel() * 4 for k in lay_names)
     d2h = sum(v.numel() * v.element_size() for v in out_host.values())
 
@@ -332,10 +440,11 @@ def run_ours(args, rank, world, dev):
     # ---- reduce over ranks -----------------------------------------------------------------------------------
     ms_step = ms_total / args.steps
     e2e_ms_step = e2e_ms / e2e_steps
+    pipe_ms_step = pipe_ms / e2e_steps
     if world > 1:
-        tt = torch.tensor([ms_step, e2e_ms_step], device=dev, dtype=torch.float64)
+        tt = torch.tensor([ms_step, e2e_ms_step, pipe_ms_step], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_step, e2e_ms_step = float(tt[0]), float(tt[1])
+        ms_step, e2e_ms_step, pipe_ms_step = float(tt[0]), float(tt[1]), float(tt[2])
     if rank != 0:
         return None
     mpix = world * N / 1e6
@@ -381,8 +490,7 @@ def run_ours(args, rank, world, dev):
                    "image": [W, H], "views_per_step": world, "l2": "flushed between steps (256 MiB fill, outside the timed events)",
                    "launch": "one CUDA graph per view (fwd+bwd+exchange captured once, MOSS_FLAG_ASYNC)" if use_graph else "stream launches",
                    "parallelism": f"dp{world} (views sharded, packed parameter gradient all-reduced: {collective_kind})" if world > 1 else "single GPU"},
-        "e2e": {"value": round(mpix / (e2e_ms_step * 1e-3), 2), "unit": "Mpix/s", "ms_per_step": round(e2e_ms_step, 5),
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps, "device_mallocs": e2e_mallocs},
+        "e2e": e2e_object(mpix, pipe_ms_step, e2e_ms_step, h2d, d2h, e2e_steps, device_mallocs=e2e_mallocs),
         "gpu_launches": int(launches_timed),
         "roofline": roof, "clocks": clocks,
     }
@@ -460,33 +568,48 @@ def run_reference(args, rank, world, dev):
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
     out_host = {}
 
-    def call(t, i):
+    side = torch.cuda.Stream(dev)          # same protocol as our arm: forward outputs are read back beside the backward
+
+    def to_host(j, r):
+        if j not in out_host:
+            out_host[j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
+        out_host[j].copy_(r.detach(), non_blocking=True)   # detach: a pinned tensor must not join the autograd graph
+
+    def fwd_bwd(t, i, after_forward):
         means2D = torch.zeros_like(t["means3D"], requires_grad=True)
         color, radii, depth, alpha = rast[(i * world + rank) % len(rast)](means3D=t["means3D"], means2D=means2D, shs=t.get("shs"),
                                                          colors_precomp=t.get("colors_precomp"), opacities=t["opacities"],
                                                          scales=t.get("scales"), rotations=t.get("rotations"),
                                                          cov3D_precomp=t.get("cov3D_precomp"))
+        after_forward((color, depth, alpha, radii))
         torch.autograd.backward([color, alpha], [gc, ga])
-        return [color, depth, alpha, radii, means2D.grad] + [t[k].grad for k in lay_names]
+        return [means2D.grad] + [t[k].grad for k in lay_names]
 
     def dev_step(i):
         t = {k: devt[k].detach().requires_grad_(True) for k in lay_names}
-        res = call(t, i)
+        res = fwd_bwd(t, i, lambda outs: None)
         if world > 1:
-            for g in res[4:]:
+            for g in res:
                 dist.all_reduce(g)
 
     def e2e_step(i):
+        main = torch.cuda.current_stream(dev)
         t = {k: host[k].to(dev, non_blocking=True).requires_grad_(True) for k in lay_names}
-        res = call(t, i)
+
+        def after_forward(outs):
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                for j, r in enumerate(outs):
+                    to_host(j, r)
+
+        res = fwd_bwd(t, i, after_forward)
         if world > 1:
-            for g in res[4:]:
+            for g in res:
                 dist.all_reduce(g)
         for j, r in enumerate(res):
-            if j not in out_host:
-                out_host[j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
-            out_host[j].copy_(r.detach(), non_blocking=True)   # detach: a pinned tensor must not join the autograd graph
-        torch.cuda.current_stream(dev).synchronize()
+            to_host(4 + j, r)
+        main.synchronize()
+        side.synchronize()
 
     def timed_loop(fn, steps, warmup):
         for i in range(warmup):
@@ -509,10 +632,12 @@ def run_reference(args, rank, world, dev):
     ms_step = timed_loop(dev_step, args.steps, args.warmup) / args.steps
     e2e_steps = max(10, min(args.steps, 200))
     e2e_ms_step = timed_loop(e2e_step, e2e_steps, max(3, min(args.warmup, 10))) / e2e_steps
+    pipe_ms, _ = e2e_pipelined(dev, host, lay_names, fwd_bwd, world, e2e_steps, 3, flush)
+    pipe_ms_step = pipe_ms / e2e_steps
     if world > 1:
-        tt = torch.tensor([ms_step, e2e_ms_step], device=dev, dtype=torch.float64)
+        tt = torch.tensor([ms_step, e2e_ms_step, pipe_ms_step], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_step, e2e_ms_step = float(tt[0]), float(tt[1])
+        ms_step, e2e_ms_step, pipe_ms_step = float(tt[0]), float(tt[1]), float(tt[2])
     if rank != 0:
         return None
     mpix = world * N / 1e6
@@ -524,8 +649,7 @@ def run_reference(args, rank, world, dev):
             "config": {"workload": WORKLOADS[args.workload]["desc"], "gaussians": P, "image": [W, H], "views_per_step": world,
                        "reference": "unmodified DGR CUDA rasterizer rebuilt for sm_100 (the reference has no CPU path)",
                        "l2": "flushed between steps (256 MiB fill, outside the timed events)"},
-            "e2e": {"value": round(mpix / (e2e_ms_step * 1e-3), 2), "unit": "Mpix/s", "ms_per_step": round(e2e_ms_step, 5),
-                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps}}
+            "e2e": e2e_object(mpix, pipe_ms_step, e2e_ms_step, h2d, d2h, e2e_steps)}
 
 
 # ---------------------------------------------------------------------------------------------------------

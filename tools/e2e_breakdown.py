@@ -1,49 +1,61 @@
-"""Host-side phase breakdown of one e2e step (H2D, forward, backward, D2H) for ours and the reference arm."""
+"""Developer tool: where does the ZJU e2e step (host buffers in, image + gradients out) spend its time?
+Times each leg alone, synchronised: H2D of the inputs, the public-API fwd+bwd on resident inputs, D2H of the outputs."""
 import os, sys, time
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+import moss_b200 as M
 from moss_b200 import synth
 from tests import scenes as S
 
-def run(impl, n=100):
-    dev = torch.device("cuda", 0)
-    if impl == "ours":
-        import moss_b200 as R
-    else:
-        sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
-        import diff_gaussian_rasterization as R
-    d = S.make_scene("zju")
-    cams = synth.ring_cameras(23, 512, 512)
-    names = ("means3D", "shs", "colors_precomp", "opacities", "scales", "rotations", "cov3D_precomp")
-    host = {k: d[k].contiguous().pin_memory() for k in names if d[k] is not None}
-    rast = [R.GaussianRasterizer(R.GaussianRasterizationSettings(**synth.settings_kwargs(c, d["bg"], d["sh_degree"], d["scale_modifier"], device=dev))) for c in cams]
-    gc, gd, ga = (t.to(dev) for t in S.upstream_grads(512, 512, depth=False))
-    out_host = {}
-    acc = dict(h2d=0.0, fwd_host=0.0, fwd=0.0, bwd_host=0.0, bwd=0.0, d2h=0.0, total=0.0)
-    sync = lambda: torch.cuda.synchronize(dev)
-    for i in range(n + 10):
-        if i == 10:
-            acc = {k: 0.0 for k in acc}
-        sync(); t0 = time.perf_counter()
-        t = {k: host[k].to(dev, non_blocking=True).requires_grad_(True) for k in host}
-        means2D = torch.zeros_like(t["means3D"], requires_grad=True)
-        sync(); t1 = time.perf_counter()
-        color, radii, depth, alpha = rast[i % 23](means3D=t["means3D"], means2D=means2D, shs=t.get("shs"), colors_precomp=None,
-                                                  opacities=t["opacities"], scales=None, rotations=None, cov3D_precomp=t.get("cov3D_precomp"))
-        t2h = time.perf_counter(); sync(); t2 = time.perf_counter()
-        torch.autograd.backward([color, alpha], [gc, ga])
-        t3h = time.perf_counter(); sync(); t3 = time.perf_counter()
-        res = [color, depth, alpha, radii, means2D.grad] + [t[k].grad for k in host]
-        for j, r in enumerate(res):
-            if j not in out_host:
-                out_host[j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
-            out_host[j].copy_(r, non_blocking=True)
-        sync(); t4 = time.perf_counter()
-        for k, v in (("h2d", t1 - t0), ("fwd_host", t2h - t1), ("fwd", t2 - t1), ("bwd_host", t3h - t2), ("bwd", t3 - t2), ("d2h", t4 - t3), ("total", t4 - t0)):
-            acc[k] += v
-    print(impl, {k: round(v / n * 1e3, 3) for k, v in acc.items()}, "ms", flush=True)
-    print("  grad strides", [(tuple(r.shape), r.is_contiguous()) for r in res[4:]])
+dev = torch.device("cuda:0")
+d = S.make_scene("zju")
+cam = d["cam"]
+rs = M.GaussianRasterizationSettings(**synth.settings_kwargs(cam, d["bg"], d["sh_degree"], d["scale_modifier"], device=dev))
+rast = M.GaussianRasterizer(rs)
+names = [k for k in ("means3D", "shs", "colors_precomp", "opacities", "scales", "rotations", "cov3D_precomp") if d[k] is not None]
+host = {k: d[k].contiguous().pin_memory() for k in names}
+gc, gd, ga = (x.to(dev) for x in S.upstream_grads(cam.image_width, cam.image_height, depth=False))
+devt = {k: host[k].to(dev) for k in names}
+out_host = {}
 
-if __name__ == "__main__":
-    run(sys.argv[1])
+
+def h2d():
+    return {k: host[k].to(dev, non_blocking=True).requires_grad_(True) for k in names}
+
+
+def compute(t):
+    m2 = torch.zeros_like(t["means3D"], requires_grad=True)
+    c, r, dp, a = rast(means3D=t["means3D"], means2D=m2, shs=t.get("shs"), colors_precomp=t.get("colors_precomp"),
+                       opacities=t["opacities"], scales=t.get("scales"), rotations=t.get("rotations"), cov3D_precomp=t.get("cov3D_precomp"))
+    torch.autograd.backward([c, a], [gc, ga])
+    return [c, dp, a, r, m2.grad] + [t[k].grad for k in names]
+
+
+def d2h(res):
+    for j, r in enumerate(res):
+        if j not in out_host:
+            out_host[j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
+        out_host[j].copy_(r.detach(), non_blocking=True)
+
+
+def timeit(label, fn, n=200):
+    for _ in range(10):
+        fn()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(n):
+        fn()
+        torch.cuda.current_stream().synchronize()
+    dt = (time.perf_counter() - t0) / n * 1e6
+    print(f"{label:34s} {dt:8.1f} us/step (wall, synchronised every step)")
+
+
+res0 = compute({k: devt[k].detach().requires_grad_(True) for k in names})
+timeit("h2d only", h2d)
+timeit("fwd+bwd (resident inputs)", lambda: compute({k: devt[k].detach().requires_grad_(True) for k in names}))
+timeit("d2h only", lambda: d2h(res0))
+timeit("d2h grads only", lambda: d2h(res0[4:]))
+timeit("h2d + fwd+bwd", lambda: compute(h2d()))
+timeit("all three", lambda: d2h(compute(h2d())))
+for k in names:
+    timeit(f"h2d {k} ({host[k].numel() * 4 >> 10} KiB)", lambda k=k: host[k].to(dev, non_blocking=True))
