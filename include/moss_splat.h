@@ -106,7 +106,8 @@ int moss_rasterize_forward(void* stream, const MossScene* scene, unsigned flags,
 
 /* Backward.  Replaces CudaRasterizer::Rasterizer::backward (DGR/cuda_rasterizer/rasterizer.h:62-98,
  * rasterizer_impl.cu:345-447) and RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:121-206).
- * The workspaces must be the ones the forward call filled.
+ * The workspaces must be the ones the forward call filled.  dL_ddepth and dL_dalpha may be NULL (no gradient
+ * reaches that output: the same arithmetic as an all-zero array, without the array).
  * EVERY output is fully written (rows of culled Gaussians with zeros): dL_dmean2D [P,3], dL_dconic [P,4],
  * dL_dopacity [P], dL_dcolor [P,3], dL_dmean3D [P,3], dL_dcov3D [P,6], dL_dsh [P,M,3] (if shs), dL_dscale [P,3]
  * and dL_drot [P,4] (if scales).  Nothing needs zero-filling beforehand (the reference zero-fills nine tensors,

@@ -432,8 +432,8 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 	if (inside) {
 		const int HW = H * W;
 		dpix[0] = dL_dpix[pix]; dpix[1] = dL_dpix[HW + pix]; dpix[2] = dL_dpix[2 * HW + pix];
-		ddepth = dL_ddepths[pix];
-		dalpha = dL_dalphas[pix];
+		ddepth = dL_ddepths ? dL_ddepths[pix] : 0.f;      // NULL = no gradient reaches this output
+		dalpha = dL_dalphas ? dL_dalphas[pix] : 0.f;
 	}
 	const float bg_dot_dpixel = bg[0] * dpix[0] + bg[1] * dpix[1] + bg[2] * dpix[2];
 
@@ -656,7 +656,8 @@ upstream_maxabs_kernel(int N, const float* __restrict__ dL_dpix, const float* __
 	float m = 0.f;
 	for (int i = blockIdx.x * 256 + threadIdx.x; i < N; i += gridDim.x * 256) {
 		m = fmaxf(m, fmaxf(fmaxf(fabsf(dL_dpix[i]), fabsf(dL_dpix[N + i])), fabsf(dL_dpix[2 * N + i])));
-		m = fmaxf(m, fmaxf(fabsf(dL_ddepth[i]), fabsf(dL_dalpha[i])));
+		if (dL_ddepth) m = fmaxf(m, fabsf(dL_ddepth[i]));
+		if (dL_dalpha) m = fmaxf(m, fabsf(dL_dalpha[i]));
 	}
 #pragma unroll
 	for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));

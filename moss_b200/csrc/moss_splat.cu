@@ -367,7 +367,7 @@ int moss_rasterize_backward(void* stream_, const MossScene* sc, unsigned flags, 
 	if (!scene_valid(sc)) return MOSS_ERR_INVALID_ARGUMENT;
 	const int P = sc->P, W = sc->W, H = sc->H, N = W * H;
 	if (P == 0) return MOSS_OK;
-	if (!radii || !dL_dpix || !dL_ddepth || !dL_dalpha || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
+	if (!radii || !dL_dpix || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
 		!dL_dmean3D || !dL_dcov3D || (sc->shs && !dL_dsh) || (sc->scales && (!dL_dscale || !dL_drot)))
 		return MOSS_ERR_INVALID_ARGUMENT;
 	const ViewParams vp = make_view(sc);

@@ -58,6 +58,7 @@ def _f32c(t, name):
 
 # remembered instance counts so that the binning workspace is right-sized without a host sync
 _capacity_hint = {}
+_EMPTY = torch.Tensor([])       # the reference's placeholder for an absent optional input (DGR/.../__init__.py:200-210)
 
 # Segmented backward (checkpoint workspace, include/moss_splat.h MossScene.ckpt_ws): "auto" turns it on for images of
 # up to 4096 tiles, where a few deep tiles set the backward's duration; larger images have enough tiles to fill the
@@ -196,11 +197,11 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
     P, M, H, W = sc.P, sc.M, sc.H, sc.W
     dev = radii.device
     with torch.cuda.device(dev):
-        def _g(t, shape):
-            if t is None:
-                return torch.zeros(shape, dtype=torch.float32, device=dev)
+        def _g(t, shape, required=False):
+            if t is None:      # no gradient reaches this output: the ABI takes NULL for depth / alpha
+                return torch.zeros(shape, dtype=torch.float32, device=dev) if required else None
             return _f32c(t, "grad").expand(shape).contiguous() if tuple(t.shape) != tuple(shape) else _f32c(t, "grad")
-        grad_color = _g(grad_color, (3, H, W)); grad_depth = _g(grad_depth, (1, H, W)); grad_alpha = _g(grad_alpha, (1, H, W))
+        grad_color = _g(grad_color, (3, H, W), required=True); grad_depth = _g(grad_depth, (1, H, W)); grad_alpha = _g(grad_alpha, (1, H, W))
         has_sh = sc.shs is not None
         has_sr = sc.scales is not None
         lay, param_numel, zero_from, total = grad_layout(P, M, has_sh, has_sr)
@@ -223,7 +224,7 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
         stream = torch.cuda.current_stream(dev).cuda_stream
         status = lib.moss_rasterize_backward(
             stream, C.byref(sc), flags | st.flags, _ptr(radii),
-            grad_color.data_ptr(), grad_depth.data_ptr(), grad_alpha.data_ptr(),
+            grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha),
             _ptr(dmeans2D), _ptr(dconic), _ptr(dopacity), _ptr(dcolors), _ptr(dmeans3D), _ptr(dcov3D),
             _ptr(dsh) if has_sh else None, _ptr(dscales) if has_sr else None, _ptr(drot) if has_sr else None)
         _abi.check(status, "moss_rasterize_backward")
@@ -246,6 +247,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.raster_settings = raster_settings
         ctx.num_rendered = st.num_rendered
         ctx.mark_non_differentiable(radii)
+        ctx.set_materialize_grads(False)       # an output nobody differentiates arrives as None, not as a zero image
         # The workspaces and the inputs whose device pointers sit in st.scene go through save_for_backward, like
         # the reference's three state tensors (DGR/diff_gaussian_rasterization/__init__.py:97): autograd frees
         # them right after the backward unless retain_graph is set.
@@ -296,7 +298,7 @@ class GaussianRasterizer(nn.Module):
         if ((scales is None or rotations is None) and cov3D_precomp is None) or \
                 ((scales is not None or rotations is not None) and cov3D_precomp is not None):
             raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
-        empty = torch.Tensor([])
+        empty = _EMPTY
         shs = empty if shs is None else shs
         colors_precomp = empty if colors_precomp is None else colors_precomp
         scales = empty if scales is None else scales

@@ -31,8 +31,8 @@ def compute(t):
     return [c, dp, a, r, m2.grad] + [t[k].grad for k in names]
 
 
-def d2h(res):
-    for j, r in enumerate(res):
+def d2h(res, base=0):
+    for j, r in enumerate(res, base):
         if j not in out_host:
             out_host[j] = torch.empty(r.shape, dtype=r.dtype, pin_memory=True)
         out_host[j].copy_(r.detach(), non_blocking=True)
@@ -54,7 +54,24 @@ res0 = compute({k: devt[k].detach().requires_grad_(True) for k in names})
 timeit("h2d only", h2d)
 timeit("fwd+bwd (resident inputs)", lambda: compute({k: devt[k].detach().requires_grad_(True) for k in names}))
 timeit("d2h only", lambda: d2h(res0))
-timeit("d2h grads only", lambda: d2h(res0[4:]))
+timeit("d2h grads only", lambda: d2h(res0[4:], 4))
+def raw():
+    c, r, dp, a, st = M.forward_raw(devt["means3D"], devt.get("shs", E), devt.get("colors_precomp", E), devt["opacities"],
+                                    devt.get("scales", E), devt.get("rotations", E), devt.get("cov3D_precomp", E), rs)
+    M.backward_raw(st, r, gc, gd, ga)
+
+
+def fwd_only():
+    t = {k: devt[k].detach().requires_grad_(True) for k in names}
+    m2 = torch.zeros_like(t["means3D"], requires_grad=True)
+    return rast(means3D=t["means3D"], means2D=m2, shs=t.get("shs"), colors_precomp=t.get("colors_precomp"),
+                opacities=t["opacities"], scales=t.get("scales"), rotations=t.get("rotations"), cov3D_precomp=t.get("cov3D_precomp"))
+
+
+E = torch.empty(0, device=dev)
+timeit("forward_raw + backward_raw", raw)
+timeit("public forward only", fwd_only)
+timeit("requires_grad_ x4 + zeros_like", lambda: ({k: devt[k].detach().requires_grad_(True) for k in names}, torch.zeros_like(devt["means3D"], requires_grad=True)))
 timeit("h2d + fwd+bwd", lambda: compute(h2d()))
 timeit("all three", lambda: d2h(compute(h2d())))
 for k in names:
