@@ -48,6 +48,7 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict_
 	__syncthreads();
 	// per-tile totals; the sub-counters become the scatter cursors (exclusive prefix inside the tile's segment);
 	// size-class histogram
+	uint32_t c_first = 0u;     // total of tile threadIdx.x, kept in a register (images of up to 1024 tiles never re-read)
 	for (int t = threadIdx.x; t < T; t += SCAN_THREADS) {
 		uint4* sub = reinterpret_cast<uint4*>(tile_count + (size_t)t * TILE_SUB);
 		static_assert(TILE_SUB == 8, "two uint4 per tile");
@@ -58,6 +59,7 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict_
 		const uint32_t c = pb.w + b.w;
 		sub[0] = pa; sub[1] = pb;
 		tile_total[t] = c;
+		if (t == (int)threadIdx.x) c_first = c;
 		atomicAdd(&bucket_n[order_bucket(c)], 1u);
 	}
 	__syncthreads();
@@ -79,13 +81,13 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict_
 	}
 	__syncthreads();
 	for (int t = threadIdx.x; t < T; t += SCAN_THREADS)
-		tile_order[atomicAdd(&bucket_n[order_bucket(tile_total[t])], 1u)] = (uint32_t)t;
+		tile_order[atomicAdd(&bucket_n[order_bucket(t == (int)threadIdx.x ? c_first : tile_total[t])], 1u)] = (uint32_t)t;
 	__syncthreads();
 	// classes 1..3 never occur (count 1 maps to class 4), so the offset of class 1 is the number of non-empty tiles
 	const uint32_t busy = bucket_n[1];
 	for (int base = 0; base < T; base += SCAN_THREADS) {
 		const int t = base + threadIdx.x;
-		const uint32_t c = (t < T) ? tile_total[t] : 0u;
+		const uint32_t c = (t < T) ? (base == 0 ? c_first : tile_total[t]) : 0u;
 		uint32_t v = c;
 #pragma unroll
 		for (int o = 1; o < 32; o <<= 1) {
@@ -130,13 +132,15 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict_
 // lanes at once instead of one lane waiting for each returned slot in turn -- that serial chain of L2 round trips
 // of the LARGEST splat used to set this launch's duration (22 us at ZJU shape).
 // The exclusive start of tile t (ranges[t].x) is only meaningful for non-empty tiles, which is all the scatter asks for.
-__global__ void __launch_bounds__(256)
+constexpr int SCATTER_THREADS = 128;
+
+__global__ void __launch_bounds__(SCATTER_THREADS)
 scatter_keys_kernel(int P, int grid_x, const int* __restrict__ radii, GeomWS g,
 	const uint2* __restrict__ ranges, uint32_t* __restrict__ cursor, const uint32_t* __restrict__ counters,
 	unsigned long long* __restrict__ keys)
 {
 	const unsigned full = 0xffffffffu;
-	const int idx = blockIdx.x * 256 + threadIdx.x;
+	const int idx = blockIdx.x * SCATTER_THREADS + threadIdx.x;
 	const int lane = threadIdx.x & 31;
 	if (counters[1]) return;          // binning buffer too small: host re-runs with a larger one (uniform exit)
 	const bool vis = idx < P && radii[idx] > 0;

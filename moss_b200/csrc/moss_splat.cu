@@ -310,7 +310,7 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 	}
 
 	{ MOSS_STAGE(MOSS_STAGE_SCATTER, stream);
-	scatter_keys_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, vp.grid_x, radii, g, im.ranges, im.tile_count,
+	scatter_keys_kernel<<<(P + SCATTER_THREADS - 1) / SCATTER_THREADS, SCATTER_THREADS, 0, stream>>>(P, vp.grid_x, radii, g, im.ranges, im.tile_count,
 		im.counters, b.keys); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_TILE_SORT, stream);
