@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MOSS_ABI_VERSION 7
+#define MOSS_ABI_VERSION 8
 
 /* status codes */
 #define MOSS_OK                  0
@@ -159,6 +159,12 @@ int moss_skin_backward(void* stream, const MossSkin* skin, const float* g_means3
                        float* d_A_tgt, float* d_poseoff_tgt);
 size_t moss_sizeof_skin(void);
 
+/* Nearest SMPL vertex of every Gaussian: replaces the knn_cuda call `self.knn(smpl_pts.float(), query_pts.float())`
+ * with KNN(k=1, transpose_mode=True) (scene/gaussian_model.py:85, :827 -> vert_ids; :657 -> distance).  Exhaustive
+ * search, smallest squared distance, lowest index on ties.  xyz [P,3], verts [V,3] -> vert_ids int32 [P] and,
+ * optionally (NULL to skip), dist float [P] (Euclidean).  V >= 1. */
+int moss_nearest_vertex(void* stream, int P, const float* xyz, int V, const float* verts, int* vert_ids, float* dist);
+
 /* Data-parallel exchange step (no reference counterpart: MOSS trains on one GPU).  Sum, in
  * place and on every rank, `numel` floats starting `offset_floats` (multiple of 4) into a SYMMETRIC buffer: the same
  * allocation made on each of `world` (<= 8) GPUs of one node and mapped into every process (CUDA IPC / fabric handles,
@@ -212,7 +218,8 @@ long long moss_export_state(void* stream, const MossScene* scene, int which, voi
 #define MOSS_STAGE_SKIN            8
 #define MOSS_STAGE_SKIN_BWD        9
 #define MOSS_STAGE_PEER_REDUCE     10
-#define MOSS_STAGE_COUNT           11
+#define MOSS_STAGE_NEAREST         11
+#define MOSS_STAGE_COUNT           12
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

@@ -19,6 +19,7 @@
 #include "binning.cuh"
 #include "blend.cuh"
 #include "skin.cuh"
+#include "nearest.cuh"
 #include "peer_reduce.cuh"
 
 using namespace moss;
@@ -201,7 +202,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -543,6 +544,18 @@ int moss_skin_backward(void* stream_, const MossSkin* k, const float* g_means3D,
 	{ MOSS_STAGE(MOSS_STAGE_SKIN_BWD, stream);
 		skin_backward_kernel<<<(k->P + SKIN_THREADS - 1) / SKIN_THREADS, SKIN_THREADS, 0, stream>>>(
 			make_skin(k), g_means3D, g_cov3D, d_xyz, d_scaling, d_rotation, d_lbs_delta, d_A_tgt, d_poseoff_tgt); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+int moss_nearest_vertex(void* stream_, int P, const float* xyz, int V, const float* verts, int* vert_ids, float* dist)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (P < 0 || V < 1) return MOSS_ERR_INVALID_ARGUMENT;
+	if (P == 0) return MOSS_OK;
+	if (!xyz || !verts || !vert_ids) return MOSS_ERR_INVALID_ARGUMENT;
+	{ MOSS_STAGE(MOSS_STAGE_NEAREST, stream);
+		nearest_vertex_kernel<<<(P + 31) / 32, NEAR_THREADS, 0, stream>>>(P, xyz, V, verts, vert_ids, dist); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }

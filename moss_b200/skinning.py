@@ -253,3 +253,26 @@ def skin_and_covariance(xyz, vert_ids, weights, ft: FrameTables, scaling=None, r
                                              weights, ft.A_big, ft.poseoff_big, ft.shapeoff, ft.R, ft.Th,
                                              scaling_modifier, return_transl)
     return m, (c if c.numel() else None), tr, bw, (tl if return_transl else None)
+
+
+def nearest_vertex(xyz, t_vertices, return_distance=False):
+    """int32 [P]: index of the nearest SMPL vertex of every Gaussian -- what the reference asks knn_cuda for on every
+    render, ``_, vert_ids = self.knn(smpl_pts.float(), query_pts.float())`` with ``KNN(k=1, transpose_mode=True)``
+    (scene/gaussian_model.py:85, :827).  ``xyz`` [P,3] or [1,P,3], ``t_vertices`` [V,3] or [1,V,3] (the big-pose world
+    vertices).  With ``return_distance`` also the Euclidean distance [P] (``distance, _ = self.knn(...)``, :657).
+    Gaussians move little between densifications, so a training loop may keep the result and refresh it only when the
+    set of Gaussians changes."""
+    lib = _abi.load()
+    q = _dev_f32(xyz.detach().reshape(-1, 3), "xyz")
+    v = _dev_f32(t_vertices.detach().reshape(-1, 3), "t_vertices")
+    if v.device != q.device:
+        raise RuntimeError("xyz and t_vertices must be on the same device")
+    P, V = q.shape[0], v.shape[0]
+    if V < 1:
+        raise RuntimeError("t_vertices is empty")
+    ids = torch.empty((P,), dtype=torch.int32, device=q.device)
+    dist = torch.empty((P,), dtype=torch.float32, device=q.device) if return_distance else None
+    with torch.cuda.device(q.device):
+        status = lib.moss_nearest_vertex(torch.cuda.current_stream(q.device).cuda_stream, P, _p(q), V, _p(v), _p(ids), _p(dist))
+    _abi.check(status, "moss_nearest_vertex")
+    return (ids, dist) if return_distance else ids

@@ -28,7 +28,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_versions_and_strings(lib):
-    assert lib.moss_abi_version() == 7
+    assert lib.moss_abi_version() == 8
     assert lib.moss_error_string(0) == b"ok"
     assert b"binning" in lib.moss_error_string(_abi.MOSS_ERR_BINNING_OVERFLOW)
 
@@ -66,6 +66,16 @@ def test_skin_entry_points_validate_without_a_gpu(lib):
     assert lib.moss_skin_backward(None, C.byref(k), *([None] * 8)) == _abi.MOSS_ERR_INVALID_ARGUMENT
     k.P, k.V = 0, 6890       # empty input: nothing to launch, no accumulators requested
     assert lib.moss_skin_forward(None, C.byref(k), None, None, None, None, None) == _abi.MOSS_OK
+
+
+def test_nearest_vertex_entry_point_validates_without_a_gpu(lib):
+    assert lib.moss_nearest_vertex(None, 4, None, 0, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT    # no vertices
+    assert lib.moss_nearest_vertex(None, 4, None, 10, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT   # NULL arrays
+    assert lib.moss_nearest_vertex(None, 0, None, 10, None, None, None) == _abi.MOSS_OK                     # nothing to do
+    from moss_b200 import skinning as K
+    import torch
+    with pytest.raises(RuntimeError):
+        K.nearest_vertex(torch.zeros(3, 3), torch.zeros(5, 3))      # no CPU path
 
 
 def test_skinning_host_tables_match_oracle_and_refuse_cpu_compute():

@@ -138,3 +138,49 @@ def test_skin_then_rasterize_end_to_end():
     assert float((color.cpu() - fw.color).abs().mean()) < 1e-5
     for a, b in ((xyz.grad, xyz_c.grad), (sc.grad, sc_c.grad), (rot.grad, rot_c.grad)):
         assert _rel(a, b) < 2e-2      # pixel-test flips dominate; tight checks are in the two tests above
+
+
+# ---- nearest SMPL vertex (replaces the knn_cuda call at scene/gaussian_model.py:827) ---------------------------------
+def _check_nearest(q, v, ids, dist=None):
+    """ids must attain the minimum distance (fp64), and where the fp64 argmin differs the two candidates are tied to
+    fp32 resolution; on exact ties the lowest index wins."""
+    from oracle import lbs_oracle as L
+    ref = L.nearest_vertex(v.cpu(), q.cpu())
+    ids = ids.cpu().long()
+    assert ids.min() >= 0 and ids.max() < v.shape[0]
+    dd = torch.cdist(q.cpu().double(), v.cpu().double())
+    d_ours = dd.gather(1, ids[:, None])[:, 0]
+    d_ref = dd.gather(1, ref[:, None])[:, 0]
+    differ = ids != ref
+    assert float(differ.float().mean()) < 1e-3
+    assert torch.all(d_ours[differ] <= d_ref[differ] * (1 + 1e-6) + 1e-12)
+    if dist is not None:
+        assert torch.allclose(dist.cpu().double(), d_ours, rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("name", LBS_CASES)
+def test_nearest_vertex_matches_reference_golden(name):
+    """The golden files hold the vert_ids the REAL coarse_deform_c2source used (exact k=1 search)."""
+    d, ft, body = load_case(name)
+    ids = K.nearest_vertex(d["xyz"].to(DEV)[None], body.verts.to(DEV)[None])
+    assert ids.dtype == torch.int32
+    assert torch.equal(ids.cpu(), d["vert_ids"].to(torch.int32).cpu())
+
+
+@pytest.mark.parametrize("P,V", [(1, 1), (129, 1023), (1000, 1025), (20000, 6890), (5, 2500)])
+def test_nearest_vertex_matches_oracle(P, V):
+    g = torch.Generator().manual_seed(P * 7919 + V)
+    v = torch.randn(V, 3, generator=g)
+    q = v[torch.randint(0, V, (P,), generator=g)] + 0.05 * torch.randn(P, 3, generator=g)
+    ids, dist = K.nearest_vertex(q.to(DEV), v.to(DEV), return_distance=True)
+    _check_nearest(q, v, ids, dist)
+
+
+def test_nearest_vertex_ties_take_the_lowest_index():
+    v = torch.tensor([[0., 0., 0.], [1., 0., 0.], [1., 0., 0.], [1., 0., 0.], [1., 0., 0.], [1., 0., 0.], [-1., 0., 0.]])
+    v = torch.cat([v, v + 10.0])                           # 14 vertices: duplicates across the 4-way unroll
+    q = torch.tensor([[1., 0., 0.], [0.9, 0., 0.], [0., 0., 0.], [11., 10., 10.], [-1.2, 0., 0.]])
+    ids = K.nearest_vertex(q.to(DEV), v.to(DEV)).cpu().tolist()
+    assert ids == [1, 1, 0, 8, 6]
+    # equidistant from vertex 0 and vertex 1 (exactly representable): lowest index
+    assert K.nearest_vertex(torch.tensor([[0.5, 0., 0.]], device=DEV), v.to(DEV)).item() == 0
