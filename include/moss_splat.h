@@ -159,6 +159,14 @@ int moss_skin_backward(void* stream, const MossSkin* skin, const float* g_means3
                        float* d_A_tgt, float* d_poseoff_tgt);
 size_t moss_sizeof_skin(void);
 
+/* Densification statistics of one iteration, for the Gaussians with radii > 0 (the reference's visibility_filter,
+ * gaussian_renderer/__init__.py:128): max_radii2D = max(max_radii2D, radii) (train_ZJU.py:173), xyz_gradient_accum +=
+ * |dL_dmean2D[:, :2]|, denom += 1 (GaussianModel.add_densification_stats, scene/gaussian_model.py:816-818).  All
+ * float [P] (the reference's [P,1] tensors are the same memory), updated in place; any of the three may be NULL.
+ * dL_dmean2D [P,3] is the backward's screen-space gradient (viewspace_point_tensor.grad). */
+int moss_densify_stats(void* stream, int P, const int* radii, const float* dL_dmean2D, float* xyz_gradient_accum,
+                       float* denom, float* max_radii2D);
+
 /* Nearest SMPL vertex of every Gaussian: replaces the knn_cuda call `self.knn(smpl_pts.float(), query_pts.float())`
  * with KNN(k=1, transpose_mode=True) (scene/gaussian_model.py:85, :827 -> vert_ids; :657 -> distance).  Exhaustive
  * search, smallest squared distance, lowest index on ties.  xyz [P,3], verts [V,3] -> vert_ids int32 [P] and,
@@ -219,7 +227,8 @@ long long moss_export_state(void* stream, const MossScene* scene, int which, voi
 #define MOSS_STAGE_SKIN_BWD        9
 #define MOSS_STAGE_PEER_REDUCE     10
 #define MOSS_STAGE_NEAREST         11
-#define MOSS_STAGE_COUNT           12
+#define MOSS_STAGE_DENSIFY_STATS   12
+#define MOSS_STAGE_COUNT           13
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

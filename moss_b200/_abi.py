@@ -34,9 +34,9 @@ SYMBOLS = [
     "moss_rasterize_backward", "moss_mark_visible", "moss_export_state", "moss_abi_version",
     "moss_error_string", "moss_last_cuda_error", "moss_sizeof_scene", "moss_kernel_launches",
     "moss_profile_enable", "moss_profile_read", "moss_stage_name",
-    "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_peer_signal_bytes", "moss_peer_allreduce",
+    "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_peer_signal_bytes", "moss_peer_allreduce",
 ]
-STAGE_COUNT = 12
+STAGE_COUNT = 13
 
 
 class MossScene(C.Structure):
@@ -119,6 +119,8 @@ def load():
     lib.moss_peer_allreduce.restype = C.c_int
     lib.moss_peer_allreduce.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, vp, vp]
     lib.moss_sizeof_skin.restype = C.c_size_t
+    lib.moss_densify_stats.restype = C.c_int
+    lib.moss_densify_stats.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp]
     lib.moss_nearest_vertex.restype = C.c_int
     lib.moss_nearest_vertex.argtypes = [vp, C.c_int, vp, C.c_int, vp, vp, vp]
     lib.moss_skin_forward.restype = C.c_int

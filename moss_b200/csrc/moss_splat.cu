@@ -20,6 +20,7 @@
 #include "blend.cuh"
 #include "skin.cuh"
 #include "nearest.cuh"
+#include "densify.cuh"
 #include "peer_reduce.cuh"
 
 using namespace moss;
@@ -202,7 +203,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -556,6 +557,19 @@ int moss_nearest_vertex(void* stream_, int P, const float* xyz, int V, const flo
 	if (!xyz || !verts || !vert_ids) return MOSS_ERR_INVALID_ARGUMENT;
 	{ MOSS_STAGE(MOSS_STAGE_NEAREST, stream);
 		nearest_vertex_kernel<<<(P + 31) / 32, NEAR_THREADS, 0, stream>>>(P, xyz, V, verts, vert_ids, dist); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+int moss_densify_stats(void* stream_, int P, const int* radii, const float* dL_dmean2D, float* xyz_gradient_accum,
+	float* denom, float* max_radii2D)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (P < 0) return MOSS_ERR_INVALID_ARGUMENT;
+	if (P == 0) return MOSS_OK;
+	if (!radii || (xyz_gradient_accum && !dL_dmean2D)) return MOSS_ERR_INVALID_ARGUMENT;
+	{ MOSS_STAGE(MOSS_STAGE_DENSIFY_STATS, stream);
+		densify_stats_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, radii, dL_dmean2D, xyz_gradient_accum, denom, max_radii2D); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }

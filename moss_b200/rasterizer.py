@@ -335,3 +335,34 @@ def export_state(st, name):
 def export_state_counters(st):
     """int32[4] on the host side of a sync: num_rendered, overflow flag, capacity, non-empty tiles."""
     return export_state(st, "counters").cpu()
+
+
+def add_densification_stats(radii, viewspace_grad, xyz_gradient_accum=None, denom=None, max_radii2D=None):
+    """In place, for the Gaussians with ``radii > 0`` (the reference's visibility_filter): ``max_radii2D = max(max_radii2D,
+    radii)`` (train_ZJU.py:173), ``xyz_gradient_accum += |viewspace_grad[:, :2]|`` and ``denom += 1``
+    (GaussianModel.add_densification_stats, scene/gaussian_model.py:816-818) -- one kernel, no boolean-mask indexing
+    (each of the reference's three masked updates synchronises the host through ``nonzero``).
+    ``viewspace_grad`` is ``viewspace_point_tensor.grad`` ([P,3] float32); the statistics are float32 [P] or [P,1]."""
+    lib = _abi.load()
+    if not radii.is_cuda:
+        raise RuntimeError("moss_b200 needs CUDA tensors (there is no CPU path)")
+    P = radii.shape[0]
+    if radii.dtype != torch.int32 or not radii.is_contiguous():
+        raise RuntimeError("radii must be a contiguous int32 tensor (as returned by the rasterizer)")
+
+    def stat(t, name):
+        if t is None:
+            return None
+        if t.dtype != torch.float32 or not t.is_contiguous() or t.numel() != P or t.device != radii.device:
+            raise RuntimeError(f"{name} must be a contiguous float32 tensor with one entry per Gaussian on the device of radii")
+        return t
+    acc, den, mx = stat(xyz_gradient_accum, "xyz_gradient_accum"), stat(denom, "denom"), stat(max_radii2D, "max_radii2D")
+    g = None
+    if acc is not None:
+        g = _f32c(viewspace_grad, "viewspace_grad")
+        if g.shape != (P, 3) or g.device != radii.device:
+            raise RuntimeError("viewspace_grad must be [P,3] on the device of radii")
+    with torch.cuda.device(radii.device):
+        status = lib.moss_densify_stats(torch.cuda.current_stream(radii.device).cuda_stream, P, _ptr(radii), _ptr(g),
+                                        _ptr(acc), _ptr(den), _ptr(mx))
+    _abi.check(status, "moss_densify_stats")

@@ -78,6 +78,15 @@ def test_nearest_vertex_entry_point_validates_without_a_gpu(lib):
         K.nearest_vertex(torch.zeros(3, 3), torch.zeros(5, 3))      # no CPU path
 
 
+def test_densify_stats_entry_point_validates_without_a_gpu(lib):
+    assert lib.moss_densify_stats(None, 4, None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT   # no radii
+    assert lib.moss_densify_stats(None, -1, None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    assert lib.moss_densify_stats(None, 0, None, None, None, None, None) == _abi.MOSS_OK
+    import moss_b200 as M
+    with pytest.raises(RuntimeError):
+        M.add_densification_stats(torch.zeros(3, dtype=torch.int32), torch.zeros(3, 3))      # no CPU path
+
+
 def test_skinning_host_tables_match_oracle_and_refuse_cpu_compute():
     """frame_tables (host logic, torch) == the oracle's restatement of the reference; the per-Gaussian kernel has no
     CPU path."""
