@@ -167,6 +167,24 @@ size_t moss_sizeof_skin(void);
 int moss_densify_stats(void* stream, int P, const int* radii, const float* dL_dmean2D, float* xyz_gradient_accum,
                        float* denom, float* max_radii2D);
 
+/* Fused AdamW step over up to 8 parameter groups in ONE launch.  Replaces `gaussians.optimizer.step()` for the
+ * per-Gaussian groups of `torch.optim.AdamW(l, lr=0.0, eps=1e-15)` (scene/gaussian_model.py:203-225, train_ZJU.py:189);
+ * same arithmetic and order as torch/optim/adam.py::_single_tensor_adam with decoupled weight decay, amsgrad and
+ * maximize off.  `step` is the 1-based step count AFTER this update (torch increments before using it).  All arrays
+ * float32 [numel], updated in place (grad is read only). */
+typedef struct MossAdamGroup {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    size_t numel;
+    double lr;          /* hyper-parameters are doubles, like the Python floats torch derives its scalars from: */
+    int step;           /* 1 - beta2 formed from a float beta2 would be off by 1e-5 relative */
+} MossAdamGroup;
+int moss_adamw_step(void* stream, int n_groups, const MossAdamGroup* groups, double beta1, double beta2, double eps,
+                    double weight_decay);
+size_t moss_sizeof_adam_group(void);
+
 /* Nearest SMPL vertex of every Gaussian: replaces the knn_cuda call `self.knn(smpl_pts.float(), query_pts.float())`
  * with KNN(k=1, transpose_mode=True) (scene/gaussian_model.py:85, :827 -> vert_ids; :657 -> distance).  Exhaustive
  * search, smallest squared distance, lowest index on ties.  xyz [P,3], verts [V,3] -> vert_ids int32 [P] and,
@@ -228,7 +246,8 @@ long long moss_export_state(void* stream, const MossScene* scene, int which, voi
 #define MOSS_STAGE_PEER_REDUCE     10
 #define MOSS_STAGE_NEAREST         11
 #define MOSS_STAGE_DENSIFY_STATS   12
-#define MOSS_STAGE_COUNT           13
+#define MOSS_STAGE_ADAMW           13
+#define MOSS_STAGE_COUNT           14
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

@@ -34,9 +34,9 @@ SYMBOLS = [
     "moss_rasterize_backward", "moss_mark_visible", "moss_export_state", "moss_abi_version",
     "moss_error_string", "moss_last_cuda_error", "moss_sizeof_scene", "moss_kernel_launches",
     "moss_profile_enable", "moss_profile_read", "moss_stage_name",
-    "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_peer_signal_bytes", "moss_peer_allreduce",
+    "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
 ]
-STAGE_COUNT = 13
+STAGE_COUNT = 14
 
 
 class MossScene(C.Structure):
@@ -53,6 +53,11 @@ class MossScene(C.Structure):
         ("binning_ws", C.c_void_p), ("binning_bytes", C.c_size_t),
         ("ckpt_ws", C.c_void_p), ("ckpt_bytes", C.c_size_t),
     ]
+
+
+class MossAdamGroup(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("numel", C.c_size_t), ("lr", C.c_double), ("step", C.c_int)]
 
 
 class MossSkin(C.Structure):
@@ -119,6 +124,9 @@ def load():
     lib.moss_peer_allreduce.restype = C.c_int
     lib.moss_peer_allreduce.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, vp, vp]
     lib.moss_sizeof_skin.restype = C.c_size_t
+    lib.moss_adamw_step.restype = C.c_int
+    lib.moss_adamw_step.argtypes = [vp, C.c_int, C.POINTER(MossAdamGroup), C.c_double, C.c_double, C.c_double, C.c_double]
+    lib.moss_sizeof_adam_group.restype = C.c_size_t
     lib.moss_densify_stats.restype = C.c_int
     lib.moss_densify_stats.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp]
     lib.moss_nearest_vertex.restype = C.c_int
@@ -127,6 +135,8 @@ def load():
     lib.moss_skin_forward.argtypes = [vp, C.POINTER(MossSkin)] + [vp] * 5
     lib.moss_skin_backward.restype = C.c_int
     lib.moss_skin_backward.argtypes = [vp, C.POINTER(MossSkin)] + [vp] * 8
+    if lib.moss_sizeof_adam_group() != C.sizeof(MossAdamGroup):
+        raise RuntimeError("MossAdamGroup layout differs between include/moss_splat.h and moss_b200/_abi.py")
     if lib.moss_sizeof_skin() != C.sizeof(MossSkin):
         raise RuntimeError("moss_b200: MossSkin layout mismatch between _abi.py and the library; rebuild")
     if lib.moss_sizeof_scene() != C.sizeof(MossScene):

@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <math.h>
 #include <mutex>
 #include <atomic>
 #include <vector>
@@ -21,6 +22,7 @@
 #include "skin.cuh"
 #include "nearest.cuh"
 #include "densify.cuh"
+#include "adamw.cuh"
 #include "peer_reduce.cuh"
 
 using namespace moss;
@@ -203,7 +205,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -570,6 +572,40 @@ int moss_densify_stats(void* stream_, int P, const int* radii, const float* dL_d
 	if (!radii || (xyz_gradient_accum && !dL_dmean2D)) return MOSS_ERR_INVALID_ARGUMENT;
 	{ MOSS_STAGE(MOSS_STAGE_DENSIFY_STATS, stream);
 		densify_stats_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, radii, dL_dmean2D, xyz_gradient_accum, denom, max_radii2D); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+size_t moss_sizeof_adam_group(void) { return sizeof(MossAdamGroup); }
+
+int moss_adamw_step(void* stream_, int n_groups, const MossAdamGroup* groups, double beta1, double beta2, double eps,
+	double weight_decay)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (n_groups < 0 || n_groups > ADAM_MAX_GROUPS || (n_groups && !groups)) return MOSS_ERR_INVALID_ARGUMENT;
+	AdamGroups a;
+	memset(&a, 0, sizeof(a));
+	unsigned long long chunks = 0;
+	for (int i = 0; i < n_groups; i++) {
+		const MossAdamGroup& g = groups[i];
+		if (g.numel == 0) continue;
+		if (!g.param || !g.grad || !g.exp_avg || !g.exp_avg_sq || g.step < 1) return MOSS_ERR_INVALID_ARGUMENT;
+		const int k = a.n++;
+		a.param[k] = g.param; a.grad[k] = g.grad; a.exp_avg[k] = g.exp_avg; a.exp_avg_sq[k] = g.exp_avg_sq;
+		a.numel[k] = g.numel;
+		chunks += (g.numel + ADAM_CHUNK - 1) / ADAM_CHUNK;
+		if (chunks > 0x7fffffffull) return MOSS_ERR_INVALID_ARGUMENT;
+		a.chunk_end[k] = (unsigned)chunks;
+		// the scalars in double, like the Python floats torch derives them from
+		const double lr = g.lr;
+		a.decay[k] = (float)(1.0 - lr * weight_decay);
+		a.step_size[k] = (float)(lr / (1.0 - pow(beta1, (double)g.step)));
+		a.bc2_sqrt[k] = (float)sqrt(1.0 - pow(beta2, (double)g.step));
+	}
+	if (a.n == 0) return MOSS_OK;
+	a.w1 = (float)(1.0 - beta1); a.beta2 = (float)beta2; a.w2 = (float)(1.0 - beta2); a.eps = (float)eps;
+	{ MOSS_STAGE(MOSS_STAGE_ADAMW, stream);
+		adamw_kernel<<<(unsigned)chunks, 256, 0, stream>>>(a); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }

@@ -87,6 +87,23 @@ def test_densify_stats_entry_point_validates_without_a_gpu(lib):
         M.add_densification_stats(torch.zeros(3, dtype=torch.int32), torch.zeros(3, 3))      # no CPU path
 
 
+def test_adamw_entry_point_validates_without_a_gpu(lib):
+    assert lib.moss_sizeof_adam_group() == C.sizeof(_abi.MossAdamGroup)
+    g = (_abi.MossAdamGroup * 2)()
+    g[0].numel, g[0].lr, g[0].step = 16, 0.1, 1                 # NULL arrays
+    assert lib.moss_adamw_step(None, 2, g, 0.9, 0.999, 1e-15, 0.01) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    assert lib.moss_adamw_step(None, 9, g, 0.9, 0.999, 1e-15, 0.01) == _abi.MOSS_ERR_INVALID_ARGUMENT     # > 8 groups
+    g[0].numel = 0                                             # only empty groups: nothing to launch
+    assert lib.moss_adamw_step(None, 2, g, 0.9, 0.999, 1e-15, 0.01) == _abi.MOSS_OK
+    from moss_b200.optim import FusedAdamW
+    w = torch.nn.Parameter(torch.zeros(4))
+    opt = FusedAdamW([{"params": [w], "lr": 0.1, "name": "xyz"}], lr=0.0, eps=1e-15)
+    assert opt.param_groups[0]["name"] == "xyz" and opt.param_groups[0]["weight_decay"] == 1e-2
+    w.grad = torch.ones(4)
+    with pytest.raises(RuntimeError):
+        opt.step()                                             # no CPU path
+
+
 def test_skinning_host_tables_match_oracle_and_refuse_cpu_compute():
     """frame_tables (host logic, torch) == the oracle's restatement of the reference; the per-Gaussian kernel has no
     CPU path."""
