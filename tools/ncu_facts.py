@@ -5,7 +5,7 @@ import collections, csv, io, json, os, subprocess, sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NAMES = ("preprocess_forward", "tile_scan", "scatter_keys", "tile_sort", "blend_forward", "blend_backward", "preprocess_backward",
-         "skin_forward", "skin_backward", "peer_allreduce")
+         "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw")
 FACTS = {"issue_active_pct": "smsp__issue_active.avg.pct_of_peak_sustained_active",
          "warps_active_pct": "sm__warps_active.avg.pct_of_peak_sustained_active",
          "pipe_fma_pct": "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
