@@ -51,7 +51,7 @@ nearest_vertex_kernel(int P, const float* __restrict__ xyz, int V, const float* 
 		const int m = min(NEAR_TILE, V - base);
 		__syncthreads();
 		for (int j = threadIdx.x; j < NEAR_TILE; j += NEAR_THREADS) {
-			float4 v = make_float4(0.f, 0.f, 0.f, INF);      // padding never wins (distance + inf)
+			float4 v = make_float4(INF, INF, INF, 0.f);      // padding never wins: (q - inf)^2 = inf
 			if (j < m) { const float* s = verts + 3 * (size_t)(base + j); v = make_float4(s[0], s[1], s[2], 0.f); }
 			tile[j] = v;
 		}
@@ -64,7 +64,7 @@ nearest_vertex_kernel(int P, const float* __restrict__ xyz, int V, const float* 
 				for (int u = 0; u < 4; u++) {
 					const float4 v = tile[j + u];
 					const float dx = __fsub_rn(qx, v.x), dy = __fsub_rn(qy, v.y), dz = __fsub_rn(qz, v.z);
-					const float d2 = __fadd_rn(__fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx))), v.w);
+					const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
 					// ascending scan inside one accumulator: a strict < keeps the lowest index of equal distances
 					const bool lt = d2 < bd[u];
 					bd[u] = lt ? d2 : bd[u];
