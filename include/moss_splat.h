@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MOSS_ABI_VERSION 8
+#define MOSS_ABI_VERSION 9
 
 /* status codes */
 #define MOSS_OK                  0
@@ -89,12 +89,24 @@ typedef struct MossScene {
     void* image_ws;  size_t image_bytes;   /* >= moss_image_workspace_bytes(W,H) */
     void* binning_ws; size_t binning_bytes; /* capacity derived with moss_binning_capacity() */
     void* ckpt_ws;   size_t ckpt_bytes;    /* optional (NULL/0 = off), >= moss_ckpt_workspace_bytes(capacity, W, H): the
-                                              forward stores per-pixel blend state every 256 instances of a tile so that
-                                              the backward walks a deep tile as independent 256-instance segments
+                                              forward stores per-pixel blend state every 128 instances of a tile so that
+                                              the backward walks a deep tile as independent 128-instance segments
                                               (shorter critical path at ZJU/MonoCap shapes).  Forward outputs are
                                               unaffected; gradients agree with the unsegmented walk to fp32 rounding.
                                               Must be the same buffer in the forward and the backward call. */
 } MossScene;
+
+/* One camera of a batched call: the per-view fields of GaussianRasterizationSettings
+ * (DGR/diff_gaussian_rasterization/__init__.py:160-172).  Image size, SH degree, scale modifier and `prefiltered` are
+ * shared by the batch and come from the MossScene. */
+#define MOSS_MAX_VIEWS 32
+typedef struct MossView {
+    const float* viewmatrix;     /* [16] device */
+    const float* projmatrix;     /* [16] device */
+    const float* campos;         /* [3]  device (may be NULL with colors_precomp) */
+    const float* bg;             /* [3]  device */
+    float tanfovx, tanfovy;
+} MossView;
 
 /* Forward.  Replaces CudaRasterizer::Rasterizer::forward (DGR/cuda_rasterizer/rasterizer.h:33-60,
  * rasterizer_impl.cu:198-341) and the torch glue RasterizeGaussiansCUDA (DGR/rasterize_points.cu:35-119).
@@ -118,6 +130,32 @@ int moss_rasterize_backward(void* stream, const MossScene* scene, unsigned flags
                             const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
                             float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                             float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot);
+
+/* Batched multi-view calls (no reference counterpart: MOSS renders one view per iteration, train_ZJU.py:93-100; SURVEY.md
+ * section 7 step 7 / BASELINE.json config 4).  ONE launch sequence renders `V` (1..MOSS_MAX_VIEWS) cameras of the SAME
+ * Gaussians: the view index is folded into the tile index (tile' = v*T + tile) and into the Gaussian index of the
+ * per-view state (id' = v*P + i), so every view's outputs -- radii, sorted lists, ranges, image -- are bit-identical to V
+ * separate single-view calls, while the blend kernels see V times the busy tiles (a single 512x512 body view fills
+ * ~1/4 of the GPU).  `scene` supplies the Gaussians, image size and workspaces (its viewmatrix / projmatrix / campos /
+ * bg / tanfov fields are ignored); workspaces are sized with the *_batch queries; the binning capacity counts the
+ * instances of all views together.  `views` is a HOST array.
+ *   forward : out_color [V,3,H,W], out_depth [V,H,W], out_alpha [V,H,W], radii int32 [V,P]; *num_rendered = total.
+ *   backward: dL_dpix [V,3,H,W], dL_ddepth / dL_dalpha [V,H,W] or NULL.  Per view: dL_dmean2D [V,P,3] and (optional,
+ *             NULL to skip) dL_dconic [V,P,4].  SUMMED over the views, in view order (reproducible): dL_dopacity [P],
+ *             dL_dcolor [P,3], dL_dmean3D [P,3], dL_dcov3D [P,6], dL_dsh [P,M,3], dL_dscale [P,3], dL_drot [P,4].
+ *             `tmp_ws` (>= moss_batch_grad_workspace_bytes, only needed for V > 1) holds the per-view rows. */
+size_t moss_geom_workspace_bytes_batch(int P, int V);
+size_t moss_image_workspace_bytes_batch(int W, int H, int V);
+size_t moss_ckpt_workspace_bytes_batch(long long capacity, int W, int H, int V);
+size_t moss_batch_grad_workspace_bytes(int P, int M, int V);
+int moss_rasterize_forward_batch(void* stream, const MossScene* scene, int V, const MossView* views, unsigned flags,
+                                 float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered);
+int moss_rasterize_backward_batch(void* stream, const MossScene* scene, int V, const MossView* views, unsigned flags,
+                                  const int* radii, const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+                                  float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                                  float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                  void* tmp_ws, size_t tmp_bytes);
+size_t moss_sizeof_view(void);
 
 /* markVisible.  Replaces CudaRasterizer::Rasterizer::markVisible (DGR/cuda_rasterizer/rasterizer.h:26-31,
  * rasterizer_impl.cu:54-66,141-153).  present: uint8[P]. */
@@ -226,6 +264,11 @@ int moss_peer_allreduce(void* stream, int rank, int world, void* const* buffer_p
 #define MOSS_STATE_FINAL_T       14 /* f32[W*H] */
 #define MOSS_STATE_COUNTERS      15 /* u32[4]: num_rendered, overflow flag, capacity, reserved */
 long long moss_export_state(void* stream, const MossScene* scene, int which, void* dst, long long max_bytes);
+/* The same for the workspaces of a batched call: per-Gaussian arrays are [V*P], per-pixel [V*W*H], ranges [V*tiles] with
+ * offsets into the batch's one sorted list (view v's instances are contiguous: MOSS_STATE_VIEW_BASE, u32[V+1]);
+ * MOSS_STATE_POINT_LIST holds id' = v*P + i. */
+#define MOSS_STATE_VIEW_BASE     16
+long long moss_export_state_batch(void* stream, const MossScene* scene, int V, int which, void* dst, long long max_bytes);
 
 /* Instrumentation (no reference counterpart: the reference only has cudaDeviceSynchronize-after-every-launch
  * debugging, DGR/cuda_rasterizer/auxiliary.h:166-173).
@@ -247,7 +290,8 @@ long long moss_export_state(void* stream, const MossScene* scene, int which, voi
 #define MOSS_STAGE_NEAREST         11
 #define MOSS_STAGE_DENSIFY_STATS   12
 #define MOSS_STAGE_ADAMW           13
-#define MOSS_STAGE_COUNT           14
+#define MOSS_STAGE_SUM_VIEWS       14
+#define MOSS_STAGE_COUNT           15
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

@@ -25,7 +25,8 @@ FLAG_NO_CULL = 32
 FLAG_SPLIT_SHIFT = 8          # bits 8-9: 0 auto, 1 whole-tile blocks, 2 half-tile, 3 quarter-tile
 
 STATE = dict(depths=0, clamped=1, means2D=2, cov3D=3, conic_opacity=4, rgb=5, tiles_touched=7,
-             keys_sorted=9, point_list=11, ranges=12, n_contrib=13, final_T=14, counters=15)
+             keys_sorted=9, point_list=11, ranges=12, n_contrib=13, final_T=14, counters=15, view_base=16)
+MAX_VIEWS = 32
 
 # every symbol include/moss_splat.h declares
 SYMBOLS = [
@@ -34,9 +35,12 @@ SYMBOLS = [
     "moss_rasterize_backward", "moss_mark_visible", "moss_export_state", "moss_abi_version",
     "moss_error_string", "moss_last_cuda_error", "moss_sizeof_scene", "moss_kernel_launches",
     "moss_profile_enable", "moss_profile_read", "moss_stage_name",
+    "moss_geom_workspace_bytes_batch", "moss_image_workspace_bytes_batch", "moss_ckpt_workspace_bytes_batch",
+    "moss_batch_grad_workspace_bytes", "moss_rasterize_forward_batch", "moss_rasterize_backward_batch", "moss_sizeof_view",
+    "moss_export_state_batch",
     "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
 ]
-STAGE_COUNT = 14
+STAGE_COUNT = 15
 
 
 class MossScene(C.Structure):
@@ -53,6 +57,11 @@ class MossScene(C.Structure):
         ("binning_ws", C.c_void_p), ("binning_bytes", C.c_size_t),
         ("ckpt_ws", C.c_void_p), ("ckpt_bytes", C.c_size_t),
     ]
+
+
+class MossView(C.Structure):
+    _fields_ = [("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p), ("bg", C.c_void_p),
+                ("tanfovx", C.c_float), ("tanfovy", C.c_float)]
 
 
 class MossAdamGroup(C.Structure):
@@ -124,6 +133,24 @@ def load():
     lib.moss_peer_allreduce.restype = C.c_int
     lib.moss_peer_allreduce.argtypes = [vp, C.c_int, C.c_int, vp, vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_uint, vp, vp]
     lib.moss_sizeof_skin.restype = C.c_size_t
+    lib.moss_geom_workspace_bytes_batch.restype = C.c_size_t
+    lib.moss_geom_workspace_bytes_batch.argtypes = [C.c_int, C.c_int]
+    lib.moss_image_workspace_bytes_batch.restype = C.c_size_t
+    lib.moss_image_workspace_bytes_batch.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.moss_ckpt_workspace_bytes_batch.restype = C.c_size_t
+    lib.moss_ckpt_workspace_bytes_batch.argtypes = [C.c_longlong, C.c_int, C.c_int, C.c_int]
+    lib.moss_batch_grad_workspace_bytes.restype = C.c_size_t
+    lib.moss_batch_grad_workspace_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    lib.moss_rasterize_forward_batch.restype = C.c_int
+    lib.moss_rasterize_forward_batch.argtypes = [vp, C.POINTER(MossScene), C.c_int, C.POINTER(MossView), C.c_uint, vp, vp, vp, vp,
+                                                 C.POINTER(C.c_int)]
+    lib.moss_rasterize_backward_batch.restype = C.c_int
+    lib.moss_rasterize_backward_batch.argtypes = [vp, C.POINTER(MossScene), C.c_int, C.POINTER(MossView), C.c_uint, vp] + [vp] * 12 + [vp, C.c_size_t]
+    lib.moss_export_state_batch.restype = C.c_longlong
+    lib.moss_export_state_batch.argtypes = [vp, C.POINTER(MossScene), C.c_int, C.c_int, vp, C.c_longlong]
+    lib.moss_sizeof_view.restype = C.c_size_t
+    if lib.moss_sizeof_view() != C.sizeof(MossView):
+        raise RuntimeError("moss_b200: MossView layout mismatch between _abi.py and the library; rebuild")
     lib.moss_adamw_step.restype = C.c_int
     lib.moss_adamw_step.argtypes = [vp, C.c_int, C.POINTER(MossAdamGroup), C.c_double, C.c_double, C.c_double, C.c_double]
     lib.moss_sizeof_adam_group.restype = C.c_size_t

@@ -26,29 +26,39 @@ __device__ __forceinline__ int order_bucket(uint32_t c)
 	return bits * 4 + sub;                                // 4..131
 }
 
-// One block.  ranges[t] = [first,last) (or (0,0) for an empty tile, as the reference's memset leaves it),
-// tile_count[t] <- 0 (re-used as the scatter cursor), counters = {R, R > capacity, capacity, busy tiles}.
-// host_R (mapped pinned host memory, may be null) also receives R so the host can read it without a
-// blocking copy.
-// tile_order[k] = the tile the k-th block of a blend launch works on: tiles in descending size class (a
-// counting sort over ORDER_BUCKETS log-scale classes), empty tiles last.  The hardware hands blocks to SMs in
-// index order, so the deepest tiles start first and the shallow ones fill in behind them (LPT scheduling);
-// with the natural order several deep tiles of the body's centre column land on one SM and the launch waits
-// for that SM while the others idle (ncu: sm__cycles_active.avg 37% of elapsed).
+// One block PER VIEW (grid = V).  Block v owns the tiles [v*T, (v+1)*T) of its view:
+// ranges[t'] = [first,last) into the global sorted list (or (0,0) for an empty tile, as the reference's memset leaves
+// it), tile_count[t'] <- the scatter cursors, view_busy[v] = its non-empty tiles, view_base[v] = its first instance.
+// The views are chained with a one-shot look-back: block v publishes (its instance total + 1) in view_sync[v] as soon
+// as it knows it and adds up the totals of the views before it (V <= 32 blocks, all resident at once).  The last view's
+// block writes counters = {R, R > capacity, capacity, ...}; host_R (mapped pinned host memory, may be null) also
+// receives R so the host can read it without a blocking copy.
+// tile_order[v*T + k] = the k-th tile (global index) of view v in descending size class (a counting sort over
+// ORDER_BUCKETS log-scale classes), empty tiles last.  Blend/sort block b works on view b % V, rank b / V: the hardware
+// hands blocks to SMs in index order, so the deepest tiles of every view start first and the shallow ones fill in behind
+// them (LPT scheduling); with the natural order several deep tiles of the body's centre column land on one SM and the
+// launch waits for that SM while the others idle (ncu: sm__cycles_active.avg 37% of elapsed).
 __global__ void __launch_bounds__(SCAN_THREADS)
-tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_total, uint2* __restrict__ ranges,
-	uint32_t* __restrict__ counters, uint32_t capacity, volatile int* host_R, uint32_t* __restrict__ tile_order)
+tile_scan_kernel(int T, int V, uint32_t* __restrict__ tile_count_all, uint32_t* __restrict__ tile_total_all, uint2* __restrict__ ranges_all,
+	uint32_t* __restrict__ counters, uint32_t capacity, volatile int* host_R, uint32_t* __restrict__ tile_order_all,
+	uint32_t* __restrict__ view_busy, uint32_t* __restrict__ view_base, uint32_t* __restrict__ view_sync)
 {
 	__shared__ uint32_t warp_sums[32];
 	__shared__ uint32_t carry_s;
 	__shared__ uint32_t bucket_n[ORDER_BUCKETS];
+	const int view = blockIdx.x;
+	const uint32_t tile0 = (uint32_t)view * (uint32_t)T;
+	uint32_t* tile_count = tile_count_all + (size_t)tile0 * TILE_SUB;
+	uint32_t* tile_total = tile_total_all + tile0;
+	uint2* ranges = ranges_all + tile0;
+	uint32_t* tile_order = tile_order_all + tile0;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	if (threadIdx.x == 0) carry_s = 0;
 	if (threadIdx.x < ORDER_BUCKETS) bucket_n[threadIdx.x] = 0;
 	__syncthreads();
 	// per-tile totals; the sub-counters become the scatter cursors (exclusive prefix inside the tile's segment);
-	// size-class histogram
+	// size-class histogram; the view's instance total
 	uint32_t c_first = 0u;     // total of tile threadIdx.x, kept in a register (images of up to 1024 tiles never re-read)
+	uint32_t my_sum = 0u;
 	for (int t = threadIdx.x; t < T; t += SCAN_THREADS) {
 		uint4* sub = reinterpret_cast<uint4*>(tile_count + (size_t)t * TILE_SUB);
 		static_assert(TILE_SUB == 8, "two uint4 per tile");
@@ -60,10 +70,18 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict_
 		sub[0] = pa; sub[1] = pb;
 		tile_total[t] = c;
 		if (t == (int)threadIdx.x) c_first = c;
+		my_sum += c;
 		atomicAdd(&bucket_n[order_bucket(c)], 1u);
 	}
+	my_sum = __reduce_add_sync(0xffffffffu, my_sum);
+	if (lane == 0) warp_sums[warp] = my_sum;
 	__syncthreads();
 	if (warp == 0) {
+		const uint32_t view_total = __reduce_add_sync(0xffffffffu, warp_sums[lane]);
+		if (lane == 0) {
+			__threadfence();
+			atomicExch(&view_sync[view], view_total + 1u);       // 0 = not known yet
+		}
 		// descending exclusive offsets: class 131 first ... class 0 (empty) last
 		uint32_t run = 0;
 		for (int base = ORDER_BUCKETS - 1; base >= 0; base -= 32) {
@@ -78,13 +96,39 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict_
 			if (bkt >= 0) bucket_n[bkt] = run + v - c;
 			run += __shfl_sync(0xffffffffu, v, 31);
 		}
+		// look-back: instances of the views before this one (lane u waits for view u)
+		uint32_t before = 0u;
+		if (lane < view) {
+			const volatile uint32_t* w = view_sync + lane;
+			uint32_t x;
+			while ((x = *w) == 0u) { }
+			before = x - 1u;
+		}
+		before = __reduce_add_sync(0xffffffffu, before);
+		if (lane == 0) {
+			carry_s = before;
+			view_base[view] = before;
+			if (view == V - 1) {
+				const uint32_t R = before + view_total;
+				view_base[V] = R;
+				counters[0] = R;
+				counters[1] = (R > capacity) ? 1u : 0u;
+				counters[2] = capacity;
+				counters[4] = 0u;       // backward segments / checkpoint records: handed out by tile_sort_kernel
+				counters[5] = 0u;
+				if (host_R) { *host_R = (int)R; __threadfence_system(); }
+			}
+		}
 	}
 	__syncthreads();
 	for (int t = threadIdx.x; t < T; t += SCAN_THREADS)
-		tile_order[atomicAdd(&bucket_n[order_bucket(t == (int)threadIdx.x ? c_first : tile_total[t])], 1u)] = (uint32_t)t;
+		tile_order[atomicAdd(&bucket_n[order_bucket(t == (int)threadIdx.x ? c_first : tile_total[t])], 1u)] = tile0 + (uint32_t)t;
 	__syncthreads();
 	// classes 1..3 never occur (count 1 maps to class 4), so the offset of class 1 is the number of non-empty tiles
-	const uint32_t busy = bucket_n[1];
+	if (threadIdx.x == 0) {
+		view_busy[view] = bucket_n[1];
+		if (view == 0) counters[3] = (V == 1) ? bucket_n[1] : 0u;     // per-view counts live in view_busy
+	}
 	for (int base = 0; base < T; base += SCAN_THREADS) {
 		const int t = base + threadIdx.x;
 		const uint32_t c = (t < T) ? (base == 0 ? c_first : tile_total[t]) : 0u;
@@ -115,16 +159,6 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict_
 		if (threadIdx.x == SCAN_THREADS - 1) carry_s = incl;
 		__syncthreads();
 	}
-	if (threadIdx.x == 0) {
-		const uint32_t R = carry_s;
-		counters[0] = R;
-		counters[1] = (R > capacity) ? 1u : 0u;
-		counters[2] = capacity;
-		counters[3] = busy;
-		counters[4] = 0u;       // backward segments / checkpoint records: handed out by tile_sort_kernel
-		counters[5] = 0u;
-		if (host_R) { *host_R = (int)R; __threadfence_system(); }
-	}
 }
 
 // K3.  A warp flattens the tile lists of its 32 Gaussians into one index space and every lane takes one
@@ -134,19 +168,23 @@ tile_scan_kernel(int T, uint32_t* __restrict__ tile_count, uint32_t* __restrict_
 // The exclusive start of tile t (ranges[t].x) is only meaningful for non-empty tiles, which is all the scatter asks for.
 constexpr int SCATTER_THREADS = 128;
 
+// grid = (ceil(P / SCATTER_THREADS), V)
 __global__ void __launch_bounds__(SCATTER_THREADS)
-scatter_keys_kernel(int P, int grid_x, const int* __restrict__ radii, GeomWS g,
+scatter_keys_kernel(int P, int grid_x, int T, const int* __restrict__ radii, GeomWS g,
 	const uint2* __restrict__ ranges, uint32_t* __restrict__ cursor, const uint32_t* __restrict__ counters,
 	unsigned long long* __restrict__ keys)
 {
 	const unsigned full = 0xffffffffu;
+	const int view = blockIdx.y;
 	const int idx = blockIdx.x * SCATTER_THREADS + threadIdx.x;
 	const int lane = threadIdx.x & 31;
 	if (counters[1]) return;          // binning buffer too small: host re-runs with a larger one (uniform exit)
-	const bool vis = idx < P && radii[idx] > 0;
+	const size_t vid = (size_t)view * P + idx;
+	const uint32_t tile0 = (uint32_t)view * (uint32_t)T;
+	const bool vis = idx < P && radii[vid] > 0;
 	ushort4 r = make_ushort4(0, 0, 0, 0);
 	uint32_t depth_bits = 0;
-	if (vis) { r = g.rect[idx]; depth_bits = __float_as_uint(g.depths[idx]); }
+	if (vis) { r = g.rect[vid]; depth_bits = __float_as_uint(g.depths[vid]); }
 	const uint32_t w = (uint32_t)r.z - (uint32_t)r.x;
 	const uint32_t cnt = vis ? w * ((uint32_t)r.w - (uint32_t)r.y) : 0u;
 	uint32_t incl = cnt;
@@ -157,6 +195,7 @@ scatter_keys_kernel(int P, int grid_x, const int* __restrict__ radii, GeomWS g,
 	}
 	const uint32_t total = __shfl_sync(full, incl, 31);
 	const uint32_t origin = (uint32_t)r.x | ((uint32_t)r.y << 16);
+	const uint32_t vid_lane0 = (uint32_t)(vid - lane);        // virtual ids fit 32 bits (checked by the host: V*P < 2^32)
 	for (uint32_t base = 0; base < total; base += 32) {
 		const uint32_t k = base + lane;
 		// owner = first lane whose inclusive count exceeds k (branch-free binary search over the lanes)
@@ -175,11 +214,13 @@ scatter_keys_kernel(int P, int grid_x, const int* __restrict__ radii, GeomWS g,
 		if (k < total) {
 			const uint32_t local = k - (o_incl - o_cnt);
 			const uint32_t ty = local / o_w, tx = local - ty * o_w;
-			const uint32_t t = ((o_origin >> 16) + ty) * (uint32_t)grid_x + (o_origin & 0xffffu) + tx;
+			const uint32_t t = tile0 + ((o_origin >> 16) + ty) * (uint32_t)grid_x + (o_origin & 0xffffu) + tx;
 			// the cursor of the sub-counter this warp counted into (preprocess: same warp <-> same 32 Gaussians)
 			const uint32_t sub = ((uint32_t)idx >> 5) & (TILE_SUB - 1);
-			const uint32_t slot = ranges[t].x + atomicAdd(&cursor[t * TILE_SUB + sub], 1u);
-			keys[slot] = ((unsigned long long)o_depth << 32) | (uint32_t)(idx - lane + owner);
+			const uint32_t slot = ranges[t].x + atomicAdd(&cursor[(size_t)t * TILE_SUB + sub], 1u);
+			// low word: the VIRTUAL Gaussian id (v*P + i): inside one view it orders like i, and the blend kernels
+			// gather the view's state rows with it directly
+			keys[slot] = ((unsigned long long)o_depth << 32) | (vid_lane0 + (uint32_t)owner);
 		}
 	}
 }

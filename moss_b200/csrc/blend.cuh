@@ -116,7 +116,7 @@ __device__ __forceinline__ int compact_hits(const uint8_t* mask, uint8_t* hits, 
 
 template <bool CULL, int NW>
 __global__ void __launch_bounds__(32 * NW)
-blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b, CkptWS ck,
+blend_forward_kernel(const __grid_constant__ ViewBatch vb, GeomWS g, ImageWS im, BinWS b, CkptWS ck,
 	float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha)
 {
 	constexpr int NT = BlendCfg<NW>::NT;          // threads per block
@@ -126,10 +126,15 @@ blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Geo
 	__shared__ BlendSmem<NW> bs;
 
 	if (im.counters[1]) return;   // binning overflow: the host re-runs with a larger buffer
-	const int tile = (int)im.tile_order[blockIdx.x / SPLIT];   // deepest tiles first (binning.cuh)
+	const int W = vb.W, H = vb.H, grid_x = vb.grid_x;
+	// unit u = blockIdx.x / SPLIT: view u % V, that view's (u / V)-th deepest tile (deepest tiles of all views first)
+	const uint32_t unit = blockIdx.x / SPLIT;
+	const int view = (int)(unit % (uint32_t)vb.V);
+	const int vtile = (int)im.tile_order[(size_t)view * vb.T + unit / (uint32_t)vb.V];   // virtual tile v*T + t
+	const int tile = vtile - view * vb.T;
 	const int sub = blockIdx.x % SPLIT;
 	const int tile_y = tile / grid_x, tile_x = tile - tile_y * grid_x;
-	const uint2 range = im.ranges[tile];
+	const uint2 range = im.ranges[vtile];
 	const int n = (int)(range.y - range.x);
 	const unsigned full = 0xffffffffu;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -160,7 +165,7 @@ blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Geo
 	}
 
 	// boundary records of this tile (nullptr: no checkpointing); pixel slot = patch * 32 + lane, whatever NW is
-	float* ck_rec = ck.rec ? ck.rec + (size_t)ck.seg_base[tile] * CKPT_REC_FLOATS + (sub * NW + warp) * 32 + lane : nullptr;
+	float* ck_rec = ck.rec ? ck.rec + (size_t)ck.seg_base[vtile] * CKPT_REC_FLOATS + (sub * NW + warp) * 32 + lane : nullptr;
 
 	for (int base = 0; base < n; base += BLEND_BATCH) {
 		if (__syncthreads_count(done) == NT) break;
@@ -258,15 +263,18 @@ blend_forward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Geo
 
 	if (inside) {
 		const int pix = py * W + px;
-		im.final_T[pix] = T;
-		im.n_contrib[pix] = last_contributor;
-		const int HW = H * W;
-		out_color[pix] = ffma(T, bg[0], C0);
-		out_color[HW + pix] = ffma(T, bg[1], C1);
-		out_color[2 * HW + pix] = ffma(T, bg[2], C2);
-		out_alpha[pix] = weight;   // sum of alpha*T, DGR forward.cu:380
-		out_depth[pix] = Dp;
-		if (ck.fin) ck.fin[pix] = make_float4(C0, C1, C2, Dp);
+		const size_t HW = (size_t)H * W;
+		const size_t vpix = (size_t)view * HW + pix;          // pixel of the batch: outputs are [V,3,H,W] / [V,H,W]
+		const float* __restrict__ bg = vb.cam[view].bg;
+		im.final_T[vpix] = T;
+		im.n_contrib[vpix] = last_contributor;
+		float* oc = out_color + (size_t)view * 3 * HW;
+		oc[pix] = ffma(T, bg[0], C0);
+		oc[HW + pix] = ffma(T, bg[1], C1);
+		oc[2 * HW + pix] = ffma(T, bg[2], C2);
+		out_alpha[vpix] = weight;   // sum of alpha*T, DGR forward.cu:380
+		out_depth[vpix] = Dp;
+		if (ck.fin) ck.fin[vpix] = make_float4(C0, C1, C2, Dp);
 	}
 }
 
@@ -387,7 +395,7 @@ struct BwdSmem {
 
 template <int NW>
 __global__ void __launch_bounds__(32 * NW)
-blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, GeomWS g, ImageWS im, BinWS b, CkptWS ck,
+blend_backward_kernel(const __grid_constant__ ViewBatch vb, GeomWS g, ImageWS im, BinWS b, CkptWS ck,
 	const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas,
 	int deterministic)
 {
@@ -398,19 +406,25 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 
 	// Unit of work: a whole tile, or -- with a checkpoint workspace -- one CKPT_SEG-long segment [seg_lo, seg_hi) of
 	// its instance list, so that the segments of a deep tile run as independent blocks.
-	int tile, seg = 0;
+	const int W = vb.W, H = vb.H, grid_x = vb.grid_x;
+	int vtile, seg = 0;              // virtual tile v*T + t
 	if (ck.rec) {
 		if (blockIdx.x / SPLIT >= im.counters[4]) return;
 		const uint2 ts = ck.seg_map[blockIdx.x / SPLIT];
-		tile = (int)ts.x; seg = (int)ts.y;
+		vtile = (int)ts.x; seg = (int)ts.y;
 	} else {
-		tile = (int)im.tile_order[blockIdx.x / SPLIT];         // deepest tiles first (binning.cuh)
+		const uint32_t unit = blockIdx.x / SPLIT;           // deepest tiles of every view first (binning.cuh)
+		const uint32_t v_ = unit % (uint32_t)vb.V;
+		vtile = (int)im.tile_order[(size_t)v_ * vb.T + unit / (uint32_t)vb.V];
 	}
+	const int view = vtile / vb.T;
+	const int tile = vtile - view * vb.T;
 	const int sub = blockIdx.x % SPLIT;
 	const int tile_y = tile / grid_x, tile_x = tile - tile_y * grid_x;
-	const uint2 range = im.ranges[tile];
+	const uint2 range = im.ranges[vtile];
 	const int n = (int)(range.y - range.x);
 	if (n == 0) return;
+	const float* __restrict__ bg = vb.cam[view].bg;
 	const uint32_t seg_lo = ck.rec ? (uint32_t)seg * CKPT_SEG : 0u;
 	const uint32_t seg_hi = ck.rec ? min((uint32_t)n, seg_lo + CKPT_SEG) : (uint32_t)n;
 
@@ -423,17 +437,19 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	const unsigned full = 0xffffffffu;
 
-	const float T_final = inside ? im.final_T[pix] : 0.f;
+	const size_t HW = (size_t)H * W;
+	const size_t vpix = (size_t)view * HW + pix;
+	const float T_final = inside ? im.final_T[vpix] : 0.f;
 	float T = T_final;
-	const uint32_t n_contrib = inside ? im.n_contrib[pix] : 0u;
+	const uint32_t n_contrib = inside ? im.n_contrib[vpix] : 0u;
 	// positions [seg_lo, last_contributor) of this unit can receive gradient from this pixel
 	const uint32_t last_contributor = n_contrib > seg_lo ? min(n_contrib, seg_hi) : seg_lo;
 	float dpix[3] = {0.f, 0.f, 0.f}, ddepth = 0.f, dalpha = 0.f;
 	if (inside) {
-		const int HW = H * W;
-		dpix[0] = dL_dpix[pix]; dpix[1] = dL_dpix[HW + pix]; dpix[2] = dL_dpix[2 * HW + pix];
-		ddepth = dL_ddepths ? dL_ddepths[pix] : 0.f;      // NULL = no gradient reaches this output
-		dalpha = dL_dalphas ? dL_dalphas[pix] : 0.f;
+		const float* dp = dL_dpix + (size_t)view * 3 * HW;
+		dpix[0] = dp[pix]; dpix[1] = dp[HW + pix]; dpix[2] = dp[2 * HW + pix];
+		ddepth = dL_ddepths ? dL_ddepths[vpix] : 0.f;      // NULL = no gradient reaches this output
+		dalpha = dL_dalphas ? dL_dalphas[vpix] : 0.f;
 	}
 	const float bg_dot_dpixel = bg[0] * dpix[0] + bg[1] * dpix[1] + bg[2] * dpix[2];
 
@@ -455,9 +471,9 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 		// the pixel kept blending behind this segment: start from the forward's state in front of position seg_hi.
 		// With P = that prefix state and F the final sums, the reference's running "what lies behind" values are
 		// (F - P) / T_P  (DGR backward.cu:531-551 unrolled over the instances behind the boundary).
-		const float* r = ck.rec + ((size_t)ck.seg_base[tile] + seg) * CKPT_REC_FLOATS + (sub * NW + warp) * 32 + lane;
+		const float* r = ck.rec + ((size_t)ck.seg_base[vtile] + seg) * CKPT_REC_FLOATS + (sub * NW + warp) * 32 + lane;
 		const float Tp = r[0];
-		const float4 F = ck.fin[pix];
+		const float4 F = ck.fin[vpix];
 		const float inv = __fdividef(1.0f, Tp);
 		accum_rec[0] = (F.x - r[TILE_PIX]) * inv; accum_rec[1] = (F.y - r[2 * TILE_PIX]) * inv;
 		accum_rec[2] = (F.z - r[3 * TILE_PIX]) * inv;
@@ -634,11 +650,10 @@ blend_backward_kernel(int W, int H, int grid_x, const float* __restrict__ bg, Ge
 				// order-independent accumulation: the block's partial sums (themselves computed in a fixed order)
 				// are added as 64-bit fixed-point integers
 				const float S = det_scale_from_bits(im.counters[6], false);
-				unsigned long long* acc = reinterpret_cast<unsigned long long*>(g.grad_acc + GRAD_ACC_VEC * (size_t)sm.id[j]);
 				const int first = second ? 4 : 0, cnt = second ? 5 : 4;
 #pragma unroll
 				for (int i = 0; i < 5; i++)
-					if (i < cnt) atomicAdd(acc + first + i, (unsigned long long)__float2ll_rn(r[i] * S));
+					if (i < cnt) atomicAdd(det_slot(g, (size_t)sm.id[j], first + i), (unsigned long long)__float2ll_rn(r[i] * S));
 			}
 		}
 	}
@@ -653,6 +668,7 @@ __global__ void __launch_bounds__(256)
 upstream_maxabs_kernel(int N, const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepth,
 	const float* __restrict__ dL_dalpha, uint32_t* __restrict__ out)
 {
+	// N = pixels of the whole batch (V*H*W): dL_dpix holds 3N values in any layout, max is layout-blind
 	float m = 0.f;
 	for (int i = blockIdx.x * 256 + threadIdx.x; i < N; i += gridDim.x * 256) {
 		m = fmaxf(m, fmaxf(fmaxf(fabsf(dL_dpix[i]), fabsf(dL_dpix[N + i])), fabsf(dL_dpix[2 * N + i])));

@@ -42,7 +42,13 @@ __host__ __device__ __forceinline__ size_t align_up(size_t v, size_t a) { return
 // Workspace carving (caller-owned memory; layout private to this library).
 // ---------------------------------------------------------------------------------------------
 constexpr int TILE_SUB = 8;        // sub-counters per tile (ImageWS::tile_count)
-constexpr int GRAD_ACC_VEC = 5;    // float4 slots per Gaussian in GeomWS::grad_acc
+constexpr int GRAD_ACC_VEC = 3;    // float4 slots per Gaussian in GeomWS::grad_acc (48 B)
+constexpr int GRAD_EXT_VEC = 2;    // + float4 slots in GeomWS::grad_ext, touched by MOSS_FLAG_DETERMINISTIC only
+constexpr int MAX_VIEWS = 32;      // views per batched call (MOSS_MAX_VIEWS); the per-view camera table travels as a kernel argument
+constexpr int VIEW_SYNC_WORDS = 64; // look-back words of the per-view tile scan, carved behind tile_count (one memset clears both)
+
+// A batched call renders V views of the SAME Gaussians in one launch sequence.  Everything per view is laid out
+// view-major: "virtual Gaussian" id' = v*P + i, "virtual tile" t' = v*T + t, pixel v*N + p.  V = 1 is the plain call.
 
 struct GeomWS {
 	float*    depths;         // [P]   view-space z (sort key low bits)
@@ -53,18 +59,26 @@ struct GeomWS {
 	uint32_t* tiles_touched;  // [P]
 	ushort4*  rect;           // [P]   tile rect (xmin, ymin, xmax, ymax)
 	uint8_t*  clamped;        // [P]   bit c set <=> SH colour channel c was clamped at 0
-	float4*   grad_acc;       // [5P]  blend-backward accumulators, 80 B per Gaussian; the first 48 B take VECTOR atomics:
+	float4*   grad_acc;       // [3P]  blend-backward accumulators, 48 B per Gaussian, VECTOR atomics:
 	                          //       [0] = (dL_dcolor rgb, dL_dopacity)  [1] = (dL_dmean2D xy, dL_dconic xy)
-	                          //       [2] = (dL_dconic w, -, -, -).  Zeroed by the forward preprocess, consumed and
-	                          //       re-zeroed by the backward preprocess: no memset launch anywhere.
-	                          //       MOSS_FLAG_DETERMINISTIC views the 80 B as nine int64 fixed-point sums instead
-	                          //       (colour rgb, opacity, mean2D xy, conic x y w): integer adds commute, so the
-	                          //       result does not depend on the order in which blocks arrive.
+	                          //       [2] = (dL_dconic w, -, -, -).  Rows of VISIBLE Gaussians are zeroed by the forward
+	                          //       preprocess, consumed and re-zeroed by the backward preprocess (rows of culled
+	                          //       Gaussians are never touched): no memset launch, no bytes for culled Gaussians.
+	float4*   grad_ext;       // [2P]  MOSS_FLAG_DETERMINISTIC only: the mode views grad_acc (48 B) + grad_ext (32 B) as
+	                          //       nine int64 fixed-point sums (colour rgb, opacity, mean2D xy | conic x y w):
+	                          //       integer adds commute, so the result does not depend on the order in which blocks
+	                          //       arrive.  Cleared by a memset in the deterministic backward; untouched otherwise.
 };
+// slot s (0..8) of a Gaussian's deterministic accumulator
+__device__ __forceinline__ unsigned long long* det_slot(const GeomWS& g, size_t id, int s)
+{
+	return s < 6 ? reinterpret_cast<unsigned long long*>(g.grad_acc + GRAD_ACC_VEC * id) + s
+	             : reinterpret_cast<unsigned long long*>(g.grad_ext + GRAD_EXT_VEC * id) + (s - 6);
+}
 struct ImageWS {
 	float*    final_T;        // [N]
 	uint32_t* n_contrib;      // [N]
-	uint32_t* tile_count;     // [T][TILE_SUB]  per-tile instance counts, split over TILE_SUB sub-counters picked by the
+	uint32_t* tile_count;     // [T][TILE_SUB] (+ VIEW_SYNC_WORDS look-back words)  per-tile instance counts, split over TILE_SUB sub-counters picked by the
 	                          //      counting warp (a busy tile's single counter is a serialisation point in L2: ~1700
 	                          //      same-address atomics took ~9 us at ZJU shape); after the scan: the scatter cursors
 	uint32_t* tile_total;     // [T]  instances per tile
@@ -72,6 +86,9 @@ struct ImageWS {
 	uint32_t* tile_order;     // [T]  launch order of the blend kernels: tiles by descending instance count
 	uint32_t* counters;       // [8]  num_rendered, overflow, capacity, non-empty tiles, backward segments, checkpoint records,
 	                          //      bits of max|upstream gradient| (deterministic backward), reserved
+	uint32_t* view_busy;      // [MAX_VIEWS]    non-empty tiles of every view
+	uint32_t* view_base;      // [MAX_VIEWS+1]  first instance of every view in the sorted list (+ total)
+	uint32_t* view_sync;      // = tile_count + T*TILE_SUB: (instances of view v) + 1 once block v of the scan knows it
 };
 struct BinWS {
 	unsigned long long* keys; // [cap] (depth_bits << 32 | gaussian id), grouped per tile, sorted in place
@@ -101,6 +118,7 @@ __host__ __device__ inline GeomWS carve_geom(char* base, size_t P, size_t* bytes
 	g.rect = carve<ushort4>(p, P);
 	g.clamped = carve<uint8_t>(p, P);
 	g.grad_acc = carve<float4>(p, GRAD_ACC_VEC * P);
+	g.grad_ext = carve<float4>(p, GRAD_EXT_VEC * P);
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return g;
 }
@@ -110,11 +128,14 @@ __host__ __device__ inline ImageWS carve_image(char* base, size_t N, size_t T, s
 	ImageWS s;
 	s.final_T = carve<float>(p, N);
 	s.n_contrib = carve<uint32_t>(p, N);
-	s.tile_count = carve<uint32_t>(p, T * TILE_SUB);
+	s.tile_count = carve<uint32_t>(p, T * TILE_SUB + VIEW_SYNC_WORDS);
+	s.view_sync = s.tile_count + T * TILE_SUB;
 	s.tile_total = carve<uint32_t>(p, T);
 	s.ranges = carve<uint2>(p, T);
 	s.tile_order = carve<uint32_t>(p, T);
 	s.counters = carve<uint32_t>(p, 8);
+	s.view_busy = carve<uint32_t>(p, MAX_VIEWS);
+	s.view_base = carve<uint32_t>(p, MAX_VIEWS + 1);
 	if (bytes) *bytes = (size_t)(p - base) + 256;
 	return s;
 }
@@ -174,17 +195,25 @@ __host__ __device__ inline CkptWS no_ckpt()
 	return c;
 }
 
-// Per-view parameters.  The matrices live in device memory (they are torch tensors in the reference
-// API: DGR/diff_gaussian_rasterization/__init__.py:160-172); each block stages them in shared memory once.
-struct ViewParams {
+// Camera table of a (batched) call.  The matrices live in device memory (they are torch tensors in the reference
+// API: DGR/diff_gaussian_rasterization/__init__.py:160-172); each block stages its view's in shared memory once.
+// Passed by value as a __grid_constant__ kernel argument, so a batched call needs no device-side table and
+// stays CUDA-graph capturable.
+struct ViewCam {
 	const float* view;    // [16]
 	const float* proj;    // [16]
 	const float* campos;  // [3]
 	const float* bg;      // [3]
 	float tanfovx, tanfovy, focal_x, focal_y;
-	float scale_modifier;
+};
+struct ViewBatch {
+	int V;                // views in this call (1 = the reference's single-view call)
+	int P;                // Gaussians (shared by all views)
 	int W, H, grid_x, grid_y;
+	int T;                // tiles per view
 	int D, M;
+	float scale_modifier;
+	ViewCam cam[MAX_VIEWS];
 };
 
 } // namespace moss

@@ -13,6 +13,7 @@
 #include <mutex>
 #include <atomic>
 #include <vector>
+#include <algorithm>
 #include "../../include/moss_splat.h"
 #include "common.cuh"
 #include "preprocess.cuh"
@@ -46,40 +47,50 @@ inline int check_launch(cudaStream_t s, unsigned flags)
 std::atomic<unsigned long long> g_launches{0};
 struct Profiler {
 	static constexpr int CAP = 8192;
+	struct Rec { cudaEvent_t a, b; int stage, dev; };
 	bool on = false;
-	std::vector<cudaEvent_t> ev;       // 2 per record
-	std::vector<int> stage;
+	std::vector<Rec> rec;              // events belong to the device that was current when they were created
 	int n = 0;
 	double ms[MOSS_STAGE_COUNT] = {0};
 	unsigned long long cnt[MOSS_STAGE_COUNT] = {0};
 	std::mutex mu;
 	int drain()
 	{
+		int cur = 0;
+		cudaGetDevice(&cur);
+		int status = MOSS_OK;
 		for (int i = 0; i < n; i++) {
 			float t = 0.f;
-			if (cudaEventSynchronize(ev[2 * i + 1]) != cudaSuccess) return MOSS_ERR_CUDA;
-			if (cudaEventElapsedTime(&t, ev[2 * i], ev[2 * i + 1]) != cudaSuccess) return MOSS_ERR_CUDA;
-			ms[stage[i]] += t; cnt[stage[i]]++;
+			if (rec[i].dev != cur) cudaSetDevice(rec[i].dev);
+			if (cudaEventSynchronize(rec[i].b) != cudaSuccess || cudaEventElapsedTime(&t, rec[i].a, rec[i].b) != cudaSuccess) status = MOSS_ERR_CUDA;
+			else { ms[rec[i].stage] += t; cnt[rec[i].stage]++; }
+			if (rec[i].dev != cur) cudaSetDevice(cur);
 		}
 		n = 0;
-		return MOSS_OK;
+		return status;
 	}
 	void begin(int st, cudaStream_t s)
 	{
 		std::lock_guard<std::mutex> lk(mu);
 		if (n == CAP) drain();
-		if ((int)ev.size() < 2 * (n + 1)) {
-			cudaEvent_t a, b;
-			cudaEventCreate(&a); cudaEventCreate(&b);
-			ev.push_back(a); ev.push_back(b); stage.push_back(st);
+		int cur = 0;
+		cudaGetDevice(&cur);
+		if ((int)rec.size() <= n) {
+			Rec r; r.stage = st; r.dev = cur;
+			cudaEventCreate(&r.a); cudaEventCreate(&r.b);
+			rec.push_back(r);
+		} else if (rec[n].dev != cur) {         // a pooled pair made on another device: replace it
+			cudaEventDestroy(rec[n].a); cudaEventDestroy(rec[n].b);
+			cudaEventCreate(&rec[n].a); cudaEventCreate(&rec[n].b);
+			rec[n].dev = cur;
 		}
-		stage[n] = st;
-		cudaEventRecord(ev[2 * n], s);
+		rec[n].stage = st;
+		cudaEventRecord(rec[n].a, s);
 	}
 	void end(cudaStream_t s)
 	{
 		std::lock_guard<std::mutex> lk(mu);
-		cudaEventRecord(ev[2 * n + 1], s);
+		cudaEventRecord(rec[n].b, s);
 		n++;
 	}
 };
@@ -91,15 +102,19 @@ struct StageScope {
 };
 #define MOSS_STAGE(stage, stream) StageScope stage_scope__(stage, stream)
 
-// Pinned, device-mapped slots through which K2 hands num_rendered to the host without a blocking copy.
+// Pinned, device-mapped slots through which K2 hands num_rendered to the host without a blocking copy.  One pool per
+// device (an event may only be recorded on a stream of the device it was created on); a slot stays marked busy from
+// acquire() until its forward call has read it, so concurrent callers never share one.
+constexpr int MAX_DEVICES = 64;
 struct HostSlots {
 	static constexpr int N = 64;
 	int* host = nullptr;       // cudaHostAlloc'ed, mapped
 	cudaEvent_t ev[N];
+	bool busy[N] = {false};
 	int next = 0;
 	bool ok = false;
 	std::mutex mu;
-	int acquire()
+	int acquire()              // -1: pool exhausted (64 forwards in flight on this device) or CUDA error
 	{
 		std::lock_guard<std::mutex> lk(mu);
 		if (!ok) {
@@ -108,39 +123,75 @@ struct HostSlots {
 				if (cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming) != cudaSuccess) return -1;
 			ok = true;
 		}
-		const int s = next;
-		next = (next + 1) % N;
-		return s;
+		for (int k = 0; k < N; k++) {
+			const int s = (next + k) % N;
+			if (!busy[s]) { busy[s] = true; next = (s + 1) % N; return s; }
+		}
+		return -1;
+	}
+	void release(int s)
+	{
+		std::lock_guard<std::mutex> lk(mu);
+		if (s >= 0 && s < N) busy[s] = false;
 	}
 };
-HostSlots g_slots;
+HostSlots g_slots_dev[MAX_DEVICES];
+inline HostSlots* device_slots()
+{
+	int dev = 0;
+	if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return nullptr;
+	return &g_slots_dev[dev];
+}
+struct SlotLease {             // releases the slot on every return path of the forward
+	HostSlots* pool = nullptr; int slot = -1;
+	~SlotLease() { if (pool && slot >= 0) pool->release(slot); }
+};
 
-inline bool scene_valid(const MossScene* sc)
+// cudaFuncSetAttribute is per device: remember where the sort kernel's dynamic shared memory was already raised
+std::atomic<bool> g_sort_attr_set[MAX_DEVICES];
+
+inline bool scene_valid(const MossScene* sc, bool own_camera = true)
 {
 	if (!sc || sc->P < 0 || sc->W <= 0 || sc->H <= 0) return false;
+	if (own_camera && !sc->bg) return false;
 	if (sc->P == 0) return true;
-	if (!sc->means3D || !sc->opacities || !sc->viewmatrix || !sc->projmatrix || !sc->bg) return false;
+	if (!sc->means3D || !sc->opacities) return false;
+	if (own_camera && (!sc->viewmatrix || !sc->projmatrix)) return false;
 	if ((sc->shs != nullptr) == (sc->colors_precomp != nullptr)) return false;
 	const bool sr = (sc->scales != nullptr) && (sc->rotations != nullptr);
 	if (sr == (sc->cov3D_precomp != nullptr)) return false;
 	if (!sr && (sc->scales || sc->rotations)) return false;
-	if (sc->shs && (!sc->campos || sc->D < 0 || sc->D > 3 || sc->M < (sc->D + 1) * (sc->D + 1))) return false;
+	if (sc->shs && ((own_camera && !sc->campos) || sc->D < 0 || sc->D > 3 || sc->M < (sc->D + 1) * (sc->D + 1))) return false;
 	if (((sc->W + TILE_X - 1) / TILE_X) > 65535 || ((sc->H + TILE_Y - 1) / TILE_Y) > 65535) return false;
 	return true;
 }
 
-inline ViewParams make_view(const MossScene* sc)
+// Camera table of a call.  `views` == nullptr: the single camera described by the scene itself.
+inline bool make_batch(const MossScene* sc, int V, const MossView* views, ViewBatch* vb)
 {
-	ViewParams vp;
-	vp.view = sc->viewmatrix; vp.proj = sc->projmatrix; vp.campos = sc->campos; vp.bg = sc->bg;
-	vp.tanfovx = sc->tanfovx; vp.tanfovy = sc->tanfovy;
-	vp.focal_y = sc->H / (2.0f * sc->tanfovy);   // DGR rasterizer_impl.cu:224-225
-	vp.focal_x = sc->W / (2.0f * sc->tanfovx);
-	vp.scale_modifier = sc->scale_modifier;
-	vp.W = sc->W; vp.H = sc->H;
-	vp.grid_x = (sc->W + TILE_X - 1) / TILE_X; vp.grid_y = (sc->H + TILE_Y - 1) / TILE_Y;
-	vp.D = sc->D; vp.M = sc->M;
-	return vp;
+	if (V < 1 || V > MAX_VIEWS) return false;
+	vb->V = V; vb->P = sc->P;
+	vb->W = sc->W; vb->H = sc->H;
+	vb->grid_x = (sc->W + TILE_X - 1) / TILE_X; vb->grid_y = (sc->H + TILE_Y - 1) / TILE_Y;
+	vb->T = vb->grid_x * vb->grid_y;
+	vb->D = sc->D; vb->M = sc->M;
+	vb->scale_modifier = sc->scale_modifier;
+	for (int v = 0; v < V; v++) {
+		ViewCam& c = vb->cam[v];
+		float tx, ty;
+		if (views) {
+			c.view = views[v].viewmatrix; c.proj = views[v].projmatrix; c.campos = views[v].campos; c.bg = views[v].bg;
+			tx = views[v].tanfovx; ty = views[v].tanfovy;
+		} else {
+			c.view = sc->viewmatrix; c.proj = sc->projmatrix; c.campos = sc->campos; c.bg = sc->bg;
+			tx = sc->tanfovx; ty = sc->tanfovy;
+		}
+		if (!c.view || !c.proj || !c.bg || (sc->shs && !c.campos)) return false;
+		c.tanfovx = tx; c.tanfovy = ty;
+		c.focal_y = sc->H / (2.0f * ty);   // DGR rasterizer_impl.cu:224-225
+		c.focal_x = sc->W / (2.0f * tx);
+	}
+	return true;
 }
 
 // Blend block shape (1 whole tile / 2 half / 3 quarter).  Small images have few busy tiles and the deepest one sets
@@ -154,12 +205,12 @@ inline int blend_split(unsigned flags, int T)
 }
 
 // The optional checkpoint workspace is used when it is large enough for this call's binning capacity.
-inline CkptWS scene_ckpt(const MossScene* sc, uint32_t capacity, int N, int T, unsigned flags)
+inline CkptWS scene_ckpt(const MossScene* sc, uint32_t capacity, size_t N, int T, int V, unsigned flags)
 {
 	// whole-tile (8-warp) blocks stage 256 instances per round and would skip every other boundary
-	if (blend_split(flags, T) == 1 && CKPT_SEG < 256) return no_ckpt();
-	if (!sc->ckpt_ws || sc->ckpt_bytes < moss_ckpt_workspace_bytes((long long)capacity, sc->W, sc->H)) return no_ckpt();
-	return carve_ckpt((char*)sc->ckpt_ws, (size_t)N, (size_t)T, (size_t)capacity);
+	if (blend_split(flags, T * V) == 1 && CKPT_SEG < 256) return no_ckpt();
+	if (!sc->ckpt_ws || sc->ckpt_bytes < moss_ckpt_workspace_bytes_batch((long long)capacity, sc->W, sc->H, V)) return no_ckpt();
+	return carve_ckpt((char*)sc->ckpt_ws, N, (size_t)T * V, (size_t)capacity);
 }
 
 __global__ void reset_overflow_kernel(uint32_t* counters, uint32_t capacity)
@@ -169,13 +220,17 @@ __global__ void reset_overflow_kernel(uint32_t* counters, uint32_t capacity)
 	counters[4] = 0u; counters[5] = 0u;
 }
 
-__global__ void fill_background_kernel(int N, const float* __restrict__ bg, float* __restrict__ color,
+// grid = (ceil(N / 256), V)
+__global__ void fill_background_kernel(const __grid_constant__ ViewBatch vb, int N, float* __restrict__ color,
 	float* __restrict__ depth, float* __restrict__ alpha)
 {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= N) return;
-	color[i] = bg[0]; color[N + i] = bg[1]; color[2 * N + i] = bg[2];
-	depth[i] = 0.f; alpha[i] = 0.f;
+	const size_t v = blockIdx.y;
+	const float* bg = vb.cam[v].bg;
+	float* c = color + v * 3 * N;
+	c[i] = bg[0]; c[N + i] = bg[1]; c[2 * N + i] = bg[2];
+	depth[v * N + i] = 0.f; alpha[v * N + i] = 0.f;
 }
 
 } // namespace
@@ -205,7 +260,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step", "sum_views"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -222,19 +277,22 @@ const char* moss_error_string(int status)
 	}
 }
 
-size_t moss_geom_workspace_bytes(int P)
+size_t moss_geom_workspace_bytes_batch(int P, int V)
 {
 	size_t b = 0;
-	carve_geom(nullptr, (size_t)(P > 0 ? P : 0), &b);
+	carve_geom(nullptr, (size_t)(P > 0 ? P : 0) * (size_t)(V > 0 ? V : 1), &b);
 	return b;
 }
-size_t moss_image_workspace_bytes(int W, int H)
+size_t moss_geom_workspace_bytes(int P) { return moss_geom_workspace_bytes_batch(P, 1); }
+size_t moss_image_workspace_bytes_batch(int W, int H, int V)
 {
 	size_t b = 0;
+	const size_t v = (size_t)(V > 0 ? V : 1);
 	const size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-	carve_image(nullptr, (size_t)W * H, T, &b);
+	carve_image(nullptr, (size_t)W * H * v, T * v, &b);
 	return b;
 }
+size_t moss_image_workspace_bytes(int W, int H) { return moss_image_workspace_bytes_batch(W, H, 1); }
 size_t moss_binning_workspace_bytes_ex(long long capacity, int export_keys)
 {
 	size_t b = 0;
@@ -242,13 +300,15 @@ size_t moss_binning_workspace_bytes_ex(long long capacity, int export_keys)
 	return b;
 }
 size_t moss_binning_workspace_bytes(long long capacity) { return moss_binning_workspace_bytes_ex(capacity, 0); }
-size_t moss_ckpt_workspace_bytes(long long capacity, int W, int H)
+size_t moss_ckpt_workspace_bytes_batch(long long capacity, int W, int H, int V)
 {
 	size_t b = 0;
+	const size_t v = (size_t)(V > 0 ? V : 1);
 	const size_t T = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-	carve_ckpt(nullptr, (size_t)W * H, T, (size_t)(capacity > 0 ? capacity : 0), &b);
+	carve_ckpt(nullptr, (size_t)W * H * v, T * v, (size_t)(capacity > 0 ? capacity : 0), &b);
 	return b;
 }
+size_t moss_ckpt_workspace_bytes(long long capacity, int W, int H) { return moss_ckpt_workspace_bytes_batch(capacity, W, H, 1); }
 long long moss_binning_capacity(size_t bytes, int export_keys)
 {
 	const size_t per = export_keys ? 28 : 20;
@@ -260,53 +320,79 @@ long long moss_binning_capacity(size_t bytes, int export_keys)
 	return lo;
 }
 
-int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
+namespace {
+
+// per-view row of the batched backward's scratch area (floats; every segment 16 B-aligned)
+struct BatchRow { size_t opacity, color, mean3D, cov3D, sh, scale, rot, total; };
+inline BatchRow batch_row(size_t P, size_t M)
+{
+	auto pad = [](size_t n) { return (n + 3) / 4 * 4; };
+	BatchRow r; size_t o = 0;
+	r.opacity = o; o += pad(P);
+	r.color = o; o += pad(3 * P);
+	r.mean3D = o; o += pad(3 * P);
+	r.cov3D = o; o += pad(6 * P);
+	r.sh = o; o += pad(3 * M * P);
+	r.scale = o; o += pad(3 * P);
+	r.rot = o; o += pad(4 * P);
+	r.total = o;
+	return r;
+}
+
+int forward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossView* views, unsigned flags,
 	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
 {
-	cudaStream_t stream = (cudaStream_t)stream_;
-	if (!scene_valid(sc) || !out_color || !out_depth || !out_alpha) return MOSS_ERR_INVALID_ARGUMENT;
+	if (!scene_valid(sc, views == nullptr) || !out_color || !out_depth || !out_alpha) return MOSS_ERR_INVALID_ARGUMENT;
 	if (sc->P > 0 && !radii) return MOSS_ERR_INVALID_ARGUMENT;
+	if ((unsigned long long)sc->P * (unsigned long long)V >= 0xffffffffull) return MOSS_ERR_INVALID_ARGUMENT;   // id' = v*P + i is 32 bits
 	if (num_rendered) *num_rendered = (flags & MOSS_FLAG_ASYNC) ? -1 : 0;
+	ViewBatch vb;
+	if (!make_batch(sc, V, views, &vb)) return MOSS_ERR_INVALID_ARGUMENT;
 	const int P = sc->P, W = sc->W, H = sc->H, N = W * H;
-	const ViewParams vp = make_view(sc);
-	const int T = vp.grid_x * vp.grid_y;
-	if (sc->image_bytes < moss_image_workspace_bytes(W, H) || !sc->image_ws) return MOSS_ERR_WORKSPACE_TOO_SMALL;
-	ImageWS im = carve_image((char*)sc->image_ws, (size_t)N, (size_t)T);
+	const int T = vb.T, TV = T * V;
+	const size_t NV = (size_t)N * V;
+	if (sc->image_bytes < moss_image_workspace_bytes_batch(W, H, V) || !sc->image_ws) return MOSS_ERR_WORKSPACE_TOO_SMALL;
+	ImageWS im = carve_image((char*)sc->image_ws, NV, (size_t)TV);
 	if (P == 0) {
 		// DGR/rasterize_points.cu:83: nothing rendered; outputs are background / zeros, state says "no contributors"
 		{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
-		fill_background_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, sc->bg, out_color, out_depth, out_alpha); }
-		MOSS_CUDA_TRY(cudaMemsetAsync(sc->image_ws, 0, moss_image_workspace_bytes(W, H) - 256, stream));
+		fill_background_kernel<<<dim3((N + 255) / 256, V), 256, 0, stream>>>(vb, N, out_color, out_depth, out_alpha); }
+		MOSS_CUDA_TRY(cudaMemsetAsync(sc->image_ws, 0, moss_image_workspace_bytes_batch(W, H, V) - 256, stream));
 		MOSS_CHECK_LAUNCH(stream, flags);
 		return MOSS_OK;
 	}
-	if (sc->geom_bytes < moss_geom_workspace_bytes(P) || !sc->geom_ws) return MOSS_ERR_WORKSPACE_TOO_SMALL;
+	if (sc->geom_bytes < moss_geom_workspace_bytes_batch(P, V) || !sc->geom_ws) return MOSS_ERR_WORKSPACE_TOO_SMALL;
 	const bool export_keys = (flags & MOSS_FLAG_EXPORT_KEYS) != 0;
 	const long long cap_ll = sc->binning_ws ? moss_binning_capacity(sc->binning_bytes, export_keys) : 0;
 	const uint32_t capacity = (uint32_t)(cap_ll > 0xfffffff0ll ? 0xfffffff0ll : cap_ll);
-	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P);
+	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P * V);
 	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
-	const CkptWS ck = scene_ckpt(sc, capacity, N, T, flags);
+	const CkptWS ck = scene_ckpt(sc, capacity, NV, T, V, flags);
 
-	int slot = -1;
-	if (!(flags & MOSS_FLAG_ASYNC)) {
-		slot = g_slots.acquire();
-		if (slot < 0) { g_last_cuda_error = (int)cudaGetLastError(); return MOSS_ERR_CUDA; }
+	// synchronous mode: K2 drops the instance count into a pinned mapped slot and the host waits for an event recorded
+	// right behind K2 (K3/K4 are queued behind it already); without a free slot it reads the counters with a copy
+	SlotLease lease;
+	if (!(flags & (MOSS_FLAG_ASYNC | MOSS_FLAG_REBIN))) {
+		lease.pool = device_slots();
+		lease.slot = lease.pool ? lease.pool->acquire() : -1;
 	}
+	const int slot = lease.slot;
+	const dim3 pre_grid((P + PRE_THREADS - 1) / PRE_THREADS, V);
 
 	if (!(flags & MOSS_FLAG_REBIN)) {
-		MOSS_CUDA_TRY(cudaMemsetAsync(im.tile_count, 0, (size_t)T * TILE_SUB * sizeof(uint32_t), stream));
+		MOSS_CUDA_TRY(cudaMemsetAsync(im.tile_count, 0, ((size_t)TV * TILE_SUB + VIEW_SYNC_WORDS) * sizeof(uint32_t), stream));
 		{ MOSS_STAGE(MOSS_STAGE_PREPROCESS, stream);
-		preprocess_forward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
-			P, vp, sc->means3D, sc->shs, sc->colors_precomp, sc->opacities, sc->scales, sc->rotations,
+		preprocess_forward_kernel<<<pre_grid, PRE_THREADS, 0, stream>>>(
+			vb, sc->means3D, sc->shs, sc->colors_precomp, sc->opacities, sc->scales, sc->rotations,
 			sc->cov3D_precomp, sc->prefiltered, g, im.tile_count, radii); }
 		MOSS_CHECK_LAUNCH(stream, flags);
 		int* host_R = nullptr;
-		if (slot >= 0) MOSS_CUDA_TRY(cudaHostGetDevicePointer((void**)&host_R, g_slots.host + slot, 0));
+		if (slot >= 0) MOSS_CUDA_TRY(cudaHostGetDevicePointer((void**)&host_R, lease.pool->host + slot, 0));
 		{ MOSS_STAGE(MOSS_STAGE_TILE_SCAN, stream);
-		tile_scan_kernel<<<1, SCAN_THREADS, 0, stream>>>(T, im.tile_count, im.tile_total, im.ranges, im.counters, capacity, host_R, im.tile_order); }
+		tile_scan_kernel<<<V, SCAN_THREADS, 0, stream>>>(T, V, im.tile_count, im.tile_total, im.ranges, im.counters, capacity, host_R,
+			im.tile_order, im.view_busy, im.view_base, im.view_sync); }
 		MOSS_CHECK_LAUNCH(stream, flags);
-		if (slot >= 0) MOSS_CUDA_TRY(cudaEventRecord(g_slots.ev[slot], stream));
+		if (slot >= 0) MOSS_CUDA_TRY(cudaEventRecord(lease.pool->ev[slot], stream));
 	} else {
 		{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
 		reset_overflow_kernel<<<1, 1, 0, stream>>>(im.counters, capacity); }
@@ -314,43 +400,42 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 	}
 
 	{ MOSS_STAGE(MOSS_STAGE_SCATTER, stream);
-	scatter_keys_kernel<<<(P + SCATTER_THREADS - 1) / SCATTER_THREADS, SCATTER_THREADS, 0, stream>>>(P, vp.grid_x, radii, g, im.ranges, im.tile_count,
-		im.counters, b.keys); }
+	scatter_keys_kernel<<<dim3((P + SCATTER_THREADS - 1) / SCATTER_THREADS, V), SCATTER_THREADS, 0, stream>>>(P, vb.grid_x, T, radii, g,
+		im.ranges, im.tile_count, im.counters, b.keys); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_TILE_SORT, stream);
 	// opt in to > 48 KB of dynamic shared memory (the attribute is per device)
-	static int sort_attr_dev = -1;
 	int cur_dev = 0;
-	cudaGetDevice(&cur_dev);
-	if (cur_dev != sort_attr_dev) {
+	MOSS_CUDA_TRY(cudaGetDevice(&cur_dev));
+	if (cur_dev >= 0 && cur_dev < MAX_DEVICES && !g_sort_attr_set[cur_dev].load(std::memory_order_acquire)) {
 		MOSS_CUDA_TRY(cudaFuncSetAttribute(tile_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SortSmem)));
-		sort_attr_dev = cur_dev;
+		g_sort_attr_set[cur_dev].store(true, std::memory_order_release);
 	}
-	tile_sort_kernel<<<T, TILE_PIX, sizeof(SortSmem), stream>>>(im, b, ck); }
+	tile_sort_kernel<<<TV, TILE_PIX, sizeof(SortSmem), stream>>>(im, b, ck, T, V); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_FWD, stream);
 	const bool cull = !(flags & MOSS_FLAG_NO_CULL);
-	switch (blend_split(flags, T)) {
+	switch (blend_split(flags, TV)) {
 	case 1:
-		if (cull) blend_forward_kernel<true, 8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
-		else blend_forward_kernel<false, 8><<<T, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
+		if (cull) blend_forward_kernel<true, 8><<<TV, 256, 0, stream>>>(vb, g, im, b, ck, out_color, out_depth, out_alpha);
+		else blend_forward_kernel<false, 8><<<TV, 256, 0, stream>>>(vb, g, im, b, ck, out_color, out_depth, out_alpha);
 		break;
 	case 2:
-		if (cull) blend_forward_kernel<true, 4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
-		else blend_forward_kernel<false, 4><<<2 * T, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
+		if (cull) blend_forward_kernel<true, 4><<<2 * TV, 128, 0, stream>>>(vb, g, im, b, ck, out_color, out_depth, out_alpha);
+		else blend_forward_kernel<false, 4><<<2 * TV, 128, 0, stream>>>(vb, g, im, b, ck, out_color, out_depth, out_alpha);
 		break;
 	default:
-		if (cull) blend_forward_kernel<true, 2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
-		else blend_forward_kernel<false, 2><<<4 * T, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, out_color, out_depth, out_alpha);
+		if (cull) blend_forward_kernel<true, 2><<<4 * TV, 64, 0, stream>>>(vb, g, im, b, ck, out_color, out_depth, out_alpha);
+		else blend_forward_kernel<false, 2><<<4 * TV, 64, 0, stream>>>(vb, g, im, b, ck, out_color, out_depth, out_alpha);
 		break;
 	} }
 	MOSS_CHECK_LAUNCH(stream, flags);
 
 	if (flags & MOSS_FLAG_ASYNC) return MOSS_OK;
 	int R;
-	if (!(flags & MOSS_FLAG_REBIN)) {
-		MOSS_CUDA_TRY(cudaEventSynchronize(g_slots.ev[slot]));
-		R = *(volatile int*)(g_slots.host + slot);
+	if (slot >= 0) {
+		MOSS_CUDA_TRY(cudaEventSynchronize(lease.pool->ev[slot]));
+		R = *(volatile int*)(lease.pool->host + slot);
 	} else {
 		uint32_t c[4];
 		MOSS_CUDA_TRY(cudaMemcpyAsync(c, im.counters, sizeof(c), cudaMemcpyDeviceToHost, stream));
@@ -362,52 +447,122 @@ int moss_rasterize_forward(void* stream_, const MossScene* sc, unsigned flags,
 	return MOSS_OK;
 }
 
-int moss_rasterize_backward(void* stream_, const MossScene* sc, unsigned flags, const int* radii,
+int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossView* views, unsigned flags, const int* radii,
 	const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
-	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot)
+	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* tmp_ws, size_t tmp_bytes)
 {
-	cudaStream_t stream = (cudaStream_t)stream_;
-	if (!scene_valid(sc)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (!scene_valid(sc, views == nullptr)) return MOSS_ERR_INVALID_ARGUMENT;
 	const int P = sc->P, W = sc->W, H = sc->H, N = W * H;
 	if (P == 0) return MOSS_OK;
-	if (!radii || !dL_dpix || !dL_dmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
+	if (!radii || !dL_dpix || !dL_dmean2D || !dL_dopacity || !dL_dcolor ||
 		!dL_dmean3D || !dL_dcov3D || (sc->shs && !dL_dsh) || (sc->scales && (!dL_dscale || !dL_drot)))
 		return MOSS_ERR_INVALID_ARGUMENT;
-	const ViewParams vp = make_view(sc);
-	const int T = vp.grid_x * vp.grid_y;
-	if (sc->image_bytes < moss_image_workspace_bytes(W, H) || sc->geom_bytes < moss_geom_workspace_bytes(P))
+	ViewBatch vb;
+	if (!make_batch(sc, V, views, &vb)) return MOSS_ERR_INVALID_ARGUMENT;
+	const int T = vb.T, TV = T * V;
+	const size_t NV = (size_t)N * V;
+	if (sc->image_bytes < moss_image_workspace_bytes_batch(W, H, V) || sc->geom_bytes < moss_geom_workspace_bytes_batch(P, V))
 		return MOSS_ERR_WORKSPACE_TOO_SMALL;
+	if (V > 1 && (!tmp_ws || tmp_bytes < moss_batch_grad_workspace_bytes(P, sc->M, V))) return MOSS_ERR_WORKSPACE_TOO_SMALL;
 	const bool export_keys = (flags & MOSS_FLAG_EXPORT_KEYS) != 0;
 	const long long cap_ll = sc->binning_ws ? moss_binning_capacity(sc->binning_bytes, export_keys) : 0;
 	const uint32_t capacity = (uint32_t)(cap_ll > 0xfffffff0ll ? 0xfffffff0ll : cap_ll);
-	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P);
-	ImageWS im = carve_image((char*)sc->image_ws, (size_t)N, (size_t)T);
+	GeomWS g = carve_geom((char*)sc->geom_ws, (size_t)P * V);
+	ImageWS im = carve_image((char*)sc->image_ws, NV, (size_t)TV);
 	BinWS b = carve_bin((char*)sc->binning_ws, capacity, export_keys);
-	const CkptWS ck = scene_ckpt(sc, capacity, N, T, flags);
+	const CkptWS ck = scene_ckpt(sc, capacity, NV, T, V, flags);
 	// work units: tiles, or (with checkpoints) at most capacity/CKPT_SEG + T segments; surplus blocks exit at once
-	const unsigned units = ck.rec ? ck.max_segs : (unsigned)T;
+	const unsigned units = ck.rec ? ck.max_segs : (unsigned)TV;
 	const int det = (flags & MOSS_FLAG_DETERMINISTIC) ? 1 : 0;
 	if (det) {
 		MOSS_CUDA_TRY(cudaMemsetAsync(im.counters + 6, 0, sizeof(uint32_t), stream));
+		MOSS_CUDA_TRY(cudaMemsetAsync(g.grad_ext, 0, sizeof(float4) * GRAD_EXT_VEC * (size_t)P * V, stream));
 		{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
-		upstream_maxabs_kernel<<<min((N + 255) / 256, 592), 256, 0, stream>>>(N, dL_dpix, dL_ddepth, dL_dalpha, im.counters + 6); }
+		upstream_maxabs_kernel<<<(int)std::min<size_t>((NV + 255) / 256, 592), 256, 0, stream>>>((int)NV, dL_dpix, dL_ddepth, dL_dalpha, im.counters + 6); }
 		MOSS_CHECK_LAUNCH(stream, flags);
 	}
 
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_BWD, stream);
-	switch (blend_split(flags, T)) {
-	case 1: blend_backward_kernel<8><<<units, 256, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
-	case 2: blend_backward_kernel<4><<<2 * units, 128, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
-	default: blend_backward_kernel<2><<<4 * units, 64, 0, stream>>>(W, H, vp.grid_x, sc->bg, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
+	switch (blend_split(flags, TV)) {
+	case 1: blend_backward_kernel<8><<<units, 256, 0, stream>>>(vb, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
+	case 2: blend_backward_kernel<4><<<2 * units, 128, 0, stream>>>(vb, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
+	default: blend_backward_kernel<2><<<4 * units, 64, 0, stream>>>(vb, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
 	} }
 	MOSS_CHECK_LAUNCH(stream, flags);
+
+	ParamGradOut po;
+	BatchRow row = batch_row((size_t)P, (size_t)sc->M);
+	if (V == 1) {
+		po.color = dL_dcolor; po.opacity = dL_dopacity; po.mean3D = dL_dmean3D; po.cov3D = dL_dcov3D;
+		po.sh = sc->shs ? dL_dsh : nullptr; po.scale = sc->scales ? dL_dscale : nullptr; po.rot = sc->scales ? dL_drot : nullptr;
+		po.view_stride = 0;
+	} else {
+		float* t = (float*)tmp_ws;
+		po.color = t + row.color; po.opacity = t + row.opacity; po.mean3D = t + row.mean3D; po.cov3D = t + row.cov3D;
+		po.sh = sc->shs ? t + row.sh : nullptr; po.scale = sc->scales ? t + row.scale : nullptr; po.rot = sc->scales ? t + row.rot : nullptr;
+		po.view_stride = row.total;
+	}
 	{ MOSS_STAGE(MOSS_STAGE_PREPROCESS_BWD, stream);
-	preprocess_backward_kernel<<<(P + PRE_THREADS - 1) / PRE_THREADS, PRE_THREADS, 0, stream>>>(
-		P, vp, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
-		dL_dmean2D, dL_dconic, dL_dcolor, dL_dopacity, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, det, im.counters); }
+	preprocess_backward_kernel<<<dim3((P + PRE_THREADS - 1) / PRE_THREADS, V), PRE_THREADS, 0, stream>>>(
+		vb, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
+		dL_dmean2D, dL_dconic, po, det, im.counters); }
 	MOSS_CHECK_LAUNCH(stream, flags);
+	if (V > 1) {
+		SumViewsArgs a;
+		memset(&a, 0, sizeof(a));
+		a.V = V; a.view_stride = row.total;
+		const size_t p = (size_t)P, m = (size_t)sc->M;
+		float* dst[7] = {dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, sc->shs ? dL_dsh : nullptr, sc->scales ? dL_dscale : nullptr, sc->scales ? dL_drot : nullptr};
+		const float* src[7] = {po.opacity, po.color, po.mean3D, po.cov3D, po.sh, po.scale, po.rot};
+		const size_t n[7] = {p, 3 * p, 3 * p, 6 * p, 3 * m * p, 3 * p, 4 * p};
+		size_t biggest = 0;
+		for (int k = 0; k < 7; k++) { a.dst[k] = dst[k]; a.src[k] = src[k]; a.n[k] = dst[k] ? n[k] : 0; biggest = std::max(biggest, a.n[k]); }
+		const unsigned gx = (unsigned)std::min<size_t>((biggest / 4 + SUMV_THREADS - 1) / SUMV_THREADS + 1, 148 * 8);
+		{ MOSS_STAGE(MOSS_STAGE_SUM_VIEWS, stream);
+		sum_views_kernel<<<dim3(gx, 7), SUMV_THREADS, 0, stream>>>(a); }
+		MOSS_CHECK_LAUNCH(stream, flags);
+	}
 	return MOSS_OK;
+}
+
+} // namespace
+
+size_t moss_sizeof_view(void) { return sizeof(MossView); }
+size_t moss_batch_grad_workspace_bytes(int P, int M, int V)
+{
+	if (V <= 1 || P <= 0) return 0;
+	return batch_row((size_t)P, (size_t)(M > 0 ? M : 0)).total * sizeof(float) * (size_t)V;
+}
+
+int moss_rasterize_forward(void* stream, const MossScene* sc, unsigned flags,
+	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
+{
+	return forward_impl((cudaStream_t)stream, sc, 1, nullptr, flags, out_color, out_depth, out_alpha, radii, num_rendered);
+}
+int moss_rasterize_forward_batch(void* stream, const MossScene* sc, int V, const MossView* views, unsigned flags,
+	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
+{
+	if (!views) return MOSS_ERR_INVALID_ARGUMENT;
+	return forward_impl((cudaStream_t)stream, sc, V, views, flags, out_color, out_depth, out_alpha, radii, num_rendered);
+}
+int moss_rasterize_backward(void* stream, const MossScene* sc, unsigned flags, const int* radii,
+	const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot)
+{
+	if (!dL_dconic) return MOSS_ERR_INVALID_ARGUMENT;
+	return backward_impl((cudaStream_t)stream, sc, 1, nullptr, flags, radii, dL_dpix, dL_ddepth, dL_dalpha, dL_dmean2D, dL_dconic,
+		dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, 0);
+}
+int moss_rasterize_backward_batch(void* stream, const MossScene* sc, int V, const MossView* views, unsigned flags, const int* radii,
+	const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* tmp_ws, size_t tmp_bytes)
+{
+	if (!views) return MOSS_ERR_INVALID_ARGUMENT;
+	return backward_impl((cudaStream_t)stream, sc, V, views, flags, radii, dL_dpix, dL_ddepth, dL_dalpha, dL_dmean2D, dL_dconic,
+		dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, tmp_ws, tmp_bytes);
 }
 
 int moss_mark_visible(void* stream_, int P, const float* means3D, const float* viewmatrix,
@@ -441,13 +596,13 @@ __global__ void extract_rgb_kernel(int P, const float4* __restrict__ feat, float
 }
 }
 
-long long moss_export_state(void* stream_, const MossScene* sc, int which, void* dst, long long max_bytes)
+long long moss_export_state_batch(void* stream_, const MossScene* sc, int V, int which, void* dst, long long max_bytes)
 {
 	cudaStream_t stream = (cudaStream_t)stream_;
-	if (!sc || !dst) return -MOSS_ERR_INVALID_ARGUMENT;
-	const size_t P = sc->P, N = (size_t)sc->W * sc->H;
+	if (!sc || !dst || V < 1 || V > MAX_VIEWS) return -MOSS_ERR_INVALID_ARGUMENT;
+	const size_t P = (size_t)sc->P * V, N = (size_t)sc->W * sc->H * V;
 	const int gx = (sc->W + TILE_X - 1) / TILE_X, gy = (sc->H + TILE_Y - 1) / TILE_Y;
-	const size_t T = (size_t)gx * gy;
+	const size_t T = (size_t)gx * gy * V;
 	GeomWS g = carve_geom((char*)sc->geom_ws, P);
 	ImageWS im = carve_image((char*)sc->image_ws, N, T);
 	uint32_t counters[4] = {0, 0, 0, 0};
@@ -468,6 +623,7 @@ long long moss_export_state(void* stream_, const MossScene* sc, int which, void*
 	case MOSS_STATE_N_CONTRIB: src = im.n_contrib; n = 4 * N; break;
 	case MOSS_STATE_FINAL_T: src = im.final_T; n = 4 * N; break;
 	case MOSS_STATE_COUNTERS: src = im.counters; n = 16; break;
+	case MOSS_STATE_VIEW_BASE: src = im.view_base; n = 4 * ((long long)V + 1); break;
 	case MOSS_STATE_CLAMPED:
 		n = 3 * P;
 		if (n > max_bytes) return -MOSS_ERR_WORKSPACE_TOO_SMALL;
@@ -495,6 +651,10 @@ long long moss_export_state(void* stream_, const MossScene* sc, int which, void*
 	if (n > max_bytes) return -MOSS_ERR_WORKSPACE_TOO_SMALL;
 	if (n > 0 && cudaMemcpyAsync(dst, src, (size_t)n, cudaMemcpyDeviceToDevice, stream) != cudaSuccess) return -MOSS_ERR_CUDA;
 	return n;
+}
+long long moss_export_state(void* stream, const MossScene* sc, int which, void* dst, long long max_bytes)
+{
+	return moss_export_state_batch(stream, sc, 1, which, dst, max_bytes);
 }
 
 // ---- fused skinning + covariance front end ---------------------------------------------------------------

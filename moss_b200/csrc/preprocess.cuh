@@ -192,6 +192,19 @@ __device__ __forceinline__ void sh_load(int D, int M, const float* __restrict__ 
 	}
 }
 
+// One quaternion row: a 16 B load when the array is 16 B-aligned (torch allocations are), four scalar loads for a
+// view that is not (e.g. a slice of a packed buffer whose offset is not a multiple of 4 floats).
+__device__ __forceinline__ float4 load_quat(const float* __restrict__ rotations, int i)
+{
+	if ((reinterpret_cast<uintptr_t>(rotations) & 15) == 0) return reinterpret_cast<const float4*>(rotations)[i];
+	return make_float4(rotations[4 * i], rotations[4 * i + 1], rotations[4 * i + 2], rotations[4 * i + 3]);
+}
+__device__ __forceinline__ void store_quat(float* __restrict__ out, int i, float4 v)
+{
+	if ((reinterpret_cast<uintptr_t>(out) & 15) == 0) { reinterpret_cast<float4*>(out)[i] = v; return; }
+	out[4 * i] = v.x; out[4 * i + 1] = v.y; out[4 * i + 2] = v.z; out[4 * i + 3] = v.w;
+}
+
 // ndc -> pixel, evaluated in fp64 like the reference (DGR auxiliary.h:41-44).
 __device__ __forceinline__ float ndc_to_pix(float v, int S)
 {
@@ -200,8 +213,9 @@ __device__ __forceinline__ float ndc_to_pix(float v, int S)
 
 constexpr int PRE_THREADS = 128;   // 20 k Gaussians -> 157 blocks: every SM gets work (256 left 69 of 148 idle)
 
+// grid = (ceil(P / PRE_THREADS), V): block row v preprocesses the Gaussians for view v ("virtual Gaussian" v*P + i).
 __global__ void __launch_bounds__(PRE_THREADS)
-preprocess_forward_kernel(int P, ViewParams vp,
+preprocess_forward_kernel(const __grid_constant__ ViewBatch vb,
 	const float* __restrict__ means3D, const float* __restrict__ shs, const float* __restrict__ colors_precomp,
 	const float* __restrict__ opacities, const float* __restrict__ scales, const float* __restrict__ rotations,
 	const float* __restrict__ cov3D_precomp, int prefiltered,
@@ -210,9 +224,13 @@ preprocess_forward_kernel(int P, ViewParams vp,
 	// Every global read of the Gaussian is issued here, before the first data-dependent branch, so the kernel pays
 	// ONE DRAM round trip instead of a chain of four (position -> covariance -> SH -> opacity); with a cold L2 and
 	// one block per SM that chain was most of the launch's duration.  Culled Gaussians read a little more than needed.
+	const int P = vb.P;
+	const int view = blockIdx.y;
+	const ViewCam& cam = vb.cam[view];
 	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
 	const bool active = idx < P;
 	const int li = active ? idx : 0;
+	const size_t vid = (size_t)view * P + idx;            // virtual Gaussian: row of the per-view state
 	const float px = means3D[3 * li], py = means3D[3 * li + 1], pz = means3D[3 * li + 2];
 	const float opac = opacities[li];
 	float c3[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -222,27 +240,25 @@ preprocess_forward_kernel(int P, ViewParams vp,
 #pragma unroll
 		for (int k = 0; k < 6; k++) c3[k] = cov3D_precomp[6 * li + k];
 	} else {
-		quat = reinterpret_cast<const float4*>(rotations)[li];
+		quat = load_quat(rotations, li);
 		sc3[0] = scales[3 * li]; sc3[1] = scales[3 * li + 1]; sc3[2] = scales[3 * li + 2];
 	}
 	float shl[48];
 	float rgb_in[3] = {0.f, 0.f, 0.f};
 	if (colors_precomp == nullptr) {
-		const bool vec_ok = ((reinterpret_cast<uintptr_t>(shs) & 15) == 0) && ((3 * vp.M) % 4 == 0);
-		sh_load(vp.D, vp.M, shs + (size_t)li * vp.M * 3, vec_ok, shl);
+		const bool vec_ok = ((reinterpret_cast<uintptr_t>(shs) & 15) == 0) && ((3 * vb.M) % 4 == 0);
+		sh_load(vb.D, vb.M, shs + (size_t)li * vb.M * 3, vec_ok, shl);
 	} else {
 #pragma unroll
 		for (int c = 0; c < 3; c++) rgb_in[c] = colors_precomp[3 * li + c];
 	}
 
 	__shared__ float s_view[16], s_proj[16], s_cam[3];
-	if (threadIdx.x < 16) s_view[threadIdx.x] = vp.view[threadIdx.x];
-	else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
-	else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
+	if (threadIdx.x < 16) s_view[threadIdx.x] = cam.view[threadIdx.x];
+	else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = cam.proj[threadIdx.x - 16];
+	else if (threadIdx.x < 35 && colors_precomp == nullptr) s_cam[threadIdx.x - 32] = cam.campos[threadIdx.x - 32];
 	__syncthreads();
 	if (!active) return;
-#pragma unroll
-	for (int k = 0; k < GRAD_ACC_VEC; k++) g.grad_acc[GRAD_ACC_VEC * (size_t)idx + k] = make_float4(0.f, 0.f, 0.f, 0.f);
 
 	int my_radius = 0;
 	uint32_t touched = 0;
@@ -263,14 +279,14 @@ preprocess_forward_kernel(int P, ViewParams vp,
 		const float ndc_x = fmul(hx, p_w), ndc_y = fmul(hy, p_w);
 
 		if (cov3D_precomp == nullptr) {
-			cov3d_from_scale_rot(sc3[0], sc3[1], sc3[2], vp.scale_modifier, quat.x, quat.y, quat.z, quat.w, c3);
+			cov3d_from_scale_rot(sc3[0], sc3[1], sc3[2], vb.scale_modifier, quat.x, quat.y, quat.z, quat.w, c3);
 #pragma unroll
-			for (int k = 0; k < 6; k++) g.cov3D[6 * idx + k] = c3[k];
+			for (int k = 0; k < 6; k++) g.cov3D[6 * vid + k] = c3[k];
 		}
 
 		const float tx = affine_row(px, py, pz, s_view[0], s_view[4], s_view[8], s_view[12]);
 		const float ty = affine_row(px, py, pz, s_view[1], s_view[5], s_view[9], s_view[13]);
-		const Float3 cov = cov2d_ewa(tx, ty, vz, s_view, vp.focal_x, vp.focal_y, vp.tanfovx, vp.tanfovy, c3);
+		const Float3 cov = cov2d_ewa(tx, ty, vz, s_view, cam.focal_x, cam.focal_y, cam.tanfovx, cam.tanfovy, c3);
 
 		const float det = ffma(cov.x, cov.z, -fmul(cov.y, cov.y));   // SASS: FMUL b*b; FFMA a*c-bb
 		if (det == 0.0f) break;
@@ -283,10 +299,10 @@ preprocess_forward_kernel(int P, ViewParams vp,
 		const float sq = fsqrt(fmaxf(ffma(mid, mid, -det), 0.1f));
 		const float lmax = fmaxf(fadd(mid, sq), fsub(mid, sq));
 		const float radius_f = ceilf(fmul(fsqrt(lmax), 3.f));
-		const float pix_x = ndc_to_pix(ndc_x, vp.W), pix_y = ndc_to_pix(ndc_y, vp.H);
+		const float pix_x = ndc_to_pix(ndc_x, vb.W), pix_y = ndc_to_pix(ndc_y, vb.H);
 		const int ri = (int)radius_f;              // DGR auxiliary.h:46 (float -> int max_radius)
 		const float rf = (float)ri;
-		const uint32_t gx = vp.grid_x, gy = vp.grid_y;
+		const uint32_t gx = vb.grid_x, gy = vb.grid_y;
 		const uint32_t rminx = min(gx, (uint32_t)max(0, (int)fmul(fsub(pix_x, rf), 0.0625f)));
 		const uint32_t rminy = min(gy, (uint32_t)max(0, (int)fmul(fsub(pix_y, rf), 0.0625f)));
 		const uint32_t rmaxx = min(gx, (uint32_t)max(0, (int)fmul(fadd(fadd(fadd(pix_x, rf), 16.f), -1.f), 0.0625f)));
@@ -297,7 +313,7 @@ preprocess_forward_kernel(int P, ViewParams vp,
 		float rgb[3];
 		uint8_t clamp_bits = 0;
 		if (colors_precomp == nullptr) {
-			sh_to_rgb(vp.D, shl, fsub(px, s_cam[0]), fsub(py, s_cam[1]), fsub(pz, s_cam[2]), rgb);
+			sh_to_rgb(vb.D, shl, fsub(px, s_cam[0]), fsub(py, s_cam[1]), fsub(pz, s_cam[2]), rgb);
 #pragma unroll
 			for (int c = 0; c < 3; c++) {
 				if (rgb[c] < 0.f) { clamp_bits |= (1u << c); rgb[c] = 0.f; }
@@ -307,23 +323,27 @@ preprocess_forward_kernel(int P, ViewParams vp,
 			for (int c = 0; c < 3; c++) rgb[c] = rgb_in[c];
 		}
 
-		g.depths[idx] = vz;
-		g.means2D[idx] = make_float2(pix_x, pix_y);
-		g.conic_opacity[idx] = make_float4(conic_x, conic_y, conic_z, opac);
-		g.feat[idx] = make_float4(rgb[0], rgb[1], rgb[2], vz);
-		g.clamped[idx] = clamp_bits;
-		g.rect[idx] = make_ushort4((unsigned short)rminx, (unsigned short)rminy, (unsigned short)rmaxx, (unsigned short)rmaxy);
+		g.depths[vid] = vz;
+		g.means2D[vid] = make_float2(pix_x, pix_y);
+		g.conic_opacity[vid] = make_float4(conic_x, conic_y, conic_z, opac);
+		g.feat[vid] = make_float4(rgb[0], rgb[1], rgb[2], vz);
+		g.clamped[vid] = clamp_bits;
+		g.rect[vid] = make_ushort4((unsigned short)rminx, (unsigned short)rminy, (unsigned short)rmaxx, (unsigned short)rmaxy);
+		// the blend backward accumulates into this row; culled Gaussians never get one (and are never read back)
+#pragma unroll
+		for (int k = 0; k < GRAD_ACC_VEC; k++) g.grad_acc[GRAD_ACC_VEC * vid + k] = make_float4(0.f, 0.f, 0.f, 0.f);
 		my_radius = ri;
 		touched = area;
 		// bin: one counter per tile (replaces the per-Gaussian scan + key duplication + global sort)
 		const uint32_t sub = ((uint32_t)idx >> 5) & (TILE_SUB - 1);      // one sub-counter per counting warp
+		uint32_t* tc = tile_count + (size_t)view * vb.T * TILE_SUB;
 		for (uint32_t y = rminy; y < rmaxy; y++)
 			for (uint32_t x = rminx; x < rmaxx; x++)
-				atomicAdd(&tile_count[(y * gx + x) * TILE_SUB + sub], 1u);
+				atomicAdd(&tc[(y * gx + x) * TILE_SUB + sub], 1u);
 	} while (false);
 
-	radii[idx] = my_radius;
-	g.tiles_touched[idx] = touched;
+	radii[vid] = my_radius;
+	g.tiles_touched[vid] = touched;
 }
 
 // present[i] = view.z > 0.2   (DGR rasterizer_impl.cu:54-66 with auxiliary.h:139-164)

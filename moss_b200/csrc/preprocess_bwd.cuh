@@ -10,39 +10,69 @@
 
 namespace moss {
 
+// Where the per-Gaussian parameter gradients of view v go.  One view: the caller's tensors.  A batch of V views: row
+// v of a scratch area (ptr + v * view_stride), summed over the views afterwards by sum_views_kernel in a fixed order.
+struct ParamGradOut {
+	float* color;     // [P,3]  (colors_precomp path)
+	float* opacity;   // [P]
+	float* mean3D;    // [P,3]
+	float* cov3D;     // [P,6]
+	float* sh;        // [P,M,3] or null
+	float* scale;     // [P,3] or null
+	float* rot;       // [P,4] or null
+	size_t view_stride;   // floats between consecutive views' rows (0 for a single view)
+};
+
+// grid = (ceil(P / PRE_THREADS), V)
 __global__ void __launch_bounds__(PRE_THREADS)
-preprocess_backward_kernel(int P, ViewParams vp,
+preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	const float* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
 	const float* __restrict__ scales, const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
 	GeomWS g,
-	float* __restrict__ dL_dmean2D, float* __restrict__ dL_dconic, float* __restrict__ dL_dcolor,
-	float* __restrict__ dL_dopacity, float* __restrict__ dL_dmean3D, float* __restrict__ dL_dcov3D, float* __restrict__ dL_dsh,
-	float* __restrict__ dL_dscale, float* __restrict__ dL_drot, int deterministic, const uint32_t* __restrict__ counters)
+	float* __restrict__ dL_dmean2D_all, float* __restrict__ dL_dconic_all, ParamGradOut po,
+	int deterministic, const uint32_t* __restrict__ counters)
 {
 	// All global reads of the Gaussian are issued before the first data-dependent branch (one DRAM round trip instead
-	// of a chain; see preprocess_forward_kernel).
+	// of a chain; see preprocess_forward_kernel) -- except the accumulator row, which only visible Gaussians own.
+	const int P = vb.P;
+	const int view = blockIdx.y;
+	const ViewCam& cam = vb.cam[view];
 	const int idx = blockIdx.x * PRE_THREADS + threadIdx.x;
 	const bool active = idx < P;
 	const int li = active ? idx : 0;
-	const int M = vp.M, D = vp.D;
-	const int radius = radii[li];
-	float4 acc0, acc1;
-	float acc2;
-	if (!deterministic) {
-		acc0 = g.grad_acc[GRAD_ACC_VEC * (size_t)li]; acc1 = g.grad_acc[GRAD_ACC_VEC * (size_t)li + 1];
-		acc2 = g.grad_acc[GRAD_ACC_VEC * (size_t)li + 2].x;
-	} else {
-		// nine int64 fixed-point sums (blend.cuh) -> float
-		const float inv = det_scale_from_bits(counters[6], true);
-		const long long* a = reinterpret_cast<const long long*>(g.grad_acc + GRAD_ACC_VEC * (size_t)li);
-		acc0 = make_float4((float)a[0] * inv, (float)a[1] * inv, (float)a[2] * inv, (float)a[3] * inv);
-		acc1 = make_float4((float)a[4] * inv, (float)a[5] * inv, (float)a[6] * inv, (float)a[7] * inv);
-		acc2 = (float)a[8] * inv;
+	const size_t vid = (size_t)view * P + li;
+	const int M = vb.M, D = vb.D;
+	const int radius = radii[vid];
+	const size_t vo = (size_t)view * po.view_stride;
+	float* __restrict__ dL_dmean2D = dL_dmean2D_all + 3 * (size_t)view * P;
+	float* __restrict__ dL_dconic = dL_dconic_all ? dL_dconic_all + 4 * (size_t)view * P : nullptr;
+	float* __restrict__ dL_dcolor = po.color + vo;
+	float* __restrict__ dL_dopacity = po.opacity + vo;
+	float* __restrict__ dL_dmean3D = po.mean3D + vo;
+	float* __restrict__ dL_dcov3D = po.cov3D + vo;
+	float* __restrict__ dL_dsh = po.sh ? po.sh + vo : nullptr;
+	float* __restrict__ dL_dscale = po.scale ? po.scale + vo : nullptr;
+	float* __restrict__ dL_drot = po.rot ? po.rot + vo : nullptr;
+	float4 acc0 = make_float4(0.f, 0.f, 0.f, 0.f), acc1 = acc0;
+	float acc2 = 0.f;
+	if (radius > 0) {
+		if (!deterministic) {
+			acc0 = g.grad_acc[GRAD_ACC_VEC * vid]; acc1 = g.grad_acc[GRAD_ACC_VEC * vid + 1];
+			acc2 = g.grad_acc[GRAD_ACC_VEC * vid + 2].x;
+		} else {
+			// nine int64 fixed-point sums (blend.cuh) -> float
+			const float inv = det_scale_from_bits(counters[6], true);
+			const long long* a = reinterpret_cast<const long long*>(g.grad_acc + GRAD_ACC_VEC * vid);
+			const long long* e = reinterpret_cast<const long long*>(g.grad_ext + GRAD_EXT_VEC * vid);
+			acc0 = make_float4((float)a[0] * inv, (float)a[1] * inv, (float)a[2] * inv, (float)a[3] * inv);
+			acc1 = make_float4((float)a[4] * inv, (float)a[5] * inv, (float)e[0] * inv, (float)e[1] * inv);
+			acc2 = (float)e[2] * inv;
+		}
 	}
 	const float mx = means3D[3 * li], my = means3D[3 * li + 1], mz = means3D[3 * li + 2];
-	const float* c3 = cov3D_precomp ? (cov3D_precomp + 6 * (size_t)li) : (g.cov3D + 6 * (size_t)li);
+	const float* c3 = cov3D_precomp ? (cov3D_precomp + 6 * (size_t)li) : (g.cov3D + 6 * vid);
 	const float V0 = c3[0], V1 = c3[1], V2 = c3[2], V3 = c3[3], V4 = c3[4], V5 = c3[5];
-	const uint8_t cl = g.clamped[li];
+	const uint8_t cl = g.clamped[vid];
 	const bool sh_vec = shs && ((reinterpret_cast<uintptr_t>(shs) & 15) == 0) && ((3 * M) % 4 == 0);
 	const bool dsh_vec = shs && M == 16 && ((reinterpret_cast<uintptr_t>(dL_dsh) & 15) == 0);
 	float sh[48];
@@ -50,25 +80,31 @@ preprocess_backward_kernel(int P, ViewParams vp,
 	float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
 	float sc_in[3] = {0.f, 0.f, 0.f};
 	if (scales) {
-		q = reinterpret_cast<const float4*>(rotations)[li];
+		q = load_quat(rotations, li);
 		sc_in[0] = scales[3 * li]; sc_in[1] = scales[3 * li + 1]; sc_in[2] = scales[3 * li + 2];
 	}
 
 	__shared__ float v[16], pr[16], s_cam[3];
-	if (threadIdx.x < 16) v[threadIdx.x] = vp.view[threadIdx.x];
-	else if (threadIdx.x < 32) pr[threadIdx.x - 16] = vp.proj[threadIdx.x - 16];
-	else if (threadIdx.x < 35) s_cam[threadIdx.x - 32] = vp.campos[threadIdx.x - 32];
+	if (threadIdx.x < 16) v[threadIdx.x] = cam.view[threadIdx.x];
+	else if (threadIdx.x < 32) pr[threadIdx.x - 16] = cam.proj[threadIdx.x - 16];
+	else if (threadIdx.x < 35 && shs) s_cam[threadIdx.x - 32] = cam.campos[threadIdx.x - 32];
 	__syncthreads();
 	if (!active) return;
 
 	// The blend backward accumulated into g.grad_acc (vector atomics); unpack it into the caller's tensors, which are
 	// therefore fully written here (no zero-fill beforehand), and leave the accumulators zero for the next backward.
+	if (radius > 0) {
 #pragma unroll
-	for (int k = 0; k < GRAD_ACC_VEC; k++) g.grad_acc[GRAD_ACC_VEC * (size_t)idx + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+		for (int k = 0; k < GRAD_ACC_VEC; k++) g.grad_acc[GRAD_ACC_VEC * vid + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+		if (deterministic) {
+#pragma unroll
+			for (int k = 0; k < GRAD_EXT_VEC; k++) g.grad_ext[GRAD_EXT_VEC * vid + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+		}
+	}
 	dL_dcolor[3 * idx] = acc0.x; dL_dcolor[3 * idx + 1] = acc0.y; dL_dcolor[3 * idx + 2] = acc0.z;
 	dL_dopacity[idx] = acc0.w;
 	dL_dmean2D[3 * idx] = acc1.x; dL_dmean2D[3 * idx + 1] = acc1.y; dL_dmean2D[3 * idx + 2] = 0.f;
-	dL_dconic[4 * idx] = acc1.z; dL_dconic[4 * idx + 1] = acc1.w; dL_dconic[4 * idx + 2] = 0.f; dL_dconic[4 * idx + 3] = acc2;
+	if (dL_dconic) { dL_dconic[4 * idx] = acc1.z; dL_dconic[4 * idx + 1] = acc1.w; dL_dconic[4 * idx + 2] = 0.f; dL_dconic[4 * idx + 3] = acc2; }
 
 	if (!(radius > 0)) {
 #pragma unroll
@@ -87,7 +123,7 @@ preprocess_backward_kernel(int P, ViewParams vp,
 		if (scales) {
 #pragma unroll
 			for (int k = 0; k < 3; k++) dL_dscale[3 * idx + k] = 0.f;
-			reinterpret_cast<float4*>(dL_drot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+			store_quat(dL_drot, idx, make_float4(0.f, 0.f, 0.f, 0.f));
 		}
 		return;
 	}
@@ -97,13 +133,13 @@ preprocess_backward_kernel(int P, ViewParams vp,
 	float tx = v[0] * mx + v[4] * my + v[8] * mz + v[12];
 	float ty = v[1] * mx + v[5] * my + v[9] * mz + v[13];
 	const float tz = v[2] * mx + v[6] * my + v[10] * mz + v[14];
-	const float limx = 1.3f * vp.tanfovx, limy = 1.3f * vp.tanfovy;
+	const float limx = 1.3f * cam.tanfovx, limy = 1.3f * cam.tanfovy;
 	const float txtz = tx / tz, tytz = ty / tz;
 	tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
 	ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
 	const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
 	const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
-	const float hx = vp.focal_x, hy = vp.focal_y;
+	const float hx = cam.focal_x, hy = cam.focal_y;
 
 	const float J00 = hx / tz, J02 = -(hx * tx) / (tz * tz);
 	const float J11 = hy / tz, J12 = -(hy * ty) / (tz * tz);
@@ -267,7 +303,7 @@ preprocess_backward_kernel(int P, ViewParams vp,
 	// ---- cov3D -> scale, (un-normalised) quaternion --------------------------------------------------
 	if (scales) {
 		const float r = q.x, x = q.y, y = q.z, z = q.w;
-		const float s[3] = {vp.scale_modifier * sc_in[0], vp.scale_modifier * sc_in[1], vp.scale_modifier * sc_in[2]};
+		const float s[3] = {vb.scale_modifier * sc_in[0], vb.scale_modifier * sc_in[1], vb.scale_modifier * sc_in[2]};
 		// R[i][j]: column i, row j (GLM listing of DGR backward.cu:288-292)
 		const float R[3][3] = {
 			{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
@@ -295,7 +331,50 @@ preprocess_backward_kernel(int P, ViewParams vp,
 		dq.y = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) - 4 * x * (dMt[2][2] + dMt[1][1]);
 		dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
 		dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
-		reinterpret_cast<float4*>(dL_drot)[idx] = dq;   // no normalisation Jacobian (DGR backward.cu:340)
+		store_quat(dL_drot, idx, dq);   // no normalisation Jacobian (DGR backward.cu:340)
+	}
+}
+
+// Batched backward, V > 1: out[j] = sum_v rows[v*stride + j] over the views, in view order (fixed order: the sum is
+// reproducible).  One launch covers the (up to 7) parameter-gradient arrays: blockIdx.y picks the array.
+struct SumViewsArgs {
+	float* dst[7];
+	const float* src[7];       // row of view 0
+	size_t n[7];               // floats
+	size_t view_stride;
+	int V;
+};
+constexpr int SUMV_THREADS = 256;
+__global__ void __launch_bounds__(SUMV_THREADS)
+sum_views_kernel(const __grid_constant__ SumViewsArgs a)
+{
+	const int k = blockIdx.y;
+	float* __restrict__ dst = a.dst[k];
+	const float* __restrict__ src = a.src[k];
+	const size_t n = a.n[k];
+	if (!dst || n == 0) return;
+	const size_t stride = (size_t)gridDim.x * SUMV_THREADS;
+	if ((((uintptr_t)dst | (uintptr_t)src) & 15) == 0 && (a.view_stride & 3) == 0) {
+		const size_t n4 = n >> 2;
+		for (size_t i = (size_t)blockIdx.x * SUMV_THREADS + threadIdx.x; i < n4; i += stride) {
+			float4 s = reinterpret_cast<const float4*>(src)[i];
+			for (int v = 1; v < a.V; v++) {
+				const float4 x = reinterpret_cast<const float4*>(src + (size_t)v * a.view_stride)[i];
+				s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w;
+			}
+			reinterpret_cast<float4*>(dst)[i] = s;
+		}
+		for (size_t i = (n4 << 2) + (size_t)blockIdx.x * SUMV_THREADS + threadIdx.x; i < n; i += stride) {
+			float s = src[i];
+			for (int v = 1; v < a.V; v++) s += src[(size_t)v * a.view_stride + i];
+			dst[i] = s;
+		}
+	} else {
+		for (size_t i = (size_t)blockIdx.x * SUMV_THREADS + threadIdx.x; i < n; i += stride) {
+			float s = src[i];
+			for (int v = 1; v < a.V; v++) s += src[(size_t)v * a.view_stride + i];
+			dst[i] = s;
+		}
 	}
 }
 

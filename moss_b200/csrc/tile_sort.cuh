@@ -318,29 +318,32 @@ __device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 ra
 	MOSS_TD(9);
 }
 
-// One block per tile, in tile_order (deepest first).
+// One block per tile: block b sorts the (b / V)-th deepest tile of view b % V (deepest tiles of every view first).
+// `tile` handed to the sort is the tile's index INSIDE its view (what the reference's 64-bit keys carry).
 __global__ void __launch_bounds__(TILE_PIX)
-tile_sort_kernel(ImageWS im, BinWS b, CkptWS ck)
+tile_sort_kernel(ImageWS im, BinWS b, CkptWS ck, int T, int V)
 {
 	extern __shared__ __align__(16) unsigned char sort_smem_raw[];
 	SortSmem& ss = *reinterpret_cast<SortSmem*>(sort_smem_raw);
 	__shared__ uint32_t seg_off;
 	if (im.counters[1]) return;   // binning overflow: the host re-runs with a larger buffer
-	if (blockIdx.x >= im.counters[3]) return;                 // only non-empty tiles have work
-	const int tile = (int)im.tile_order[blockIdx.x];
-	const uint2 range = im.ranges[tile];
+	const uint32_t view = blockIdx.x % (uint32_t)V, rank = blockIdx.x / (uint32_t)V;
+	if (rank >= im.view_busy[view]) return;                   // only non-empty tiles have work
+	const int vtile = (int)im.tile_order[(size_t)view * T + rank];   // virtual tile v*T + t
+	const int tile = vtile - (int)view * T;
+	const uint2 range = im.ranges[vtile];
 	const int n = (int)(range.y - range.x);
 	if (ck.rec && n > 0) {
-		// hand the tile its backward segments and boundary records.  Blocks start in tile_order (deepest first), so
-		// the deep tiles' segments land at the front of seg_map; the exact order only affects scheduling.
+		// hand the tile its backward segments and boundary records.  Blocks start deepest tiles first, so the deep
+		// tiles' segments land at the front of seg_map; the exact order only affects scheduling.
 		const uint32_t nseg = ((uint32_t)n + CKPT_SEG - 1) / CKPT_SEG;
 		if (threadIdx.x == 0) {
 			seg_off = atomicAdd(&im.counters[4], nseg);
-			ck.seg_base[tile] = atomicAdd(&im.counters[5], nseg - 1u);
+			ck.seg_base[vtile] = atomicAdd(&im.counters[5], nseg - 1u);
 		}
 		__syncthreads();
 		for (uint32_t i = threadIdx.x; i < nseg; i += TILE_PIX)
-			if (seg_off + i < ck.max_segs) ck.seg_map[seg_off + i] = make_uint2((uint32_t)tile, i);
+			if (seg_off + i < ck.max_segs) ck.seg_map[seg_off + i] = make_uint2((uint32_t)vtile, i);
 	}
 	MOSS_TT(0);
 	if (n > 0) tile_sort(ss, b, range, n, tile);

@@ -16,12 +16,15 @@ class GraphedStep:
     """One view's forward+backward as a CUDA graph over STATIC input tensors.
 
     inputs: dict with the tensors of ``rasterizer.forward_raw`` (means3D, shs, colors_precomp, opacities, scales,
-    rotations, cov3D_precomp; empty tensors for the absent ones).  ``grad_out`` (optional) is the packed gradient
+    rotations, cov3D_precomp; empty tensors for the absent ones).  ``raster_settings`` may be a LIST of settings: the
+    step is then one batched call over those views (``rasterizer.forward_batch_raw``; upstream gradients [V,3,H,W] /
+    [V,1,H,W]).  ``grad_out`` (optional) is the packed gradient
     buffer the backward writes (e.g. ``parallel.PeerGradBuffer.tensor``); ``after`` (optional) is called inside the
     capture after the backward (e.g. the gradient exchange)."""
 
-    def __init__(self, inputs, raster_settings, grads, grad_out=None, after=None, flags=0):
+    def __init__(self, inputs, raster_settings, grads, grad_out=None, after=None, flags=0, forward_only=False):
         self.inputs, self.rs, self.grads = inputs, raster_settings, grads
+        self.forward_only = forward_only      # eval render (render_ZJU.py:56-72 under no_grad): no backward in the graph
         self.flags = flags | _abi.FLAG_ASYNC
         dev = inputs["means3D"].device
         # learn the instance count of this view (synchronous call), then capture with a fixed capacity
@@ -41,9 +44,10 @@ class GraphedStep:
 
     def _run(self, flags, grad_out, after):
         i = self.inputs
-        color, radii, depth, alpha, st = R.forward_raw(i["means3D"], i["shs"], i["colors_precomp"], i["opacities"],
-                                                       i["scales"], i["rotations"], i["cov3D_precomp"], self.rs, flags=flags)
-        g = R.backward_raw(st, radii, *self.grads, out=grad_out)
+        fwd = R.forward_batch_raw if isinstance(self.rs, list) else R.forward_raw
+        color, radii, depth, alpha, st = fwd(i["means3D"], i["shs"], i["colors_precomp"], i["opacities"],
+                                             i["scales"], i["rotations"], i["cov3D_precomp"], self.rs, flags=flags)
+        g = None if self.forward_only else R.backward_raw(st, radii, *self.grads, out=grad_out)
         if after is not None:
             after(st)
         return color, radii, depth, alpha, st, g

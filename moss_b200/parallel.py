@@ -95,6 +95,8 @@ class PeerGradBuffer:
             except Exception:
                 mc = 0
         self.multicast_ptr = mc                 # 0: no NVLS mapping -> loads/stores on the peer pointers
+        self.path = "nvls" if mc else "peer"
+        self.kind = "peer-memory kernel (moss_peer_allreduce, " + ("NVLS multimem data phase" if mc else "peer loads/stores") + ")"
         self.error = torch.zeros(4, dtype=torch.int32, device=device)      # [0] timeout flag, [1] device-side epoch, [2] block counter
         self.device = device
         # everyone's pad is zero and mapped before the first kernel spins on it

@@ -83,7 +83,8 @@ def _want_ckpt(W, H):
 
 class RasterState:
     """Workspaces + scene descriptor of one forward call (kept alive for the backward)."""
-    __slots__ = ("scene", "ws", "binning", "ckpt", "flags", "num_rendered", "keep", "grad_buf", "param_grad_numel")
+    __slots__ = ("scene", "ws", "binning", "ckpt", "flags", "num_rendered", "keep", "grad_buf", "param_grad_numel",
+                 "V", "views", "batched")
 
     def __init__(self):
         self.scene = _abi.MossScene()
@@ -95,55 +96,78 @@ class RasterState:
         self.keep = None
         self.grad_buf = None
         self.param_grad_numel = 0
+        self.V = 1
+        self.views = None          # ctypes array of MossView (batched calls)
+        self.batched = False
 
 
-def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings,
-                flags=0):
-    """Forward through the C ABI.  Returns (color, radii, depth, alpha, RasterState)."""
+def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, settings_list, flags, batched):
     lib = _abi.load()
-    rs = raster_settings
+    rs = settings_list[0]
+    V = len(settings_list)
     if means3D.ndim != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")   # DGR/rasterize_points.cu:57-59
     if not means3D.is_cuda:
         raise RuntimeError("moss_b200 rasterizer needs CUDA tensors (there is no CPU path)")
+    if not 1 <= V <= _abi.MAX_VIEWS:
+        raise RuntimeError(f"a batched call takes 1..{_abi.MAX_VIEWS} views, got {V}")
     dev = means3D.device
     means3D = _f32c(means3D, "means3D")
     sh = _f32c(sh, "sh"); colors_precomp = _f32c(colors_precomp, "colors_precomp")
     opacities = _f32c(opacities, "opacities"); scales = _f32c(scales, "scales")
     rotations = _f32c(rotations, "rotations"); cov3Ds_precomp = _f32c(cov3Ds_precomp, "cov3Ds_precomp")
-    bg = _f32c(rs.bg, "bg"); view = _f32c(rs.viewmatrix, "viewmatrix")
-    proj = _f32c(rs.projmatrix, "projmatrix"); campos = _f32c(rs.campos, "campos")
+    cams = []
+    for r in settings_list:
+        if (int(r.image_height), int(r.image_width), int(r.sh_degree), float(r.scale_modifier), bool(r.prefiltered)) != \
+                (int(rs.image_height), int(rs.image_width), int(rs.sh_degree), float(rs.scale_modifier), bool(rs.prefiltered)):
+            raise RuntimeError("all views of a batched call share image size, SH degree, scale modifier and prefiltered")
+        cams.append((_f32c(r.bg, "bg"), _f32c(r.viewmatrix, "viewmatrix"), _f32c(r.projmatrix, "projmatrix"),
+                     _f32c(r.campos, "campos")))
 
     P = means3D.shape[0]
     H, W = int(rs.image_height), int(rs.image_width)
     M = sh.shape[1] if sh.numel() != 0 else 0
-    if rs.debug:
+    if any(r.debug for r in settings_list):
         flags |= _abi.FLAG_DEBUG
     export = 1 if (flags & _abi.FLAG_EXPORT_KEYS) else 0
 
     with torch.cuda.device(dev):
-        out = torch.empty((5, H, W), dtype=torch.float32, device=dev)
-        radii = torch.empty((P,), dtype=torch.int32, device=dev)
-        gbytes = _align(lib.moss_geom_workspace_bytes(P))
-        ibytes = lib.moss_image_workspace_bytes(W, H)
+        # three independent output tensors, like the reference (DGR/rasterize_points.cu:68-71): callers edit renders
+        # in place (render_ZJU.py), which autograd refuses on views of a shared multi-output buffer
+        lead = (V,) if batched else ()
+        color = torch.empty(lead + (3, H, W), dtype=torch.float32, device=dev)
+        depth = torch.empty(lead + (1, H, W), dtype=torch.float32, device=dev)
+        alpha = torch.empty(lead + (1, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty(lead + (P,), dtype=torch.int32, device=dev)
+        gbytes = _align(lib.moss_geom_workspace_bytes_batch(P, V))
+        ibytes = lib.moss_image_workspace_bytes_batch(W, H, V)
         ws = torch.empty((gbytes + ibytes,), dtype=torch.uint8, device=dev)
-        key = (P, W, H, dev.index)
+        key = (P, W, H, V, dev.index)
         cap = _capacity_hint.get(key, 0)
-        cap = max(int(cap * 1.25) + 4096, 4 * P + 4096)
+        cap = max(int(cap * 1.25) + 4096, (4 * P + 4096) * V)
         st = RasterState()
+        st.V, st.batched = V, batched
         sc = st.scene
         sc.P, sc.D, sc.M, sc.W, sc.H = P, int(rs.sh_degree), M, W, H
-        sc.bg = _ptr(bg); sc.means3D = _ptr(means3D); sc.shs = _ptr(sh); sc.colors_precomp = _ptr(colors_precomp)
+        sc.means3D = _ptr(means3D); sc.shs = _ptr(sh); sc.colors_precomp = _ptr(colors_precomp)
         sc.opacities = _ptr(opacities); sc.scales = _ptr(scales); sc.rotations = _ptr(rotations)
-        sc.cov3D_precomp = _ptr(cov3Ds_precomp); sc.viewmatrix = _ptr(view); sc.projmatrix = _ptr(proj)
-        sc.campos = _ptr(campos)
-        sc.scale_modifier = float(rs.scale_modifier); sc.tanfovx = float(rs.tanfovx); sc.tanfovy = float(rs.tanfovy)
+        sc.cov3D_precomp = _ptr(cov3Ds_precomp)
+        sc.scale_modifier = float(rs.scale_modifier)
         sc.prefiltered = 1 if rs.prefiltered else 0
+        if batched:
+            views = (_abi.MossView * V)()
+            for v, (r, (bg, view, proj, campos)) in enumerate(zip(settings_list, cams)):
+                views[v].viewmatrix = _ptr(view); views[v].projmatrix = _ptr(proj); views[v].campos = _ptr(campos)
+                views[v].bg = _ptr(bg); views[v].tanfovx = float(r.tanfovx); views[v].tanfovy = float(r.tanfovy)
+            st.views = views
+        else:
+            bg, view, proj, campos = cams[0]
+            sc.bg = _ptr(bg); sc.viewmatrix = _ptr(view); sc.projmatrix = _ptr(proj); sc.campos = _ptr(campos)
+            sc.tanfovx = float(rs.tanfovx); sc.tanfovy = float(rs.tanfovy)
         sc.geom_ws = ws.data_ptr(); sc.geom_bytes = gbytes
         sc.image_ws = ws.data_ptr() + gbytes; sc.image_bytes = ibytes
         stream = torch.cuda.current_stream(dev).cuda_stream
         nr = C.c_int(0)
-        color, depth, alpha = out[0:3], out[3:4], out[4:5]
         call_flags = flags
         want_ckpt = _want_ckpt(W, H)
         while True:
@@ -152,11 +176,15 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
             sc.binning_ws = binning.data_ptr(); sc.binning_bytes = bbytes
             ckpt = None
             if want_ckpt:
-                cbytes = lib.moss_ckpt_workspace_bytes(lib.moss_binning_capacity(bbytes, export), W, H)
+                cbytes = lib.moss_ckpt_workspace_bytes_batch(lib.moss_binning_capacity(bbytes, export), W, H, V)
                 ckpt = torch.empty((cbytes,), dtype=torch.uint8, device=dev)
                 sc.ckpt_ws = ckpt.data_ptr(); sc.ckpt_bytes = cbytes
-            status = lib.moss_rasterize_forward(stream, C.byref(sc), call_flags, color.data_ptr(), depth.data_ptr(),
-                                                alpha.data_ptr(), _ptr(radii), C.byref(nr))
+            if batched:
+                status = lib.moss_rasterize_forward_batch(stream, C.byref(sc), V, st.views, call_flags, color.data_ptr(),
+                                                          depth.data_ptr(), alpha.data_ptr(), _ptr(radii), C.byref(nr))
+            else:
+                status = lib.moss_rasterize_forward(stream, C.byref(sc), call_flags, color.data_ptr(), depth.data_ptr(),
+                                                    alpha.data_ptr(), _ptr(radii), C.byref(nr))
             if status == _abi.MOSS_ERR_BINNING_OVERFLOW:
                 cap = int(nr.value * 1.25) + 4096
                 call_flags = flags | _abi.FLAG_REBIN
@@ -167,23 +195,41 @@ def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3D
             _capacity_hint[key] = nr.value
         st.ws, st.binning, st.ckpt, st.flags, st.num_rendered = ws, binning, ckpt, flags, nr.value
         # tensors whose device pointers sit in the scene struct must outlive the backward
-        st.keep = (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, bg, view, proj, campos)
+        st.keep = (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp) + tuple(t for c in cams for t in c)
     return color, radii, depth, alpha, st
 
 
-def grad_layout(P, M, has_sh, has_sr):
+def forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings,
+                flags=0):
+    """Forward through the C ABI.  Returns (color, radii, depth, alpha, RasterState)."""
+    return _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, [raster_settings], flags, False)
+
+
+def forward_batch_raw(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, settings_list, flags=0):
+    """Batched forward (include/moss_splat.h: moss_rasterize_forward_batch): V cameras of the same Gaussians in one
+    launch sequence.  Returns (color [V,3,H,W], radii [V,P], depth [V,1,H,W], alpha [V,1,H,W], RasterState)."""
+    return _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, list(settings_list), flags, True)
+
+
+def grad_layout(P, M, has_sh, has_sr, V=1):
     """Packed gradient buffer (floats): parameter gradients first -- the prefix a data-parallel job all-reduces
-    -- then the two blend-only accumulators.  -> (dict name -> (offset, numel)), param_numel, zero_from, total."""
+    -- then the blend-only accumulators.  With V > 1 views the screen-space gradient `means2D` is per view
+    ([V,P,3], like `conic`) and leaves the all-reduced prefix.
+    -> (dict name -> (offset, numel)), param_numel, zero_from, total."""
     lay, o = {}, 0
+    pad = lambda n: (n + 3) // 4 * 4   # noqa: E731  every sub-array starts 16 B-aligned (vector stores of dsh / drot rows)
     for name, n in (("means3D", 3 * P), ("cov3D", 6 * P), ("sh", 3 * M * P if has_sh else 0),
                     ("scales", 3 * P if has_sr else 0), ("rotations", 4 * P if has_sr else 0)):
-        lay[name] = (o, n); o += n
-    zero_from = o                      # everything from here on is accumulated atomically by the blend backward
-    for name, n in (("opacity", P), ("means2D", 3 * P)):
-        lay[name] = (o, n); o += n
-    param_numel = o
-    for name, n in (("colors", 3 * P), ("conic", 4 * P)):
-        lay[name] = (o, n); o += n
+        lay[name] = (o, n); o += pad(n)
+    zero_from = o
+    lay["opacity"] = (o, P); o += pad(P)
+    if V > 1:
+        param_numel = o
+    lay["means2D"] = (o, 3 * P * V); o += pad(3 * P * V)
+    if V == 1:
+        param_numel = o
+    for name, n in (("colors", 3 * P), ("conic", 4 * P * V)):
+        lay[name] = (o, n); o += pad(n)
     return lay, param_numel, zero_from, o
 
 
@@ -191,20 +237,23 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
     """Backward through the C ABI.  Returns the 8 gradient tensors in the reference's C++ order
     (DGR/rasterize_points.cu:205): dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot.
     They are views of ONE packed buffer (kept in ``st.grad_buf``; ``st.param_grad_numel`` floats of parameter
-    gradient lead it), which may be supplied as ``out``."""
+    gradient lead it), which may be supplied as ``out``.  For a batched state the upstream gradients are
+    [V,3,H,W] / [V,1,H,W], dmeans2D is [V,P,3] and the parameter gradients are summed over the views."""
     lib = _abi.load()
     sc = st.scene
-    P, M, H, W = sc.P, sc.M, sc.H, sc.W
+    P, M, H, W, V = sc.P, sc.M, sc.H, sc.W, st.V
     dev = radii.device
+    lead = (V,) if st.batched else ()
     with torch.cuda.device(dev):
         def _g(t, shape, required=False):
             if t is None:      # no gradient reaches this output: the ABI takes NULL for depth / alpha
                 return torch.zeros(shape, dtype=torch.float32, device=dev) if required else None
             return _f32c(t, "grad").expand(shape).contiguous() if tuple(t.shape) != tuple(shape) else _f32c(t, "grad")
-        grad_color = _g(grad_color, (3, H, W), required=True); grad_depth = _g(grad_depth, (1, H, W)); grad_alpha = _g(grad_alpha, (1, H, W))
+        grad_color = _g(grad_color, lead + (3, H, W), required=True)
+        grad_depth = _g(grad_depth, lead + (1, H, W)); grad_alpha = _g(grad_alpha, lead + (1, H, W))
         has_sh = sc.shs is not None
         has_sr = sc.scales is not None
-        lay, param_numel, zero_from, total = grad_layout(P, M, has_sh, has_sr)
+        lay, param_numel, zero_from, total = grad_layout(P, M, has_sh, has_sr, V)
         # every row of every output is written by the backward preprocess kernel: nothing is zero-filled here
         # (the reference fills 9 tensors, DGR/rasterize_points.cu:158-166); the atomically accumulated blend
         # gradients live in a self-cleaning scratch inside the geometry workspace
@@ -214,7 +263,8 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
             o, n = lay[name]
             return buf[o:o + n].view(*shape)
         dmeans3D, dcov3D = v("means3D", P, 3), v("cov3D", P, 6)
-        dopacity, dmeans2D, dcolors, dconic = v("opacity", P, 1), v("means2D", P, 3), v("colors", P, 3), v("conic", P, 2, 2)
+        dopacity, dcolors = v("opacity", P, 1), v("colors", P, 3)
+        dmeans2D, dconic = v("means2D", *lead, P, 3), v("conic", *lead, P, 2, 2)
         dsh = v("sh", P, M, 3) if has_sh else torch.zeros((P, 0, 3), dtype=torch.float32, device=dev)
         if has_sr:
             dscales, drot = v("scales", P, 3), v("rotations", P, 4)
@@ -222,14 +272,24 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
             dscales = torch.zeros((P, 3), dtype=torch.float32, device=dev)
             drot = torch.zeros((P, 4), dtype=torch.float32, device=dev)
         stream = torch.cuda.current_stream(dev).cuda_stream
-        status = lib.moss_rasterize_backward(
-            stream, C.byref(sc), flags | st.flags, _ptr(radii),
-            grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha),
-            _ptr(dmeans2D), _ptr(dconic), _ptr(dopacity), _ptr(dcolors), _ptr(dmeans3D), _ptr(dcov3D),
-            _ptr(dsh) if has_sh else None, _ptr(dscales) if has_sr else None, _ptr(drot) if has_sr else None)
+        outs = (_ptr(dmeans2D), _ptr(dconic), _ptr(dopacity), _ptr(dcolors), _ptr(dmeans3D), _ptr(dcov3D),
+                _ptr(dsh) if has_sh else None, _ptr(dscales) if has_sr else None, _ptr(drot) if has_sr else None)
+        if st.batched:
+            tbytes = lib.moss_batch_grad_workspace_bytes(P, M, V)
+            tmp = torch.empty((max(tbytes, 16),), dtype=torch.uint8, device=dev)
+            status = lib.moss_rasterize_backward_batch(
+                stream, C.byref(sc), V, st.views, flags | st.flags, _ptr(radii),
+                grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha), *outs, tmp.data_ptr(), tbytes)
+        else:
+            status = lib.moss_rasterize_backward(
+                stream, C.byref(sc), flags | st.flags, _ptr(radii),
+                grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha), *outs)
         _abi.check(status, "moss_rasterize_backward")
         st.grad_buf, st.param_grad_numel = buf, param_numel
     return dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot
+
+
+backward_batch_raw = backward_raw      # the state knows whether it came from a batched forward
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
@@ -239,11 +299,14 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales,
 
 
 class _RasterizeGaussians(torch.autograd.Function):
+    """One view (``raster_settings`` is a GaussianRasterizationSettings) or a batch (a list/tuple of them)."""
+
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                 raster_settings):
-        color, radii, depth, alpha, st = forward_raw(means3D, sh, colors_precomp, opacities, scales, rotations,
-                                                     cov3Ds_precomp, raster_settings)
+        batched = isinstance(raster_settings, (list, tuple)) and not isinstance(raster_settings, GaussianRasterizationSettings)
+        color, radii, depth, alpha, st = _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                                                  list(raster_settings) if batched else [raster_settings], 0, batched)
         ctx.raster_settings = raster_settings
         ctx.num_rendered = st.num_rendered
         ctx.mark_non_differentiable(radii)
@@ -266,6 +329,24 @@ class _RasterizeGaussians(torch.autograd.Function):
         # same order as DGR/diff_gaussian_rasterization/__init__.py:146-156
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
                 grad_rotations, grad_cov3Ds_precomp, None)
+
+
+def rasterize_batch(means3D, means2D, opacities, settings_list, shs=None, colors_precomp=None, scales=None,
+                    rotations=None, cov3D_precomp=None):
+    """V cameras of the SAME Gaussians in one launch sequence (no reference counterpart: MOSS renders one view per
+    iteration, train_ZJU.py:93-100).  ``settings_list``: V GaussianRasterizationSettings that
+    share image size, SH degree and scale modifier; ``means2D`` [V,P,3] is the screen-space gradient sink of every view.
+    -> (color [V,3,H,W], radii [V,P], depth [V,1,H,W], alpha [V,1,H,W]); view v equals the single-view call bit for
+    bit, and the parameter gradients are the sums over the views (in view order)."""
+    if (shs is None) == (colors_precomp is None):
+        raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+    if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+            ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+        raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+    e = _EMPTY
+    return _RasterizeGaussians.apply(means3D, means2D, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
+                                     opacities, e if scales is None else scales, e if rotations is None else rotations,
+                                     e if cov3D_precomp is None else cov3D_precomp, list(settings_list))
 
 
 class GaussianRasterizer(nn.Module):
@@ -308,12 +389,16 @@ class GaussianRasterizer(nn.Module):
                                    cov3D_precomp, raster_settings)
 
 
-def export_state(st, name):
-    """Copy one internal state array of a forward call into a fresh tensor (parity tests)."""
+def export_state(st, name, view=None):
+    """Copy one internal state array of a forward call into a fresh tensor (parity tests).  For a batched state
+    ``view=v`` returns that view's slice in single-view conventions (ranges / point_list relative to the view's own
+    instance list, Gaussian ids 0..P-1), ``view=None`` the raw batch arrays."""
     lib = _abi.load()
     sc = st.scene
-    P, N = sc.P, sc.W * sc.H
-    T = ((sc.W + 15) // 16) * ((sc.H + 15) // 16)
+    V = st.V
+    P, N = sc.P * V, sc.W * sc.H * V
+    T1 = ((sc.W + 15) // 16) * ((sc.H + 15) // 16)
+    T = T1 * V
     R = max(st.num_rendered, 0)
     dev = st.ws.device
     spec = {
@@ -321,15 +406,29 @@ def export_state(st, name):
         "cov3D": (torch.float32, (P, 6)), "conic_opacity": (torch.float32, (P, 4)), "rgb": (torch.float32, (P, 3)),
         "tiles_touched": (torch.int32, (P,)), "keys_sorted": (torch.int64, (R,)), "point_list": (torch.int32, (R,)),
         "ranges": (torch.int32, (T, 2)), "n_contrib": (torch.int32, (N,)), "final_T": (torch.float32, (N,)),
-        "counters": (torch.int32, (4,)),
+        "counters": (torch.int32, (4,)), "view_base": (torch.int32, (V + 1,)),
     }[name]
     out = torch.empty(spec[1], dtype=spec[0], device=dev)
     with torch.cuda.device(dev):
-        n = lib.moss_export_state(torch.cuda.current_stream(dev).cuda_stream, C.byref(sc), _abi.STATE[name],
-                                  out.data_ptr(), out.numel() * out.element_size())
+        n = lib.moss_export_state_batch(torch.cuda.current_stream(dev).cuda_stream, C.byref(sc), V, _abi.STATE[name],
+                                        out.data_ptr(), out.numel() * out.element_size())
     if n < 0:
         raise RuntimeError(f"moss_export_state({name}) failed: {lib.moss_error_string(int(-n)).decode()}")
-    return out
+    if view is None or name in ("counters", "view_base"):
+        return out
+    v = int(view)
+    if name in ("keys_sorted", "point_list", "ranges"):
+        base = export_state(st, "view_base").cpu()
+        lo, hi = int(base[v]), int(base[v + 1])
+        if name == "ranges":
+            r = out[v * T1:(v + 1) * T1].clone()
+            r[r[:, 1] > 0] -= lo                   # empty tiles stay (0,0) like the reference's memset
+            return r
+        if name == "point_list":
+            return out[lo:hi] - v * sc.P
+        return out[lo:hi].clone()
+    per = out.shape[0] // V
+    return out[v * per:(v + 1) * per].clone()
 
 
 def export_state_counters(st):

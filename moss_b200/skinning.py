@@ -101,12 +101,16 @@ class FrameCache:
         self.val = None
 
     def get(self, smpl, t_params):
-        key = (t_params["poses"].data_ptr(), t_params["shapes"].data_ptr(), smpl.v_template.data_ptr())
+        # keyed on storage address AND in-place version of the three tensors; the tensors themselves are kept
+        # referenced while cached, so the caching allocator cannot hand their address to different contents
+        src = (t_params["poses"], t_params["shapes"], smpl.v_template)
+        key = tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in src)
         if self.key != key:
             with torch.no_grad():
                 rm = batch_rodrigues(t_params["poses"].reshape(-1, 3))
                 self.val = (_joint_transforms(smpl, t_params["shapes"], rm).contiguous(), _pose_offsets(smpl, rm).contiguous())
             self.key = key
+            self.src = src
         return self.val
 
 

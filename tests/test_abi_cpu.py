@@ -28,7 +28,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_versions_and_strings(lib):
-    assert lib.moss_abi_version() == 8
+    assert lib.moss_abi_version() == 9
     assert lib.moss_error_string(0) == b"ok"
     assert b"binning" in lib.moss_error_string(_abi.MOSS_ERR_BINNING_OVERFLOW)
 
@@ -51,6 +51,22 @@ def test_invalid_arguments_are_rejected_without_a_gpu(lib):
     sc = _abi.MossScene()
     assert lib.moss_rasterize_forward(None, C.byref(sc), 0, None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
     assert lib.moss_mark_visible(None, -1, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
+
+
+def test_batch_entry_points_validate_without_a_gpu(lib):
+    sc = _abi.MossScene()
+    views = (_abi.MossView * 2)()
+    assert lib.moss_sizeof_view() == C.sizeof(_abi.MossView)
+    assert lib.moss_rasterize_forward_batch(None, C.byref(sc), 2, views, 0, None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    assert lib.moss_rasterize_forward_batch(None, C.byref(sc), 2, None, 0, None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    # workspace queries scale with the number of views; one view equals the single-view query
+    assert lib.moss_geom_workspace_bytes_batch(20000, 1) == lib.moss_geom_workspace_bytes(20000)
+    assert lib.moss_image_workspace_bytes_batch(512, 512, 1) == lib.moss_image_workspace_bytes(512, 512)
+    assert lib.moss_geom_workspace_bytes_batch(20000, 23) >= 23 * 70 * 20000
+    assert lib.moss_image_workspace_bytes_batch(512, 512, 23) >= 23 * 8 * 512 * 512
+    assert lib.moss_ckpt_workspace_bytes_batch(100000, 512, 512, 1) == lib.moss_ckpt_workspace_bytes(100000, 512, 512)
+    assert lib.moss_batch_grad_workspace_bytes(20000, 16, 1) == 0
+    assert lib.moss_batch_grad_workspace_bytes(20000, 16, 23) >= 23 * 4 * 20000 * (1 + 3 + 3 + 6 + 48 + 3 + 4)
 
 
 def test_scene_struct_layout_matches_header(lib):
