@@ -320,27 +320,25 @@ class OursHarness:
         """One step as stream launches of the raw C ABI."""
         color, radii, depth, alpha, st = self.forward(self.rs_of(self.group_of(i)))
         if not self.forward_only:
-            self.M.backward_raw(st, radii, self.gc, self.gd, self.ga, out=self.peer.tensor if self.peer is not None else None)
-            if self.world > 1 and collective:
-                self.exchange(st)
+            if self.peer is not None and collective:
+                self.M.backward_raw(st, radii, self.gc, self.gd, self.ga, push=self.peer)      # exchange fused into the backward
+            else:
+                self.M.backward_raw(st, radii, self.gc, self.gd, self.ga)
+                if self.world > 1 and collective:
+                    self.exchange(st)
         self.state["st"], self.state["radii"] = st, radii
         return st
 
     def exchange(self, st):
         from moss_b200 import parallel
-        if self.peer is not None:
-            self.peer.allreduce(st.param_grad_numel)
-        else:
-            parallel.allreduce_param_grads(st.grad_buf, st.param_grad_numel)
+        parallel.allreduce_param_grads(st.grad_buf, st.param_grad_numel)        # NCCL: only when peer memory is unavailable
 
     def graph_step(self, i):
         from moss_b200.graphs import GraphedStep
         g = self.group_of(i)
         gs = self.graphs.get(g)
         if gs is None:
-            after = (lambda st_: self.peer.allreduce(st_.param_grad_numel)) if self.peer is not None else None
-            gs = self.graphs[g] = GraphedStep(self.devt, self.rs_of(g), (self.gc, self.gd, self.ga),
-                                              grad_out=self.peer.tensor if self.peer is not None else None, after=after,
+            gs = self.graphs[g] = GraphedStep(self.devt, self.rs_of(g), (self.gc, self.gd, self.ga), push=self.peer,
                                               forward_only=self.forward_only)
         gs.replay()
         self.state["st"], self.state["radii"] = gs.state, gs.out[1]
@@ -466,21 +464,18 @@ def run_ours(args, rank, world, dev):
 
     # data-parallel exchange of the public-API path: ONE exchange of the packed gradient.  The autograd Function hands
     # out views of one packed buffer (rasterizer.grad_layout), so the parameter gradients are flattened for free.
-    pack = {"buf": None}
+    if h.peer is not None:
+        M.set_gradient_sink(h.peer)      # autograd's backward writes into the symmetric buffer with the exchange fused in
 
     def reduce_grads(grads):
         if world == 1 or fo or not grads:
             return grads
-        flat = torch.cat([g.reshape(-1) for g in grads[1:]])     # parameter gradients (means2D stays per view)
-        if h.peer is not None:
-            n = flat.numel()
-            h.peer.tensor[:n].copy_(flat)
-            h.peer.allreduce(n)
-            flat = h.peer.tensor[:n]
-        else:
-            dist.all_reduce(flat)
-        out, o = [grads[0]], 0
-        for g in grads[1:]:
+        if h.peer is not None:           # already summed over the ranks by the backward itself; the tensors are views of the
+            return [g.clone() for g in grads]    # symmetric buffer, which the next backward overwrites: keep a copy
+        flat = torch.cat([g.reshape(-1) for g in grads])
+        dist.all_reduce(flat)
+        out, o = [], 0
+        for g in grads:
             out.append(flat[o:o + g.numel()].view(g.shape)); o += g.numel()
         return out
 
@@ -541,13 +536,16 @@ def run_ours(args, rank, world, dev):
     # ---- N > 1: is the exchange kernel's sum the sum?  (first timed group, NCCL on a clone as the yardstick) ----------
     exchange_check = None
     if world > 1 and not fo:
-        st = h.step(0, collective=False)
-        torch.cuda.synchronize(dev)
+        det = _abi.FLAG_DETERMINISTIC          # deterministic local gradients, so that two backward runs hold the same bits
+        color_, radii_, depth_, alpha_, st = h.forward(h.rs_of(h.group_of(0)))
+        M.backward_raw(st, radii_, h.gc, h.gd, h.ga, flags=det)
         k = st.param_grad_numel
-        mine = st.grad_buf[:k].clone()
-        ref = mine.clone()
-        dist.all_reduce(ref)
-        h.exchange(st)
+        ref = st.grad_buf[:k].clone()
+        dist.all_reduce(ref)                   # the yardstick: NCCL on the rank-local gradient
+        if h.peer is not None:
+            M.backward_raw(st, radii_, h.gc, h.gd, h.ga, flags=det, push=h.peer)
+        else:
+            h.exchange(st)
         torch.cuda.synchronize(dev)
         got = st.grad_buf[:k]
         err = float((got - ref).abs().max())
@@ -559,7 +557,7 @@ def run_ours(args, rank, world, dev):
         exchange_check = {"max_abs_err": err, "max_abs_ref": scale, "rel": err / max(scale, 1e-30),
                           "bit_identical_to_nccl": bool(torch.equal(got, ref)),
                           "bit_identical_across_ranks": bool(float(ident) == 1.0),
-                          "path": h.peer.path if h.peer is not None else "nccl", "numel": int(k)}
+                          "path": ("fused push + gather, " + h.peer.path) if h.peer is not None else "nccl", "numel": int(k)}
 
     stop.set()
     if h.peer is not None:

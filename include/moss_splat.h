@@ -247,6 +247,36 @@ int moss_peer_allreduce(void* stream, int rank, int world, void* const* buffer_p
                         size_t signal_pad_bytes, size_t offset_floats, size_t numel, unsigned epoch,
                         unsigned* error_word_dev, void* multicast_ptr);
 
+/* Backward with the data-parallel exchange fused in.  `push` describes a SYMMETRIC packed gradient
+ * buffer (same allocation on each of `world` <= 8 GPUs of one node, mapped into every process) plus a symmetric staging
+ * area and the signal pads.  Every output pointer of this call that lies inside [grad_base, grad_base + numel) is not
+ * stored locally: the kernel that produces the rows (backward preprocess, or the view sum of a batch) stores each
+ * element straight into the staging area of the rank owning it (reduce-scatter as posted NVLink stores), and ONE short
+ * kernel behind it sums the `world` staged copies of this rank's slice in rank order and stores the result into every
+ * rank's buffer (multimem.st through the NVSwitch when `multicast_grad` is given).  When the call's work has finished
+ * on all ranks, [grad_base, grad_base + numel) holds the sum over ranks on every rank, bit-identical everywhere and from
+ * run to run (given MOSS_FLAG_DETERMINISTIC).  Outputs outside that range stay local.  All ranks must make the call
+ * with the same numel.  `views` == NULL with V == 1: the scene's own camera.
+ * Staging area: world * moss_push_slice_floats(numel, world) floats per rank, zeroed once by the caller. */
+typedef struct MossPush {
+    int rank, world;
+    float* grad_base;            /* this rank's packed gradient buffer, 16-byte aligned */
+    size_t numel;                /* floats summed over the ranks (multiple of 4) */
+    void* const* grad_ptrs;      /* HOST array [world]: every rank's grad_base as mapped in this process */
+    void* const* stage_ptrs;     /* HOST array [world]: every rank's staging area as mapped in this process */
+    void* const* signal_ptrs;    /* HOST array [world]: zero-initialised signal pads (shared with moss_peer_allreduce) */
+    size_t signal_pad_bytes;
+    void* multicast_grad;        /* NVLS multicast mapping of grad_base, or NULL */
+    unsigned* error_word_dev;    /* device uint32[4], zeroed once; [0] != 0: a peer did not arrive; [1]: exchanges done */
+} MossPush;
+size_t moss_push_slice_floats(size_t numel, int world);
+size_t moss_sizeof_push(void);
+int moss_rasterize_backward_push(void* stream, const MossScene* scene, int V, const MossView* views, unsigned flags,
+                                 const int* radii, const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+                                 float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                                 float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot,
+                                 void* tmp_ws, size_t tmp_bytes, const MossPush* push);
+
 /* Internal-state export for parity tests (the reference needs a C++ shim over fromChunk for this,
  * DGR/cuda_rasterizer/rasterizer_impl.cu:155-194).  Copies one state array into `dst` (device) on
  * `stream`; returns the byte count or a negative MOSS_ERR_*. */
@@ -291,7 +321,8 @@ long long moss_export_state_batch(void* stream, const MossScene* scene, int V, i
 #define MOSS_STAGE_DENSIFY_STATS   12
 #define MOSS_STAGE_ADAMW           13
 #define MOSS_STAGE_SUM_VIEWS       14
-#define MOSS_STAGE_COUNT           15
+#define MOSS_STAGE_PUSH_GATHER     15
+#define MOSS_STAGE_COUNT           16
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

@@ -37,10 +37,10 @@ SYMBOLS = [
     "moss_profile_enable", "moss_profile_read", "moss_stage_name",
     "moss_geom_workspace_bytes_batch", "moss_image_workspace_bytes_batch", "moss_ckpt_workspace_bytes_batch",
     "moss_batch_grad_workspace_bytes", "moss_rasterize_forward_batch", "moss_rasterize_backward_batch", "moss_sizeof_view",
-    "moss_export_state_batch",
+    "moss_export_state_batch", "moss_push_slice_floats", "moss_sizeof_push", "moss_rasterize_backward_push",
     "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
 ]
-STAGE_COUNT = 15
+STAGE_COUNT = 16
 
 
 class MossScene(C.Structure):
@@ -62,6 +62,13 @@ class MossScene(C.Structure):
 class MossView(C.Structure):
     _fields_ = [("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("campos", C.c_void_p), ("bg", C.c_void_p),
                 ("tanfovx", C.c_float), ("tanfovy", C.c_float)]
+
+
+class MossPush(C.Structure):
+    _fields_ = [("rank", C.c_int), ("world", C.c_int), ("grad_base", C.c_void_p), ("numel", C.c_size_t),
+                ("grad_ptrs", C.POINTER(C.c_void_p)), ("stage_ptrs", C.POINTER(C.c_void_p)),
+                ("signal_ptrs", C.POINTER(C.c_void_p)), ("signal_pad_bytes", C.c_size_t),
+                ("multicast_grad", C.c_void_p), ("error_word_dev", C.c_void_p)]
 
 
 class MossAdamGroup(C.Structure):
@@ -149,6 +156,14 @@ def load():
     lib.moss_export_state_batch.restype = C.c_longlong
     lib.moss_export_state_batch.argtypes = [vp, C.POINTER(MossScene), C.c_int, C.c_int, vp, C.c_longlong]
     lib.moss_sizeof_view.restype = C.c_size_t
+    lib.moss_push_slice_floats.restype = C.c_size_t
+    lib.moss_push_slice_floats.argtypes = [C.c_size_t, C.c_int]
+    lib.moss_sizeof_push.restype = C.c_size_t
+    lib.moss_rasterize_backward_push.restype = C.c_int
+    lib.moss_rasterize_backward_push.argtypes = [vp, C.POINTER(MossScene), C.c_int, C.POINTER(MossView), C.c_uint, vp] + [vp] * 12 + \
+        [vp, C.c_size_t, C.POINTER(MossPush)]
+    if lib.moss_sizeof_push() != C.sizeof(MossPush):
+        raise RuntimeError("moss_b200: MossPush layout mismatch between _abi.py and the library; rebuild")
     if lib.moss_sizeof_view() != C.sizeof(MossView):
         raise RuntimeError("moss_b200: MossView layout mismatch between _abi.py and the library; rebuild")
     lib.moss_adamw_step.restype = C.c_int

@@ -25,6 +25,7 @@
 #include "densify.cuh"
 #include "adamw.cuh"
 #include "peer_reduce.cuh"
+#include "push_exchange.cuh"
 
 using namespace moss;
 
@@ -260,7 +261,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step", "sum_views"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step", "sum_views", "push_gather"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -450,9 +451,38 @@ int forward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossView
 int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossView* views, unsigned flags, const int* radii,
 	const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
-	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* tmp_ws, size_t tmp_bytes)
+	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* tmp_ws, size_t tmp_bytes,
+	const MossPush* push = nullptr)
 {
 	if (!scene_valid(sc, views == nullptr)) return MOSS_ERR_INVALID_ARGUMENT;
+	PushCfg pc = no_push();
+	GatherArgs ga;
+	unsigned gather_blocks = 0;
+	if (push) {
+		if (push->world < 1 || push->world > PEER_MAX_WORLD || push->rank < 0 || push->rank >= push->world || !push->grad_base ||
+			((uintptr_t)push->grad_base & 15) || (push->numel & 3) || push->numel == 0 || push->numel > 0xfffffff0ull ||
+			!push->grad_ptrs || !push->stage_ptrs || !push->signal_ptrs || !push->error_word_dev ||
+			push->signal_pad_bytes < moss_peer_signal_bytes(push->world))
+			return MOSS_ERR_INVALID_ARGUMENT;
+		const size_t S = moss_push_slice_floats(push->numel, push->world);
+		pc.base = push->grad_base; pc.numel = (uint32_t)push->numel; pc.S = (uint32_t)S;
+		memset(&ga, 0, sizeof(ga));
+		for (int o = 0; o < push->world; o++) {
+			if (!push->grad_ptrs[o] || !push->stage_ptrs[o] || !push->signal_ptrs[o]) return MOSS_ERR_INVALID_ARGUMENT;
+			pc.stage_mine[o] = (float*)push->stage_ptrs[o] + (size_t)push->rank * S;
+			ga.grad[o] = (float*)push->grad_ptrs[o];
+			ga.pads[o] = (uint32_t*)push->signal_ptrs[o];
+		}
+		ga.stage = (const float*)push->stage_ptrs[push->rank];
+		ga.mc_grad = (float*)push->multicast_grad;
+		ga.err = push->error_word_dev;
+		ga.numel = pc.numel; ga.S = pc.S; ga.rank = push->rank; ga.world = push->world;
+		// every rank derives the same grid from (numel, world, pad size): the flag slots are indexed by it
+		size_t blocks = (S / 4 + (size_t)GATHER_THREADS * GATHER_ILP - 1) / ((size_t)GATHER_THREADS * GATHER_ILP);
+		const size_t pad_blocks = push->signal_pad_bytes / (sizeof(uint32_t) * 2 * (size_t)push->world);
+		blocks = std::min(blocks, std::min(pad_blocks, (size_t)PEER_MAX_BLOCKS));
+		gather_blocks = (unsigned)std::max<size_t>(blocks, 1);
+	}
 	const int P = sc->P, W = sc->W, H = sc->H, N = W * H;
 	if (P == 0) return MOSS_OK;
 	if (!radii || !dL_dpix || !dL_dmean2D || !dL_dopacity || !dL_dcolor ||
@@ -506,7 +536,7 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 	{ MOSS_STAGE(MOSS_STAGE_PREPROCESS_BWD, stream);
 	preprocess_backward_kernel<<<dim3((P + PRE_THREADS - 1) / PRE_THREADS, V), PRE_THREADS, 0, stream>>>(
 		vb, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
-		dL_dmean2D, dL_dconic, po, det, im.counters); }
+		dL_dmean2D, dL_dconic, po, det, im.counters, V == 1 ? pc : no_push()); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	if (V > 1) {
 		SumViewsArgs a;
@@ -520,7 +550,12 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 		for (int k = 0; k < 7; k++) { a.dst[k] = dst[k]; a.src[k] = src[k]; a.n[k] = dst[k] ? n[k] : 0; biggest = std::max(biggest, a.n[k]); }
 		const unsigned gx = (unsigned)std::min<size_t>((biggest / 4 + SUMV_THREADS - 1) / SUMV_THREADS + 1, 148 * 8);
 		{ MOSS_STAGE(MOSS_STAGE_SUM_VIEWS, stream);
-		sum_views_kernel<<<dim3(gx, 7), SUMV_THREADS, 0, stream>>>(a); }
+		sum_views_kernel<<<dim3(gx, 7), SUMV_THREADS, 0, stream>>>(a, pc); }
+		MOSS_CHECK_LAUNCH(stream, flags);
+	}
+	if (push) {
+		{ MOSS_STAGE(MOSS_STAGE_PUSH_GATHER, stream);
+		push_gather_kernel<<<gather_blocks, GATHER_THREADS, 0, stream>>>(ga); }
 		MOSS_CHECK_LAUNCH(stream, flags);
 	}
 	return MOSS_OK;
@@ -529,6 +564,22 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 } // namespace
 
 size_t moss_sizeof_view(void) { return sizeof(MossView); }
+size_t moss_sizeof_push(void) { return sizeof(MossPush); }
+size_t moss_push_slice_floats(size_t numel, int world)
+{
+	const size_t w = (size_t)(world > 0 ? world : 1);
+	return ((numel + w - 1) / w + 3) / 4 * 4;
+}
+int moss_rasterize_backward_push(void* stream, const MossScene* sc, int V, const MossView* views, unsigned flags, const int* radii,
+	const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* tmp_ws, size_t tmp_bytes,
+	const MossPush* push)
+{
+	if (!push || (!views && V != 1)) return MOSS_ERR_INVALID_ARGUMENT;
+	return backward_impl((cudaStream_t)stream, sc, V, views, flags, radii, dL_dpix, dL_ddepth, dL_dalpha, dL_dmean2D, dL_dconic,
+		dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, tmp_ws, tmp_bytes, push);
+}
 size_t moss_batch_grad_workspace_bytes(int P, int M, int V)
 {
 	if (V <= 1 || P <= 0) return 0;

@@ -7,8 +7,15 @@
 #pragma once
 #include "common.cuh"
 #include "preprocess.cuh"
+#include "push_exchange.cuh"
 
 namespace moss {
+
+__device__ __forceinline__ void store_quat_routed(const PushCfg& pc, float* out, int i, float4 v)
+{
+	if ((reinterpret_cast<uintptr_t>(out) & 15) == 0) { *reinterpret_cast<float4*>(route(pc, out + 4 * i)) = v; return; }
+	*route(pc, out + 4 * i) = v.x; *route(pc, out + 4 * i + 1) = v.y; *route(pc, out + 4 * i + 2) = v.z; *route(pc, out + 4 * i + 3) = v.w;
+}
 
 // Where the per-Gaussian parameter gradients of view v go.  One view: the caller's tensors.  A batch of V views: row
 // v of a scratch area (ptr + v * view_stride), summed over the views afterwards by sum_views_kernel in a fixed order.
@@ -30,7 +37,7 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	const float* __restrict__ scales, const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
 	GeomWS g,
 	float* __restrict__ dL_dmean2D_all, float* __restrict__ dL_dconic_all, ParamGradOut po,
-	int deterministic, const uint32_t* __restrict__ counters)
+	int deterministic, const uint32_t* __restrict__ counters, const __grid_constant__ PushCfg pc)
 {
 	// All global reads of the Gaussian are issued before the first data-dependent branch (one DRAM round trip instead
 	// of a chain; see preprocess_forward_kernel) -- except the accumulator row, which only visible Gaussians own.
@@ -101,30 +108,33 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 			for (int k = 0; k < GRAD_EXT_VEC; k++) g.grad_ext[GRAD_EXT_VEC * vid + k] = make_float4(0.f, 0.f, 0.f, 0.f);
 		}
 	}
+	// Every store of a parameter-gradient element goes through route(): with a data-parallel exchange attached the
+	// element lands in the staging area of the rank that owns it (push_exchange.cuh), otherwise in the caller's tensor.
 	dL_dcolor[3 * idx] = acc0.x; dL_dcolor[3 * idx + 1] = acc0.y; dL_dcolor[3 * idx + 2] = acc0.z;
-	dL_dopacity[idx] = acc0.w;
-	dL_dmean2D[3 * idx] = acc1.x; dL_dmean2D[3 * idx + 1] = acc1.y; dL_dmean2D[3 * idx + 2] = 0.f;
+	*route(pc, dL_dopacity + idx) = acc0.w;
+	*route(pc, dL_dmean2D + 3 * idx) = acc1.x; *route(pc, dL_dmean2D + 3 * idx + 1) = acc1.y; *route(pc, dL_dmean2D + 3 * idx + 2) = 0.f;
 	if (dL_dconic) { dL_dconic[4 * idx] = acc1.z; dL_dconic[4 * idx + 1] = acc1.w; dL_dconic[4 * idx + 2] = 0.f; dL_dconic[4 * idx + 3] = acc2; }
 
 	if (!(radius > 0)) {
 #pragma unroll
-		for (int k = 0; k < 3; k++) dL_dmean3D[3 * idx + k] = 0.f;
+		for (int k = 0; k < 3; k++) *route(pc, dL_dmean3D + 3 * idx + k) = 0.f;
 #pragma unroll
-		for (int k = 0; k < 6; k++) dL_dcov3D[6 * idx + k] = 0.f;
+		for (int k = 0; k < 6; k++) *route(pc, dL_dcov3D + 6 * idx + k) = 0.f;
 		if (shs) {
 			if (dsh_vec) {
-				float4* d4 = reinterpret_cast<float4*>(dL_dsh + (size_t)idx * 48);
+				float* d = dL_dsh + (size_t)idx * 48;
 #pragma unroll
-				for (int k = 0; k < 12; k++) d4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+				for (int k = 0; k < 12; k++) *reinterpret_cast<float4*>(route(pc, d + 4 * k)) = make_float4(0.f, 0.f, 0.f, 0.f);
 			} else {
-				for (int k = 0; k < 3 * M; k++) dL_dsh[(size_t)idx * 3 * M + k] = 0.f;
+				for (int k = 0; k < 3 * M; k++) *route(pc, dL_dsh + (size_t)idx * 3 * M + k) = 0.f;
 			}
 		}
 		if (scales) {
 #pragma unroll
-			for (int k = 0; k < 3; k++) dL_dscale[3 * idx + k] = 0.f;
-			store_quat(dL_drot, idx, make_float4(0.f, 0.f, 0.f, 0.f));
+			for (int k = 0; k < 3; k++) *route(pc, dL_dscale + 3 * idx + k) = 0.f;
+			store_quat_routed(pc, dL_drot, idx, make_float4(0.f, 0.f, 0.f, 0.f));
 		}
+		if (pc.numel) __threadfence_system();
 		return;
 	}
 
@@ -173,7 +183,7 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 		dcov[4] = 2 * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2 * T11 * T12 * dL_dc;
 	}
 #pragma unroll
-	for (int k = 0; k < 6; k++) dL_dcov3D[6 * idx + k] = dcov[k];
+	for (int k = 0; k < 6; k++) *route(pc, dL_dcov3D + 6 * idx + k) = dcov[k];
 
 	const float dT00 = 2 * VT00 * dL_da + VT10 * dL_db;
 	const float dT01 = 2 * VT01 * dL_da + VT11 * dL_db;
@@ -274,18 +284,18 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 				const float bk = (k < ncoef) ? basis[k] : 0.f;
 				o[3 * k] = bk * dRGB[0]; o[3 * k + 1] = bk * dRGB[1]; o[3 * k + 2] = bk * dRGB[2];
 			}
-			float4* d4 = reinterpret_cast<float4*>(dsh);
 #pragma unroll
-			for (int k = 0; k < 12; k++) d4[k] = make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+			for (int k = 0; k < 12; k++)
+				*reinterpret_cast<float4*>(route(pc, dsh + 4 * k)) = make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
 		} else {
 #pragma unroll
 			for (int k = 0; k < 16; k++) {
 				if (k < M) {
 					const float bk = (k < ncoef) ? basis[k] : 0.f;
-					dsh[3 * k] = bk * dRGB[0]; dsh[3 * k + 1] = bk * dRGB[1]; dsh[3 * k + 2] = bk * dRGB[2];
+					*route(pc, dsh + 3 * k) = bk * dRGB[0]; *route(pc, dsh + 3 * k + 1) = bk * dRGB[1]; *route(pc, dsh + 3 * k + 2) = bk * dRGB[2];
 				}
 			}
-			for (int k = 16; k < M; k++) { dsh[3 * k] = 0.f; dsh[3 * k + 1] = 0.f; dsh[3 * k + 2] = 0.f; }
+			for (int k = 16; k < M; k++) { *route(pc, dsh + 3 * k) = 0.f; *route(pc, dsh + 3 * k + 1) = 0.f; *route(pc, dsh + 3 * k + 2) = 0.f; }
 		}
 
 		const float ddx = dx3[0] * dRGB[0] + dx3[1] * dRGB[1] + dx3[2] * dRGB[2];
@@ -298,7 +308,7 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 		gmy += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * invsum32;
 		gmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
 	}
-	dL_dmean3D[3 * idx] = gmx; dL_dmean3D[3 * idx + 1] = gmy; dL_dmean3D[3 * idx + 2] = gmz;
+	*route(pc, dL_dmean3D + 3 * idx) = gmx; *route(pc, dL_dmean3D + 3 * idx + 1) = gmy; *route(pc, dL_dmean3D + 3 * idx + 2) = gmz;
 
 	// ---- cov3D -> scale, (un-normalised) quaternion --------------------------------------------------
 	if (scales) {
@@ -323,7 +333,7 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 		// dL_dscale_k = dot(Rt[k], dMt[k]),  Rt[k][j] = R[j][k]   (not multiplied by the modifier, as the reference)
 #pragma unroll
 		for (int k = 0; k < 3; k++)
-			dL_dscale[3 * idx + k] = R[0][k] * dMt[k][0] + R[1][k] * dMt[k][1] + R[2][k] * dMt[k][2];
+			*route(pc, dL_dscale + 3 * idx + k) = R[0][k] * dMt[k][0] + R[1][k] * dMt[k][1] + R[2][k] * dMt[k][2];
 #pragma unroll
 		for (int k = 0; k < 3; k++) { dMt[k][0] *= s[k]; dMt[k][1] *= s[k]; dMt[k][2] *= s[k]; }
 		float4 dq;
@@ -331,8 +341,9 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 		dq.y = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) - 4 * x * (dMt[2][2] + dMt[1][1]);
 		dq.z = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
 		dq.w = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
-		store_quat(dL_drot, idx, dq);   // no normalisation Jacobian (DGR backward.cu:340)
+		store_quat_routed(pc, dL_drot, idx, dq);   // no normalisation Jacobian (DGR backward.cu:340)
 	}
+	if (pc.numel) __threadfence_system();   // pushed rows are on their way before this thread retires
 }
 
 // Batched backward, V > 1: out[j] = sum_v rows[v*stride + j] over the views, in view order (fixed order: the sum is
@@ -346,7 +357,7 @@ struct SumViewsArgs {
 };
 constexpr int SUMV_THREADS = 256;
 __global__ void __launch_bounds__(SUMV_THREADS)
-sum_views_kernel(const __grid_constant__ SumViewsArgs a)
+sum_views_kernel(const __grid_constant__ SumViewsArgs a, const __grid_constant__ PushCfg pc)
 {
 	const int k = blockIdx.y;
 	float* __restrict__ dst = a.dst[k];
@@ -362,20 +373,21 @@ sum_views_kernel(const __grid_constant__ SumViewsArgs a)
 				const float4 x = reinterpret_cast<const float4*>(src + (size_t)v * a.view_stride)[i];
 				s.x += x.x; s.y += x.y; s.z += x.z; s.w += x.w;
 			}
-			reinterpret_cast<float4*>(dst)[i] = s;
+			*reinterpret_cast<float4*>(route(pc, dst + 4 * i)) = s;
 		}
 		for (size_t i = (n4 << 2) + (size_t)blockIdx.x * SUMV_THREADS + threadIdx.x; i < n; i += stride) {
 			float s = src[i];
 			for (int v = 1; v < a.V; v++) s += src[(size_t)v * a.view_stride + i];
-			dst[i] = s;
+			*route(pc, dst + i) = s;
 		}
 	} else {
 		for (size_t i = (size_t)blockIdx.x * SUMV_THREADS + threadIdx.x; i < n; i += stride) {
 			float s = src[i];
 			for (int v = 1; v < a.V; v++) s += src[(size_t)v * a.view_stride + i];
-			dst[i] = s;
+			*route(pc, dst + i) = s;
 		}
 	}
+	if (pc.numel) __threadfence_system();
 }
 
 } // namespace moss

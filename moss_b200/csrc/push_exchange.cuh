@@ -1,0 +1,124 @@
+// Gradient exchange fused into the backward (no reference counterpart: MOSS trains on one GPU).
+//
+// Data-parallel ranks render different views of the same Gaussians and their parameter gradients add.  Instead of
+// "write the packed gradient locally, then all-reduce it" (peer_reduce.cuh: barrier, remote loads, remote stores,
+// barrier), the kernel that PRODUCES the gradient rows -- the backward preprocess (one view) or the view sum (a batch)
+// -- stores every element straight into the staging area of the rank that owns it: a reduce-scatter done with posted
+// NVLink stores while the producer is still computing.  What is left behind the producer is ONE short kernel:
+//   signal "my rows are out" to every owner   -> wait until all ranks' rows have arrived in my staging area
+//   sum the `world` staged copies of my slice in rank order (local reads; bit-reproducible)
+//   store the result into slice `rank` of EVERY rank's gradient buffer (one multimem.st through the switch, or
+//   `world` peer stores), signal "slice delivered" -> wait for the other owners' slices.
+// Ownership is by position in the packed buffer: element j of the summed prefix belongs to rank j / S
+// (S = slice length, a multiple of 4 floats so a 16-byte store never straddles two owners).
+// Flags live in the peers' signal pads exactly like peer_reduce.cuh (slot ((phase * blocks + block) * world + writer),
+// value = a monotonically increasing epoch kept on the device, so the call is CUDA-graph capturable).
+#pragma once
+#include "common.cuh"
+#include "peer_reduce.cuh"
+
+namespace moss {
+
+// Where a producer stores element `off` of the packed gradient.  numel == 0: push disabled (everything local).
+struct PushCfg {
+	const float* base;               // this rank's packed gradient buffer
+	uint32_t numel;                  // floats of the summed prefix (multiple of 4)
+	uint32_t S;                      // floats per owner slice (multiple of 4)
+	float* stage_mine[PEER_MAX_WORLD];   // stage_mine[o] = rank o's staging area + my_rank * S, as mapped in this process
+};
+__device__ __forceinline__ float* route(const PushCfg& pc, float* p)
+{
+	if (pc.numel == 0u) return p;
+	const size_t off = (size_t)(p - pc.base);          // wraps to a huge value for pointers in front of the buffer
+	if (off >= (size_t)pc.numel) return p;             // blend-only outputs (colours, conics, per-view rows) stay local
+	const uint32_t o32 = (uint32_t)off;
+	const uint32_t owner = o32 / pc.S;
+	return pc.stage_mine[owner] + (o32 - owner * pc.S);
+}
+inline PushCfg no_push()
+{
+	PushCfg pc;
+	pc.base = nullptr; pc.numel = 0; pc.S = 4;
+	for (int i = 0; i < PEER_MAX_WORLD; i++) pc.stage_mine[i] = nullptr;
+	return pc;
+}
+
+struct GatherArgs {
+	float* grad[PEER_MAX_WORLD];     // every rank's packed gradient buffer, as mapped here
+	uint32_t* pads[PEER_MAX_WORLD];  // signal pads
+	const float* stage;              // MY staging area: [world][S]
+	float* mc_grad;                  // multicast mapping of the gradient buffer, or null
+	uint32_t* err;                   // [0] timeout, [1] epoch, [2] block counter
+	uint32_t numel, S;
+	int rank, world;
+};
+constexpr int GATHER_THREADS = 256;
+constexpr int GATHER_ILP = 4;
+
+__device__ __forceinline__ void flag_exchange(uint32_t* const* pads, int rank, int world, int phase, uint32_t epoch, uint32_t* err)
+{
+	// every thread's stores of this block must be visible system-wide before the flag: the block syncs, then the
+	// signalling threads fence at system scope (cumulative over what the barrier made visible to them)
+	__syncthreads();
+	if ((int)threadIdx.x < world) {
+		const int p = (int)threadIdx.x;
+		const size_t slot = (size_t)(phase * (int)gridDim.x + (int)blockIdx.x) * world;
+		__threadfence_system();
+		st_relaxed_sys(pads[p] + slot + rank, epoch);
+		const uint32_t* mine = pads[rank] + slot + p;
+		const long long t0 = clock64();
+		while ((int)(ld_relaxed_sys(mine) - epoch) < 0) {
+			if (clock64() - t0 > 20000000000ll) { atomicExch(err, 1u); break; }    // ~10 s at 2 GHz: a peer died
+		}
+		__threadfence_system();
+	}
+	__syncthreads();
+}
+
+__global__ void __launch_bounds__(GATHER_THREADS)
+push_gather_kernel(const __grid_constant__ GatherArgs a)
+{
+	const uint32_t epoch = ld_relaxed_sys(a.err + 1) + 1u;
+	__shared__ uint32_t* s_pads[PEER_MAX_WORLD];
+	if ((int)threadIdx.x < a.world) s_pads[threadIdx.x] = a.pads[threadIdx.x];
+	// phase 0: the producers of all ranks (earlier kernels in their streams) have pushed their rows into my staging area
+	flag_exchange(s_pads, a.rank, a.world, 0, epoch, a.err);
+
+	const uint32_t lo = min(a.numel, a.S * (uint32_t)a.rank), hi = min(a.numel, lo + a.S);   // my slice of the prefix
+	const uint32_t n4 = (hi - lo) >> 2;
+	const uint32_t stride = gridDim.x * GATHER_THREADS;
+	const float4* st4 = reinterpret_cast<const float4*>(a.stage);
+	const uint32_t S4 = a.S >> 2;
+	for (uint32_t i0 = blockIdx.x * GATHER_THREADS + threadIdx.x; i0 < n4; i0 += stride * GATHER_ILP) {
+		float4 s[GATHER_ILP];
+#pragma unroll
+		for (int u = 0; u < GATHER_ILP; u++) {
+			const uint32_t i = i0 + u * stride;
+			s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+			if (i < n4) {
+				s[u] = st4[i];
+				for (int p = 1; p < a.world; p++) {
+					const float4 x = st4[(size_t)p * S4 + i];
+					s[u].x += x.x; s[u].y += x.y; s[u].z += x.z; s[u].w += x.w;
+				}
+			}
+		}
+#pragma unroll
+		for (int u = 0; u < GATHER_ILP; u++) {
+			const uint32_t i = i0 + u * stride;
+			if (i < n4) {
+				const size_t e4 = ((size_t)lo >> 2) + i;
+				if (a.mc_grad) multimem_st_f4(reinterpret_cast<float4*>(a.mc_grad) + e4, s[u]);
+				else
+					for (int p = 0; p < a.world; p++) st_peer_f4(reinterpret_cast<float4*>(a.grad[p]) + e4, s[u]);
+			}
+		}
+	}
+	// phase 1: my slice is in everybody's buffer; wait for the other owners' slices
+	flag_exchange(s_pads, a.rank, a.world, 1, epoch, a.err);
+	if (threadIdx.x == 0) {
+		if (atomicAdd(a.err + 2, 1u) == gridDim.x - 1u) { a.err[2] = 0u; __threadfence(); a.err[1] = epoch; }
+	}
+}
+
+} // namespace moss

@@ -18,12 +18,14 @@ class GraphedStep:
     inputs: dict with the tensors of ``rasterizer.forward_raw`` (means3D, shs, colors_precomp, opacities, scales,
     rotations, cov3D_precomp; empty tensors for the absent ones).  ``raster_settings`` may be a LIST of settings: the
     step is then one batched call over those views (``rasterizer.forward_batch_raw``; upstream gradients [V,3,H,W] /
-    [V,1,H,W]).  ``grad_out`` (optional) is the packed gradient
-    buffer the backward writes (e.g. ``parallel.PeerGradBuffer.tensor``); ``after`` (optional) is called inside the
-    capture after the backward (e.g. the gradient exchange)."""
+    [V,1,H,W]).  ``grad_out`` (optional) is the packed gradient buffer the backward writes; ``push`` (optional) a
+    ``parallel.PeerGradBuffer``: the data-parallel exchange is fused into the captured backward; ``after`` (optional) is
+    called inside the capture after the backward (e.g. a stand-alone gradient exchange)."""
 
-    def __init__(self, inputs, raster_settings, grads, grad_out=None, after=None, flags=0, forward_only=False):
+    def __init__(self, inputs, raster_settings, grads, grad_out=None, after=None, flags=0, forward_only=False, push=None,
+                 backward_flags=0):
         self.inputs, self.rs, self.grads = inputs, raster_settings, grads
+        self.push, self.backward_flags = push, backward_flags      # parallel.PeerGradBuffer: exchange fused into the backward
         self.forward_only = forward_only      # eval render (render_ZJU.py:56-72 under no_grad): no backward in the graph
         self.flags = flags | _abi.FLAG_ASYNC
         dev = inputs["means3D"].device
@@ -47,7 +49,7 @@ class GraphedStep:
         fwd = R.forward_batch_raw if isinstance(self.rs, list) else R.forward_raw
         color, radii, depth, alpha, st = fwd(i["means3D"], i["shs"], i["colors_precomp"], i["opacities"],
                                              i["scales"], i["rotations"], i["cov3D_precomp"], self.rs, flags=flags)
-        g = None if self.forward_only else R.backward_raw(st, radii, *self.grads, out=grad_out)
+        g = None if self.forward_only else R.backward_raw(st, radii, *self.grads, flags=self.backward_flags, out=grad_out, push=self.push)
         if after is not None:
             after(st)
         return color, radii, depth, alpha, st, g

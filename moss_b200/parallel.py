@@ -55,9 +55,13 @@ def allreduce_densification_stats(radii, max_radii2D, viewspace_grad_norm, xyz_g
 
 
 class PeerGradBuffer:
-    """Symmetric (peer-mapped) packed-gradient buffer + the library's own all-reduce kernel over NVLink peer memory
-    (include/moss_splat.h: moss_peer_allreduce).  Pass ``.tensor`` as ``out=`` to ``rasterizer.backward_raw`` so the
-    backward writes the gradients straight into the mapped buffer, then call ``allreduce(param_grad_numel)``.
+    """Symmetric (peer-mapped) packed-gradient buffer for the data-parallel exchange over NVLink peer memory.
+
+    Fused form (the default of bench.py): ``rasterizer.backward_raw(..., push=buf)`` -- the backward's producer kernel
+    stores every gradient row into the staging area of the rank that owns it and one short kernel behind it gathers the
+    sums (include/moss_splat.h: moss_rasterize_backward_push).
+    Stand-alone form: write ``.tensor`` (``out=``), then ``allreduce(param_grad_numel)`` (moss_peer_allreduce: a
+    two-shot all-reduce kernel over the mapped peer pointers) -- for gradients that were produced by something else.
 
     The allocation and the exchange of the IPC handles are plumbing (torch.distributed._symmetric_memory); the data
     path is this repo's kernel.  Raises RuntimeError when symmetric memory cannot be set up on this machine -- callers
@@ -76,11 +80,16 @@ class PeerGradBuffer:
         if self.world > 8:
             raise RuntimeError("peer all-reduce supports up to 8 ranks of one node")
         numel = (int(numel) + 3) // 4 * 4
+        # one symmetric allocation: [packed gradient | staging area of the fused exchange: world slices of <= numel/world]
+        self.slice_max = int(self._lib.moss_push_slice_floats(numel, self.world))
         try:
-            self.tensor = symm.empty(numel, dtype=torch.float32, device=device)
-            self.handle = symm.rendezvous(self.tensor, group)
+            self.storage = symm.empty(numel + self.world * self.slice_max, dtype=torch.float32, device=device)
+            self.handle = symm.rendezvous(self.storage, group)
         except Exception as e:       # no IPC / fabric support on this box
             raise RuntimeError(f"symmetric memory unavailable: {e}") from e
+        self.tensor = self.storage[:numel]
+        self.stage = self.storage[numel:]
+        self._desc = {}
         need = self._lib.moss_peer_signal_bytes(self.world)
         if int(self.handle.signal_pad_size) < need:
             raise RuntimeError(f"signal pad too small ({self.handle.signal_pad_size} < {need})")
@@ -96,13 +105,41 @@ class PeerGradBuffer:
                 mc = 0
         self.multicast_ptr = mc                 # 0: no NVLS mapping -> loads/stores on the peer pointers
         self.path = "nvls" if mc else "peer"
-        self.kind = "peer-memory kernel (moss_peer_allreduce, " + ("NVLS multimem data phase" if mc else "peer loads/stores") + ")"
+        self.kind = ("exchange fused into the backward (rows pushed to their owner's staging area over NVLink, one gather kernel, "
+                     + ("multimem.st through the switch" if mc else "peer stores") + ")")
         self.error = torch.zeros(4, dtype=torch.int32, device=device)      # [0] timeout flag, [1] device-side epoch, [2] block counter
         self.device = device
         # everyone's pad is zero and mapped before the first kernel spins on it
-        self.tensor.zero_()
+        self.storage.zero_()
         torch.cuda.synchronize(device)
         dist.barrier(group)
+
+    def descriptor(self, param_numel):
+        """ctypes MossPush for a backward that sums the leading `param_numel` floats of ``tensor`` over the ranks
+        (include/moss_splat.h: moss_rasterize_backward_push)."""
+        d = self._desc.get(param_numel)
+        if d is None:
+            C = self._C
+            from . import _abi
+            if param_numel % 4 or not 0 < param_numel <= self.tensor.numel():
+                raise RuntimeError(f"param_numel {param_numel} must be a positive multiple of 4 within the buffer")
+            h = self.handle
+            w = self.world
+            numel = self.tensor.numel()
+            grads = (C.c_void_p * w)(*[int(p) for p in h.buffer_ptrs])
+            stages = (C.c_void_p * w)(*[int(p) + 4 * numel for p in h.buffer_ptrs])
+            pads = (C.c_void_p * w)(*[int(p) for p in h.signal_pad_ptrs])
+            d = _abi.MossPush()
+            d.rank, d.world = self.rank, w
+            d.grad_base = self.tensor.data_ptr()
+            d.numel = int(param_numel)
+            d.grad_ptrs, d.stage_ptrs, d.signal_ptrs = grads, stages, pads
+            d.signal_pad_bytes = int(h.signal_pad_size)
+            d.multicast_grad = self.multicast_ptr or None
+            d.error_word_dev = self.error.data_ptr()
+            d._keep = (grads, stages, pads)
+            self._desc[param_numel] = d
+        return d
 
     def allreduce(self, numel, offset=0):
         """Sum tensor[offset:offset+numel] over all ranks, in place, on the current stream (no host sync; the epoch

@@ -233,12 +233,15 @@ def grad_layout(P, M, has_sh, has_sr, V=1):
     return lay, param_numel, zero_from, o
 
 
-def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=None):
+def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=None, push=None):
     """Backward through the C ABI.  Returns the 8 gradient tensors in the reference's C++ order
     (DGR/rasterize_points.cu:205): dmeans2D, dcolors, dopacity, dmeans3D, dcov3D, dsh, dscales, drot.
     They are views of ONE packed buffer (kept in ``st.grad_buf``; ``st.param_grad_numel`` floats of parameter
     gradient lead it), which may be supplied as ``out``.  For a batched state the upstream gradients are
-    [V,3,H,W] / [V,1,H,W], dmeans2D is [V,P,3] and the parameter gradients are summed over the views."""
+    [V,3,H,W] / [V,1,H,W], dmeans2D is [V,P,3] and the parameter gradients are summed over the views.
+    ``push``: a ``parallel.PeerGradBuffer`` -- the data-parallel exchange is fused into the backward
+    (include/moss_splat.h: moss_rasterize_backward_push): the gradients are written into its symmetric buffer and, once
+    the queued work has run on every rank, the leading ``st.param_grad_numel`` floats hold the sum over the ranks."""
     lib = _abi.load()
     sc = st.scene
     P, M, H, W, V = sc.P, sc.M, sc.H, sc.W, st.V
@@ -257,6 +260,12 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
         # every row of every output is written by the backward preprocess kernel: nothing is zero-filled here
         # (the reference fills 9 tensors, DGR/rasterize_points.cu:158-166); the atomically accumulated blend
         # gradients live in a self-cleaning scratch inside the geometry workspace
+        if push is not None:
+            if out is not None and out.data_ptr() != push.tensor.data_ptr():
+                raise RuntimeError("with push= the gradients are written into the PeerGradBuffer's own tensor")
+            if push.tensor.numel() < total:
+                raise RuntimeError(f"PeerGradBuffer holds {push.tensor.numel()} floats, this call needs {total}")
+            out = push.tensor
         buf = out if out is not None else torch.empty((total,), dtype=torch.float32, device=dev)
 
         def v(name, *shape):
@@ -274,7 +283,14 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
         stream = torch.cuda.current_stream(dev).cuda_stream
         outs = (_ptr(dmeans2D), _ptr(dconic), _ptr(dopacity), _ptr(dcolors), _ptr(dmeans3D), _ptr(dcov3D),
                 _ptr(dsh) if has_sh else None, _ptr(dscales) if has_sr else None, _ptr(drot) if has_sr else None)
-        if st.batched:
+        if push is not None:
+            tbytes = lib.moss_batch_grad_workspace_bytes(P, M, V) if st.batched else 0
+            tmp = torch.empty((max(tbytes, 16),), dtype=torch.uint8, device=dev)
+            status = lib.moss_rasterize_backward_push(
+                stream, C.byref(sc), V, st.views if st.batched else None, flags | st.flags, _ptr(radii),
+                grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha), *outs, tmp.data_ptr(), tbytes,
+                C.byref(push.descriptor(param_numel)))
+        elif st.batched:
             tbytes = lib.moss_batch_grad_workspace_bytes(P, M, V)
             tmp = torch.empty((max(tbytes, 16),), dtype=torch.uint8, device=dev)
             status = lib.moss_rasterize_backward_batch(
@@ -296,6 +312,19 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales,
                         raster_settings):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
                                      cov3Ds_precomp, raster_settings)
+
+
+# Data-parallel training through the public API: with a sink set (parallel.PeerGradBuffer), the autograd backward writes
+# its gradients into the sink's symmetric buffer with the exchange fused in (one exchange per backward, the gradient
+# tensors handed to autograd are views of that buffer and hold the SUM over the ranks once the stream has run).
+_gradient_sink = None
+
+
+def set_gradient_sink(peer):
+    """peer: parallel.PeerGradBuffer or None.  Returns the previous sink."""
+    global _gradient_sink
+    prev, _gradient_sink = _gradient_sink, peer
+    return prev
 
 
 class _RasterizeGaussians(torch.autograd.Function):
@@ -325,7 +354,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         radii = saved[0]
         st = ctx.state
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh,
-         grad_scales, grad_rotations) = backward_raw(st, radii, grad_out_color, grad_depth, grad_alpha)
+         grad_scales, grad_rotations) = backward_raw(st, radii, grad_out_color, grad_depth, grad_alpha, push=_gradient_sink)
         # same order as DGR/diff_gaussian_rasterization/__init__.py:146-156
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
                 grad_rotations, grad_cov3Ds_precomp, None)
