@@ -648,6 +648,7 @@ def run_ours(args, rank, world, dev):
                          "note": "the same raw C-ABI calls as stream launches (no CUDA graph)"},
         "value_public_api": {"value": round(mpix / (sa["mean"] * 1e-3), 2), "ms_per_step": round(sa["mean"], 5),
                              "ms_median": round(sa["median"], 5), "steps": api_steps,
+                             "binding": M.public_api_kind(),
                              "note": "device-resident inputs through GaussianRasterizer + autograd (stream launches): the loop the "
                                      "reference arm's `value` is measured with"},
         "e2e": e2e_object(mpix, pipe_ms_step, se, h2d, d2h, e2e_steps, device_mallocs=e2e_mallocs),

@@ -5,7 +5,7 @@ Public surface (mirrors DGR/diff_gaussian_rasterization/__init__.py):
 plus the fused front end of gaussian_renderer/__init__.py:57-85: skinning.frame_tables, skinning.skin_and_covariance
 """
 from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer, rasterize_gaussians,  # noqa: F401
-                         forward_raw, backward_raw, forward_batch_raw, backward_batch_raw, rasterize_batch, set_gradient_sink, export_state, set_segmented_backward,
+                         forward_raw, backward_raw, forward_batch_raw, backward_batch_raw, rasterize_batch, set_gradient_sink, public_api_kind, export_state, set_segmented_backward,
                          add_densification_stats)
 
 from . import skinning  # noqa: F401,E402  (fused LBS + covariance front end: skinning.skin_and_covariance)

@@ -197,11 +197,14 @@ inline bool make_batch(const MossScene* sc, int V, const MossView* views, ViewBa
 
 // Blend block shape (1 whole tile / 2 half / 3 quarter).  Small images have few busy tiles and the deepest one sets
 // the launch time, so its patches are spread over more SMs; large images have enough tiles to fill the machine
-// and prefer fewer, larger blocks (less duplicated staging).
-inline int blend_split(unsigned flags, int T)
+// and prefer fewer, larger blocks (less duplicated staging).  A batch of views of a body-sized image has enough busy
+// tiles but they stay deep (1000-4000 instances): half-tile blocks measured best there (tools/batch_split_probe.py:
+// 23 ZJU views 1251 us vs 1351 us with whole tiles, 1264 us with quarters).
+inline int blend_split(unsigned flags, int T, int V)
 {
 	const int f = (int)((flags & MOSS_FLAG_SPLIT_MASK) >> MOSS_FLAG_SPLIT_SHIFT);
 	if (f) return f;
+	if (V > 1) return T <= 6144 ? 2 : 1;
 	return T <= 2048 ? 3 : (T <= 6144 ? 2 : 1);
 }
 
@@ -209,7 +212,7 @@ inline int blend_split(unsigned flags, int T)
 inline CkptWS scene_ckpt(const MossScene* sc, uint32_t capacity, size_t N, int T, int V, unsigned flags)
 {
 	// whole-tile (8-warp) blocks stage 256 instances per round and would skip every other boundary
-	if (blend_split(flags, T * V) == 1 && CKPT_SEG < 256) return no_ckpt();
+	if (blend_split(flags, T, V) == 1 && CKPT_SEG < 256) return no_ckpt();
 	if (!sc->ckpt_ws || sc->ckpt_bytes < moss_ckpt_workspace_bytes_batch((long long)capacity, sc->W, sc->H, V)) return no_ckpt();
 	return carve_ckpt((char*)sc->ckpt_ws, N, (size_t)T * V, (size_t)capacity);
 }
@@ -416,7 +419,7 @@ int forward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossView
 	MOSS_CHECK_LAUNCH(stream, flags);
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_FWD, stream);
 	const bool cull = !(flags & MOSS_FLAG_NO_CULL);
-	switch (blend_split(flags, TV)) {
+	switch (blend_split(flags, T, V)) {
 	case 1:
 		if (cull) blend_forward_kernel<true, 8><<<TV, 256, 0, stream>>>(vb, g, im, b, ck, out_color, out_depth, out_alpha);
 		else blend_forward_kernel<false, 8><<<TV, 256, 0, stream>>>(vb, g, im, b, ck, out_color, out_depth, out_alpha);
@@ -514,7 +517,7 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 	}
 
 	{ MOSS_STAGE(MOSS_STAGE_BLEND_BWD, stream);
-	switch (blend_split(flags, TV)) {
+	switch (blend_split(flags, T, V)) {
 	case 1: blend_backward_kernel<8><<<units, 256, 0, stream>>>(vb, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
 	case 2: blend_backward_kernel<4><<<2 * units, 128, 0, stream>>>(vb, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;
 	default: blend_backward_kernel<2><<<4 * units, 64, 0, stream>>>(vb, g, im, b, ck, dL_dpix, dL_ddepth, dL_dalpha, det); break;

@@ -114,6 +114,12 @@ class PeerGradBuffer:
         torch.cuda.synchronize(device)
         dist.barrier(group)
 
+    def raw_pointers(self):
+        """(gradient buffers, staging areas, signal pads) of all ranks as mapped in this process (lists of ints)."""
+        numel = self.tensor.numel()
+        h = self.handle
+        return ([int(p) for p in h.buffer_ptrs], [int(p) + 4 * numel for p in h.buffer_ptrs], [int(p) for p in h.signal_pad_ptrs])
+
     def descriptor(self, param_numel):
         """ctypes MossPush for a backward that sums the leading `param_numel` floats of ``tensor`` over the ranks
         (include/moss_splat.h: moss_rasterize_backward_push)."""

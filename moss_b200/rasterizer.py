@@ -13,6 +13,8 @@ Differences that are invisible through the API:
 """
 from typing import NamedTuple
 import ctypes as C
+import os
+import sys
 
 import torch
 import torch.nn as nn
@@ -75,9 +77,12 @@ def set_segmented_backward(mode):
     return prev
 
 
-def _want_ckpt(W, H):
+def _want_ckpt(W, H, V=1):
     if _segmented_backward == "auto":
-        return ((W + 15) // 16) * ((H + 15) // 16) <= 4096
+        T = ((W + 15) // 16) * ((H + 15) // 16)
+        # a batch of many views already fills the GPU with tiles: the checkpoint traffic then costs more than the shorter
+        # critical path saves (tools/batch_split_probe.py: 8 ZJU views 525 vs 539 us with segments, 23 views 1314 vs 1251)
+        return T <= 4096 and T * V <= 12288
     return bool(_segmented_backward)
 
 
@@ -169,7 +174,7 @@ def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_p
         stream = torch.cuda.current_stream(dev).cuda_stream
         nr = C.c_int(0)
         call_flags = flags
-        want_ckpt = _want_ckpt(W, H)
+        want_ckpt = _want_ckpt(W, H, V)
         while True:
             bbytes = lib.moss_binning_workspace_bytes_ex(cap, export)
             binning = torch.empty((bbytes,), dtype=torch.uint8, device=dev)
@@ -308,10 +313,62 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
 backward_batch_raw = backward_raw      # the state knows whether it came from a batched forward
 
 
+# The public API runs through the compiled autograd binding (moss_b200/_C.so, csrc/torch_binding.cpp: the same glue as
+# the Python autograd.Function below, written in C++ like the reference's DGR/rasterize_points.cu + ext.cpp) when it is
+# built; MOSS_PUBLIC_API=python forces the Python Function, =cpp makes a missing binding an error.  Both drive the same
+# C-ABI kernels -- neither is a fallback in the sense of a different compute path.
+_binding = None
+_binding_tried = False
+
+
+def _load_binding():
+    global _binding, _binding_tried
+    if _binding_tried:
+        return _binding
+    _binding_tried = True
+    mode = os.environ.get("MOSS_PUBLIC_API", "auto")
+    if mode == "python":
+        return None
+    try:
+        _abi.load()
+        from . import _C as b
+        if b.abi_version() != _abi.load().moss_abi_version():
+            raise ImportError("moss_b200/_C.so was built against another libmoss_splat.so; rebuild (python -m moss_b200.build)")
+        _binding = b
+    except ImportError as e:
+        if mode == "cpp":
+            raise
+        print(f"moss_b200: compiled autograd binding unavailable ({e}); using the Python autograd.Function", file=sys.stderr)
+    return _binding
+
+
+def public_api_kind():
+    return "compiled autograd binding (moss_b200/_C.so)" if _load_binding() is not None else "python autograd.Function over ctypes"
+
+
+def _rasterize(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings, batched):
+    b = _load_binding()
+    if b is None:
+        return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
+                                         cov3Ds_precomp, list(raster_settings) if batched else raster_settings)
+    lst = list(raster_settings) if batched else [raster_settings]
+    rs = lst[0]
+    H, W = int(rs.image_height), int(rs.image_width)
+    if batched:
+        for r in lst[1:]:
+            if (int(r.image_height), int(r.image_width), int(r.sh_degree), float(r.scale_modifier), bool(r.prefiltered)) != \
+                    (H, W, int(rs.sh_degree), float(rs.scale_modifier), bool(rs.prefiltered)):
+                raise RuntimeError("all views of a batched call share image size, SH degree, scale modifier and prefiltered")
+    out = b.rasterize(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                      [r.bg for r in lst], [r.viewmatrix for r in lst], [r.projmatrix for r in lst], [r.campos for r in lst],
+                      [float(r.tanfovx) for r in lst], [float(r.tanfovy) for r in lst], H, W, float(rs.scale_modifier),
+                      int(rs.sh_degree), bool(rs.prefiltered), any(r.debug for r in lst), batched, _want_ckpt(W, H, len(lst)), 0)
+    return tuple(out)
+
+
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
-    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings)
+    return _rasterize(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings, False)
 
 
 # Data-parallel training through the public API: with a sink set (parallel.PeerGradBuffer), the autograd backward writes
@@ -324,6 +381,14 @@ def set_gradient_sink(peer):
     """peer: parallel.PeerGradBuffer or None.  Returns the previous sink."""
     global _gradient_sink
     prev, _gradient_sink = _gradient_sink, peer
+    b = _load_binding()
+    if b is not None:
+        if peer is None:
+            b.set_gradient_sink(None, 0, 1, [], [], [], 0, 0, 0)
+        else:
+            g, st, pads = peer.raw_pointers()
+            b.set_gradient_sink(peer.tensor, peer.rank, peer.world, g, st, pads, int(peer.handle.signal_pad_size),
+                                int(peer.multicast_ptr or 0), peer.error.data_ptr())
     return prev
 
 
@@ -373,9 +438,9 @@ def rasterize_batch(means3D, means2D, opacities, settings_list, shs=None, colors
             ((scales is not None or rotations is not None) and cov3D_precomp is not None):
         raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
     e = _EMPTY
-    return _RasterizeGaussians.apply(means3D, means2D, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
-                                     opacities, e if scales is None else scales, e if rotations is None else rotations,
-                                     e if cov3D_precomp is None else cov3D_precomp, list(settings_list))
+    return _rasterize(means3D, means2D, e if shs is None else shs, e if colors_precomp is None else colors_precomp,
+                      opacities, e if scales is None else scales, e if rotations is None else rotations,
+                      e if cov3D_precomp is None else cov3D_precomp, list(settings_list), True)
 
 
 class GaussianRasterizer(nn.Module):

@@ -178,3 +178,19 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src.replace("CPU oracle", "").replace("the oracle", "") or f == "synth.py", f
+
+
+def test_compiled_autograd_binding_builds_and_loads(lib):
+    """moss_b200/_C.so (csrc/torch_binding.cpp): builds against this interpreter's torch, links the C-ABI library and
+    refuses CPU tensors (no CPU path)."""
+    build.build_binding()
+    from moss_b200 import rasterizer as R
+    import moss_b200 as M
+    b = R._load_binding()
+    assert b is not None and b.abi_version() == lib.moss_abi_version()
+    rs = M.GaussianRasterizationSettings(16, 16, 1.0, 1.0, torch.zeros(3), 1.0, torch.eye(4), torch.eye(4), 3, torch.zeros(3), False, False)
+    with pytest.raises(RuntimeError, match="CUDA tensors"):
+        M.GaussianRasterizer(rs)(torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 1), shs=torch.zeros(4, 16, 3),
+                                 scales=torch.zeros(4, 3), rotations=torch.zeros(4, 4))
+    with pytest.raises(Exception, match="excatly one of either SHs"):
+        M.GaussianRasterizer(rs)(torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 1), scales=torch.zeros(4, 3), rotations=torch.zeros(4, 4))

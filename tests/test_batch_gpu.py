@@ -167,3 +167,42 @@ def test_single_view_outputs_can_be_edited_in_place():
     color.permute(1, 2, 0)[alpha[0] < 0.5] = 0
     (color.sum() + depth.sum()).backward()
     assert torch.isfinite(t["means3D"].grad).all()
+
+
+@pytest.mark.parametrize("name,V", [("small", 1), ("small_cov", 1), ("small_color", 3), ("ragged", 4)])
+def test_compiled_binding_equals_python_autograd_function(name, V):
+    """The public API runs through moss_b200/_C.so (csrc/torch_binding.cpp); the Python autograd.Function over ctypes is
+    the same glue.  Both must give identical forward bits and (deterministic accumulation aside) the same gradients,
+    for single-view and batched calls, and free their state the same way."""
+    from moss_b200 import rasterizer as R
+    if R._load_binding() is None:
+        pytest.skip("compiled binding not built")
+    d = S.make_scene(name)
+    cams = _cams(d, V, 5)
+    rs = [_settings(d, c) for c in cams]
+    W, H = cams[0].image_width, cams[0].image_height
+    gc, gd, ga = _upstream(V, W, H)
+    batched = V > 1
+    if not batched:
+        gc, gd, ga = gc[0], gd[0], ga[0]
+    res = []
+    for use_cpp in (True, False):
+        t = {k: (d[k].to(DEV).requires_grad_(True) if d[k] is not None else R._EMPTY)
+             for k in ("means3D", "shs", "colors_precomp", "opacities", "scales", "rotations", "cov3D_precomp")}
+        P = d["means3D"].shape[0]
+        m2 = torch.zeros(((V,) if batched else ()) + (P, 3), device=DEV, requires_grad=True)
+        args = (t["means3D"], m2, t["shs"], t["colors_precomp"], t["opacities"], t["scales"], t["rotations"], t["cov3D_precomp"])
+        if use_cpp:
+            out = R._rasterize(*args, rs if batched else rs[0], batched)
+        else:
+            out = R._RasterizeGaussians.apply(*args, rs if batched else rs[0])
+        color, radii, depth, alpha = out
+        torch.autograd.backward([color, depth, alpha], [gc, gd, ga])
+        res.append((color.detach(), radii, depth.detach(), alpha.detach(), m2.grad, {k: v.grad for k, v in t.items() if v.numel()}))
+        with pytest.raises(RuntimeError):
+            torch.autograd.backward([color], [gc])          # state was freed by the first backward
+    a, b = res
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]) and torch.equal(a[2], b[2]) and torch.equal(a[3], b[3])
+    assert rel_err(a[4], b[4]) <= 1e-5
+    for k in a[5]:
+        assert rel_err(a[5][k], b[5][k]) <= 1e-5, k
