@@ -270,6 +270,9 @@ typedef struct MossPush {
     unsigned* error_word_dev;    /* device uint32[4], zeroed once; [0] != 0: a peer did not arrive; [1]: exchanges done */
 } MossPush;
 size_t moss_push_slice_floats(size_t numel, int world);
+/* The exchange alone, for a packed gradient that something else produced: sums [grad_base, grad_base + numel) over the
+ * ranks in place (push to the owners' staging areas, gather), one kernel. */
+int moss_push_allreduce(void* stream, const MossPush* push);
 size_t moss_sizeof_push(void);
 int moss_rasterize_backward_push(void* stream, const MossScene* scene, int V, const MossView* views, unsigned flags,
                                  const int* radii, const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,

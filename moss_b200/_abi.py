@@ -37,7 +37,7 @@ SYMBOLS = [
     "moss_profile_enable", "moss_profile_read", "moss_stage_name",
     "moss_geom_workspace_bytes_batch", "moss_image_workspace_bytes_batch", "moss_ckpt_workspace_bytes_batch",
     "moss_batch_grad_workspace_bytes", "moss_rasterize_forward_batch", "moss_rasterize_backward_batch", "moss_sizeof_view",
-    "moss_export_state_batch", "moss_push_slice_floats", "moss_sizeof_push", "moss_rasterize_backward_push",
+    "moss_export_state_batch", "moss_push_slice_floats", "moss_sizeof_push", "moss_rasterize_backward_push", "moss_push_allreduce",
     "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
 ]
 STAGE_COUNT = 16
@@ -159,6 +159,8 @@ def load():
     lib.moss_push_slice_floats.restype = C.c_size_t
     lib.moss_push_slice_floats.argtypes = [C.c_size_t, C.c_int]
     lib.moss_sizeof_push.restype = C.c_size_t
+    lib.moss_push_allreduce.restype = C.c_int
+    lib.moss_push_allreduce.argtypes = [vp, C.POINTER(MossPush)]
     lib.moss_rasterize_backward_push.restype = C.c_int
     lib.moss_rasterize_backward_push.argtypes = [vp, C.POINTER(MossScene), C.c_int, C.POINTER(MossView), C.c_uint, vp] + [vp] * 12 + \
         [vp, C.c_size_t, C.POINTER(MossPush)]

@@ -343,6 +343,36 @@ inline BatchRow batch_row(size_t P, size_t M)
 	return r;
 }
 
+// validates a MossPush and derives the producer-side routing table, the gather kernel's arguments and its grid
+int make_gather(const MossPush* push, PushCfg* pc, GatherArgs* ga, unsigned* gather_blocks)
+{
+	if (push->world < 1 || push->world > PEER_MAX_WORLD || push->rank < 0 || push->rank >= push->world || !push->grad_base ||
+		((uintptr_t)push->grad_base & 15) || (push->numel & 3) || push->numel == 0 || push->numel > 0xfffffff0ull ||
+		!push->grad_ptrs || !push->stage_ptrs || !push->signal_ptrs || !push->error_word_dev ||
+		push->signal_pad_bytes < moss_peer_signal_bytes(push->world))
+		return MOSS_ERR_INVALID_ARGUMENT;
+	const size_t S = moss_push_slice_floats(push->numel, push->world);
+	pc->base = push->grad_base; pc->numel = (uint32_t)push->numel; pc->S = (uint32_t)S;
+	memset(ga, 0, sizeof(*ga));
+	for (int o = 0; o < push->world; o++) {
+		if (!push->grad_ptrs[o] || !push->stage_ptrs[o] || !push->signal_ptrs[o]) return MOSS_ERR_INVALID_ARGUMENT;
+		pc->stage_mine[o] = (float*)push->stage_ptrs[o] + (size_t)push->rank * S;
+		ga->stage_mine[o] = pc->stage_mine[o];
+		ga->grad[o] = (float*)push->grad_ptrs[o];
+		ga->pads[o] = (uint32_t*)push->signal_ptrs[o];
+	}
+	ga->stage = (const float*)push->stage_ptrs[push->rank];
+	ga->mc_grad = (float*)push->multicast_grad;
+	ga->err = push->error_word_dev;
+	ga->numel = pc->numel; ga->S = pc->S; ga->rank = push->rank; ga->world = push->world;
+	// every rank derives the same grid from (numel, world, pad size): the flag slots are indexed by it
+	size_t blocks = (S / 4 + (size_t)GATHER_THREADS * GATHER_ILP - 1) / ((size_t)GATHER_THREADS * GATHER_ILP);
+	const size_t pad_blocks = push->signal_pad_bytes / (sizeof(uint32_t) * 2 * (size_t)push->world);
+	blocks = std::min(blocks, std::min(pad_blocks, (size_t)PEER_MAX_BLOCKS));
+	*gather_blocks = (unsigned)std::max<size_t>(blocks, 1);
+	return MOSS_OK;
+}
+
 int forward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossView* views, unsigned flags,
 	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
 {
@@ -462,29 +492,8 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 	GatherArgs ga;
 	unsigned gather_blocks = 0;
 	if (push) {
-		if (push->world < 1 || push->world > PEER_MAX_WORLD || push->rank < 0 || push->rank >= push->world || !push->grad_base ||
-			((uintptr_t)push->grad_base & 15) || (push->numel & 3) || push->numel == 0 || push->numel > 0xfffffff0ull ||
-			!push->grad_ptrs || !push->stage_ptrs || !push->signal_ptrs || !push->error_word_dev ||
-			push->signal_pad_bytes < moss_peer_signal_bytes(push->world))
-			return MOSS_ERR_INVALID_ARGUMENT;
-		const size_t S = moss_push_slice_floats(push->numel, push->world);
-		pc.base = push->grad_base; pc.numel = (uint32_t)push->numel; pc.S = (uint32_t)S;
-		memset(&ga, 0, sizeof(ga));
-		for (int o = 0; o < push->world; o++) {
-			if (!push->grad_ptrs[o] || !push->stage_ptrs[o] || !push->signal_ptrs[o]) return MOSS_ERR_INVALID_ARGUMENT;
-			pc.stage_mine[o] = (float*)push->stage_ptrs[o] + (size_t)push->rank * S;
-			ga.grad[o] = (float*)push->grad_ptrs[o];
-			ga.pads[o] = (uint32_t*)push->signal_ptrs[o];
-		}
-		ga.stage = (const float*)push->stage_ptrs[push->rank];
-		ga.mc_grad = (float*)push->multicast_grad;
-		ga.err = push->error_word_dev;
-		ga.numel = pc.numel; ga.S = pc.S; ga.rank = push->rank; ga.world = push->world;
-		// every rank derives the same grid from (numel, world, pad size): the flag slots are indexed by it
-		size_t blocks = (S / 4 + (size_t)GATHER_THREADS * GATHER_ILP - 1) / ((size_t)GATHER_THREADS * GATHER_ILP);
-		const size_t pad_blocks = push->signal_pad_bytes / (sizeof(uint32_t) * 2 * (size_t)push->world);
-		blocks = std::min(blocks, std::min(pad_blocks, (size_t)PEER_MAX_BLOCKS));
-		gather_blocks = (unsigned)std::max<size_t>(blocks, 1);
+		const int r = make_gather(push, &pc, &ga, &gather_blocks);
+		if (r != MOSS_OK) return r;
 	}
 	const int P = sc->P, W = sc->W, H = sc->H, N = W * H;
 	if (P == 0) return MOSS_OK;
@@ -539,7 +548,7 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 	{ MOSS_STAGE(MOSS_STAGE_PREPROCESS_BWD, stream);
 	preprocess_backward_kernel<<<dim3((P + PRE_THREADS - 1) / PRE_THREADS, V), PRE_THREADS, 0, stream>>>(
 		vb, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
-		dL_dmean2D, dL_dconic, po, det, im.counters, V == 1 ? pc : no_push()); }
+		dL_dmean2D, dL_dconic, po, det, im.counters, no_push()); }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	if (V > 1) {
 		SumViewsArgs a;
@@ -557,6 +566,9 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 		MOSS_CHECK_LAUNCH(stream, flags);
 	}
 	if (push) {
+		// one view: the rows were written locally (K7's small strided stores make poor NVLink packets) and the gather
+		// kernel opens with a coalesced push; a batch: the view sum already pushed them
+		ga.push_src = V == 1 ? push->grad_base : nullptr;
 		{ MOSS_STAGE(MOSS_STAGE_PUSH_GATHER, stream);
 		push_gather_kernel<<<gather_blocks, GATHER_THREADS, 0, stream>>>(ga); }
 		MOSS_CHECK_LAUNCH(stream, flags);
@@ -572,6 +584,19 @@ size_t moss_push_slice_floats(size_t numel, int world)
 {
 	const size_t w = (size_t)(world > 0 ? world : 1);
 	return ((numel + w - 1) / w + 3) / 4 * 4;
+}
+int moss_push_allreduce(void* stream_, const MossPush* push)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!push) return MOSS_ERR_INVALID_ARGUMENT;
+	PushCfg pc; GatherArgs ga; unsigned blocks = 0;
+	const int r = make_gather(push, &pc, &ga, &blocks);
+	if (r != MOSS_OK) return r;
+	ga.push_src = push->grad_base;
+	{ MOSS_STAGE(MOSS_STAGE_PUSH_GATHER, stream);
+	push_gather_kernel<<<blocks, GATHER_THREADS, 0, stream>>>(ga); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
 }
 int moss_rasterize_backward_push(void* stream, const MossScene* sc, int V, const MossView* views, unsigned flags, const int* radii,
 	const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,

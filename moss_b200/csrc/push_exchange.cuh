@@ -1,11 +1,16 @@
 // Gradient exchange fused into the backward (no reference counterpart: MOSS trains on one GPU).
 //
 // Data-parallel ranks render different views of the same Gaussians and their parameter gradients add.  Instead of
-// "write the packed gradient locally, then all-reduce it" (peer_reduce.cuh: barrier, remote loads, remote stores,
-// barrier), the kernel that PRODUCES the gradient rows -- the backward preprocess (one view) or the view sum (a batch)
-// -- stores every element straight into the staging area of the rank that owns it: a reduce-scatter done with posted
-// NVLink stores while the producer is still computing.  What is left behind the producer is ONE short kernel:
-//   signal "my rows are out" to every owner   -> wait until all ranks' rows have arrived in my staging area
+// "all ranks wait, then PULL each other's gradients" (peer_reduce.cuh: barrier, remote loads -- NVLink round trips --,
+// remote stores, barrier) every rank PUSHES: each element of its packed gradient is stored into the staging area of the
+// rank that owns it, a reduce-scatter made of posted NVLink stores that needs no barrier in front of it.
+//   * a batch of views: the view-sum kernel (sum_views_kernel) is the producer and its coalesced 16-byte stores go
+//     straight to the owners while it is still summing (route());
+//   * one view: the backward preprocess writes 4..16-byte pieces per thread at 12..192-byte strides, which NVLink
+//     turns into one small packet each (measured: K7 13 -> 31 us with routed stores at 2 ranks), so it keeps writing
+//     locally and the gather kernel below opens with a coalesced push of the L2-resident rows instead.
+// What is left behind the producer is ONE short kernel:
+//   [push my rows]  signal "my rows are out" to every owner -> wait until all ranks' rows have arrived in my staging area
 //   sum the `world` staged copies of my slice in rank order (local reads; bit-reproducible)
 //   store the result into slice `rank` of EVERY rank's gradient buffer (one multimem.st through the switch, or
 //   `world` peer stores), signal "slice delivered" -> wait for the other owners' slices.
@@ -44,6 +49,8 @@ inline PushCfg no_push()
 }
 
 struct GatherArgs {
+	const float* push_src;           // my packed gradient if this kernel does the push itself, null if the producer did
+	float* stage_mine[PEER_MAX_WORLD];   // stage_mine[o] = rank o's staging area + my_rank * S
 	float* grad[PEER_MAX_WORLD];     // every rank's packed gradient buffer, as mapped here
 	uint32_t* pads[PEER_MAX_WORLD];  // signal pads
 	const float* stage;              // MY staging area: [world][S]
@@ -81,14 +88,37 @@ push_gather_kernel(const __grid_constant__ GatherArgs a)
 	const uint32_t epoch = ld_relaxed_sys(a.err + 1) + 1u;
 	__shared__ uint32_t* s_pads[PEER_MAX_WORLD];
 	if ((int)threadIdx.x < a.world) s_pads[threadIdx.x] = a.pads[threadIdx.x];
+	const uint32_t stride = gridDim.x * GATHER_THREADS;
+	const uint32_t S4 = a.S >> 2;
+	if (a.push_src) {
+		// Block b pushes, for every owner o, exactly the elements block b of rank o will sum (same index pattern), so a
+		// per-block flag is all the synchronisation the data needs.  All loads of a round are issued before its stores.
+		const float4* src4 = reinterpret_cast<const float4*>(a.push_src);
+		for (int o = 0; o < a.world; o++) {
+			const uint32_t olo = min(a.numel, a.S * (uint32_t)o), ohi = min(a.numel, olo + a.S);
+			const uint32_t on4 = (ohi - olo) >> 2;
+			float4* dst4 = reinterpret_cast<float4*>(a.stage_mine[o]);
+			for (uint32_t i0 = blockIdx.x * GATHER_THREADS + threadIdx.x; i0 < on4; i0 += stride * GATHER_ILP) {
+				float4 v[GATHER_ILP];
+#pragma unroll
+				for (int u = 0; u < GATHER_ILP; u++) {
+					const uint32_t i = i0 + u * stride;
+					if (i < on4) v[u] = __ldcg(src4 + (olo >> 2) + i);
+				}
+#pragma unroll
+				for (int u = 0; u < GATHER_ILP; u++) {
+					const uint32_t i = i0 + u * stride;
+					if (i < on4) st_peer_f4(dst4 + i, v[u]);
+				}
+			}
+		}
+	}
 	// phase 0: the producers of all ranks (earlier kernels in their streams) have pushed their rows into my staging area
 	flag_exchange(s_pads, a.rank, a.world, 0, epoch, a.err);
 
 	const uint32_t lo = min(a.numel, a.S * (uint32_t)a.rank), hi = min(a.numel, lo + a.S);   // my slice of the prefix
 	const uint32_t n4 = (hi - lo) >> 2;
-	const uint32_t stride = gridDim.x * GATHER_THREADS;
 	const float4* st4 = reinterpret_cast<const float4*>(a.stage);
-	const uint32_t S4 = a.S >> 2;
 	for (uint32_t i0 = blockIdx.x * GATHER_THREADS + threadIdx.x; i0 < n4; i0 += stride * GATHER_ILP) {
 		float4 s[GATHER_ILP];
 #pragma unroll
@@ -96,9 +126,9 @@ push_gather_kernel(const __grid_constant__ GatherArgs a)
 			const uint32_t i = i0 + u * stride;
 			s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
 			if (i < n4) {
-				s[u] = st4[i];
+				s[u] = __ldcg(st4 + i);
 				for (int p = 1; p < a.world; p++) {
-					const float4 x = st4[(size_t)p * S4 + i];
+					const float4 x = __ldcg(st4 + (size_t)p * S4 + i);
 					s[u].x += x.x; s[u].y += x.y; s[u].z += x.z; s[u].w += x.w;
 				}
 			}

@@ -158,6 +158,16 @@ class PeerGradBuffer:
         _abi.check(st, "moss_peer_allreduce")
         return self.tensor
 
+    def push_allreduce(self, numel):
+        """Sum tensor[:numel] (numel a multiple of 4) over all ranks, in place, with the push exchange (one kernel: rows
+        pushed to their owners' staging areas, gathered sums stored to every rank; include/moss_splat.h:
+        moss_push_allreduce).  Same result on every rank, summed in rank order."""
+        import ctypes as C
+        from . import _abi
+        st = self._lib.moss_push_allreduce(torch.cuda.current_stream(self.device).cuda_stream, C.byref(self.descriptor(int(numel))))
+        _abi.check(st, "moss_push_allreduce")
+        return self.tensor
+
     def check(self):
         """Host-side check (synchronises): did any spin time out?"""
         if int(self.error[0].item()) != 0:

@@ -54,6 +54,25 @@ def _worker(rank, world, port, multimem):
                 assert torch.equal(buf.tensor[:n], ref), f"iteration {it}: peer all-reduce differs from NCCL"
             else:
                 assert torch.allclose(buf.tensor[:n], ref, rtol=1e-5, atol=1e-5)
+        # the push exchange on its own (moss_push_allreduce): rank-ordered sums, identical on every rank
+        n4 = n // 4 * 4
+        for it in range(3):
+            g = torch.Generator(device=dev).manual_seed(77 * it + rank)
+            x = torch.randn(n4, device=dev, generator=g)
+            buf.tensor[:n4].copy_(x)
+            ref = x.clone()
+            dist.all_reduce(ref)
+            buf.push_allreduce(n4)
+            torch.cuda.synchronize(dev)
+            buf.check()
+            assert torch.allclose(buf.tensor[:n4], ref, rtol=1e-5, atol=1e-5)
+            if world == 2:
+                assert torch.equal(buf.tensor[:n4], ref)
+            chk = buf.tensor[:n4].clone()
+            dist.broadcast(chk, src=0)
+            assert torch.equal(chk, buf.tensor[:n4]), "push exchange: ranks disagree"
+        buf.tensor[:n].copy_(torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(5 + rank)))
+        buf.allreduce(n)
         mine = buf.tensor[:n].clone()
         other = mine.clone()
         dist.broadcast(other, src=0)

@@ -27,7 +27,13 @@ for n in (1_220_000, 6_100_000):
     with torch.cuda.graph(g):
         for _ in range(10): buf.allreduce(n)
     t_graph = timeit(g.replay, 50) / 10
+    t_push = timeit(lambda: buf.push_allreduce(n))
+    g2 = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g2):
+        for _ in range(10): buf.push_allreduce(n)
+    t_push_graph = timeit(g2.replay, 50) / 10
     buf.check()
     if rank == 0:
-        print(f"world {world} numel {n} ({n*4/1e6:.1f} MB): peer {t_peer:.1f} us  peer(graph x10) {t_graph:.1f} us  nccl {t_nccl:.1f} us  pad {buf.handle.signal_pad_size} B  multicast {hex(buf.multicast_ptr)}")
+        print(f"world {world} numel {n} ({n*4/1e6:.1f} MB): pull {t_peer:.1f} us  pull(graph x10) {t_graph:.1f} us  push {t_push:.1f} us  "
+              f"push(graph x10) {t_push_graph:.1f} us  nccl {t_nccl:.1f} us  pad {buf.handle.signal_pad_size} B  multicast {hex(buf.multicast_ptr)}", flush=True)
 dist.destroy_process_group()
