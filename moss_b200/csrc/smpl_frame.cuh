@@ -42,7 +42,8 @@ struct SmplFrameArgs {
 	const float* shapes;        // [n_shapes]
 	const float* correct_Rs;    // [23,9] or null
 	float* A;                   // [24,16]
-	float* rot_mats;            // [24,9]  (after the pose correction)
+	float* rot_mats;            // [24,9]  (after the pose correction) or null
+	float* joints;              // [24,3]  J_regressor . v_shaped (the backward reads it) or null
 	float* poseoff;             // [V,3] or null (skip the pose blocks' work)
 	float* shapeoff;            // [V,3] or null
 	float* partial;             // scratch: [shape_blocks][72] joint partial sums
@@ -86,6 +87,7 @@ smpl_frame_forward_kernel(const __grid_constant__ SmplFrameArgs a)
 	__shared__ float s_pf[NPF + 1];
 	__shared__ float s_chain[NJ][12];       // rows 0..2 of the 4x4 chain transform
 	__shared__ float s_joint[NJ][3];
+	__shared__ float s_rot[NJ][9];
 	__shared__ bool s_last;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
@@ -167,15 +169,22 @@ smpl_frame_forward_kernel(const __grid_constant__ SmplFrameArgs a)
 		float s = 0.f;
 		for (int b = 0; b < a.shape_blocks; b++) s += __ldcg(a.partial + (size_t)b * (NJ * 3) + tid);
 		s_joint[tid / 3][tid % 3] = s;
+		if (a.joints) a.joints[tid] = s;
+	}
+	if (tid >= 96 && tid < 96 + NJ) {           // a different warp than the joint sums: the 24 Rodrigues evaluations
+		const int j = tid - 96;
+		const Mat3 R = joint_rotation(a.poses, a.correct_Rs, j);
+#pragma unroll
+		for (int i = 0; i < 9; i++) { s_rot[j][i] = R.m[i]; if (a.rot_mats) a.rot_mats[9 * j + i] = R.m[i]; }
 	}
 	__syncthreads();
 	if (tid == 0) {
 		*a.ticket = 0u;
 		// the chain is 24 dependent 3x4 products: one thread walks it (parents precede children in SMPL's ordering)
 		for (int j = 0; j < NJ; j++) {
-			const Mat3 R = joint_rotation(a.poses, a.correct_Rs, j);
+			Mat3 R;
 #pragma unroll
-			for (int i = 0; i < 9; i++) a.rot_mats[9 * j + i] = R.m[i];
+			for (int i = 0; i < 9; i++) R.m[i] = s_rot[j][i];
 			const int p = j == 0 ? -1 : a.parents[j];
 			float rel[3];
 #pragma unroll
@@ -214,7 +223,6 @@ smpl_frame_forward_kernel(const __grid_constant__ SmplFrameArgs a)
 struct SmplFrameBwdArgs {
 	int V;
 	const float* posedirs;      // [V*3, 207]
-	const float* J_regressor;   // unused (joints come from `joints`)
 	const int*   parents;       // [24]
 	const float* poses;         // [72]
 	const float* correct_Rs;    // [23,9] or null
