@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define MOSS_ABI_VERSION 9
+#define MOSS_ABI_VERSION 10
 
 /* status codes */
 #define MOSS_OK                  0
@@ -197,6 +197,47 @@ int moss_skin_backward(void* stream, const MossSkin* skin, const float* g_means3
                        float* d_A_tgt, float* d_poseoff_tgt);
 size_t moss_sizeof_skin(void);
 
+/* Per-frame SMPL tables: what render() recomputes for every frame before it touches a
+ * Gaussian, as ONE launch forward and ONE backward instead of ~60 torch launches and two Python loops over the joints.
+ * Replaces batch_rodrigues (scene/gaussian_model.py:1033-1064), the optional pose correction rot[1:] @ correct_Rs
+ * (:885-888, :1015-1018), get_transform_params_torch (:998-1031: v_shaped, joints = J_regressor . v_shaped),
+ * get_rigid_transformation_torch (:965-995: the 24-joint kinematic chain), the pose blend shapes
+ * pose_offsets = (rot[1:] - I).flatten() @ posedirs^T (:855-861, :878-893) and the shape blend shapes (:870-871).
+ * All arrays float32 on the device unless noted. */
+typedef struct MossSmplFrame {
+    int V;                      /* SMPL vertices (6890) */
+    int n_shapes;               /* betas used, <= shape_stride (params['shapes'].shape[-1]) */
+    int shape_stride;           /* last dimension of shapedirs (10) */
+    const float* shapedirs;     /* [V,3,shape_stride] */
+    const float* posedirs;      /* [V,3,207] (the reference's layout: one row of 207 per vertex coordinate) */
+    const float* J_template;    /* [24,3]              J_regressor . v_template   } from moss_smpl_joint_tables(), */
+    const float* J_shapedirs;   /* [24,3,shape_stride] J_regressor . shapedirs    } once per SMPL model            */
+    const int*   parents;       /* int32 [24], kintree_table[0]; parents[j] < j, parents[0] ignored */
+    const float* poses;         /* [72] axis-angle */
+    const float* shapes;        /* [n_shapes] */
+    const float* correct_Rs;    /* [23,9] or NULL */
+    void* scratch;              /* >= moss_smpl_frame_scratch_bytes(V) bytes, zeroed ONCE by the caller (self-cleaning);
+                                   used by the backward only */
+    size_t scratch_bytes;
+} MossSmplFrame;
+size_t moss_smpl_frame_scratch_bytes(int V);
+size_t moss_sizeof_smpl_frame(void);
+/* The two joint-regression tables of an SMPL model (constants of a run): joints = J_regressor . (v_template +
+ * shapedirs . betas) (scene/gaussian_model.py:1007, :1021) = J_template + J_shapedirs . betas, so the per-frame kernel
+ * needs no pass over the vertices.  v_template [V,3], shapedirs [V,3,S], J_regressor [24,V] -> J_template [24,3],
+ * J_shapedirs [24,3,S]. */
+int moss_smpl_joint_tables(void* stream, int V, int S, const float* v_template, const float* shapedirs,
+                           const float* J_regressor, float* J_template, float* J_shapedirs);
+/* A [24,16] (row-major 4x4 per joint) is always written; rot_mats [24,9] (after the correction), joints [24,3],
+ * poseoff [V,3], shapeoff [V,3] are optional (NULL to skip; a NULL poseoff skips reading posedirs altogether). */
+int moss_smpl_frame_forward(void* stream, const MossSmplFrame* frame, float* A, float* rot_mats, float* joints,
+                            float* poseoff, float* shapeoff);
+/* Gradients w.r.t. poses [72] (always written) and correct_Rs [23,9] (NULL to skip; zeros when frame->correct_Rs is
+ * NULL) from d_A [24,16] and d_poseoff [V,3] (either may be NULL = zero).  A and joints are the forward's outputs.
+ * shapes and the SMPL tables are constants of a run (no gradient), as in the reference's training loop. */
+int moss_smpl_frame_backward(void* stream, const MossSmplFrame* frame, const float* A, const float* joints,
+                             const float* d_A, const float* d_poseoff, float* d_poses, float* d_correct_Rs);
+
 /* Densification statistics of one iteration, for the Gaussians with radii > 0 (the reference's visibility_filter,
  * gaussian_renderer/__init__.py:128): max_radii2D = max(max_radii2D, radii) (train_ZJU.py:173), xyz_gradient_accum +=
  * |dL_dmean2D[:, :2]|, denom += 1 (GaussianModel.add_densification_stats, scene/gaussian_model.py:816-818).  All
@@ -325,7 +366,9 @@ long long moss_export_state_batch(void* stream, const MossScene* scene, int V, i
 #define MOSS_STAGE_ADAMW           13
 #define MOSS_STAGE_SUM_VIEWS       14
 #define MOSS_STAGE_PUSH_GATHER     15
-#define MOSS_STAGE_COUNT           16
+#define MOSS_STAGE_SMPL_FRAME      16
+#define MOSS_STAGE_SMPL_FRAME_BWD  17
+#define MOSS_STAGE_COUNT           18
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

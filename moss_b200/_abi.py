@@ -39,8 +39,9 @@ SYMBOLS = [
     "moss_batch_grad_workspace_bytes", "moss_rasterize_forward_batch", "moss_rasterize_backward_batch", "moss_sizeof_view",
     "moss_export_state_batch", "moss_push_slice_floats", "moss_sizeof_push", "moss_rasterize_backward_push", "moss_push_allreduce",
     "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
+    "moss_smpl_frame_scratch_bytes", "moss_sizeof_smpl_frame", "moss_smpl_frame_forward", "moss_smpl_frame_backward", "moss_smpl_joint_tables",
 ]
-STAGE_COUNT = 16
+STAGE_COUNT = 18
 
 
 class MossScene(C.Structure):
@@ -83,6 +84,15 @@ class MossSkin(C.Structure):
         ("A_big", C.c_void_p), ("A_tgt", C.c_void_p), ("poseoff_big", C.c_void_p), ("shapeoff", C.c_void_p),
         ("poseoff_tgt", C.c_void_p), ("Rg", C.c_void_p), ("Th", C.c_void_p), ("scaling", C.c_void_p),
         ("rotation", C.c_void_p), ("scale_modifier", C.c_float),
+    ]
+
+
+class MossSmplFrame(C.Structure):
+    _fields_ = [
+        ("V", C.c_int), ("n_shapes", C.c_int), ("shape_stride", C.c_int),
+        ("shapedirs", C.c_void_p), ("posedirs", C.c_void_p), ("J_template", C.c_void_p), ("J_shapedirs", C.c_void_p),
+        ("parents", C.c_void_p), ("poses", C.c_void_p), ("shapes", C.c_void_p), ("correct_Rs", C.c_void_p),
+        ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
     ]
 
 
@@ -179,6 +189,17 @@ def load():
     lib.moss_skin_forward.argtypes = [vp, C.POINTER(MossSkin)] + [vp] * 5
     lib.moss_skin_backward.restype = C.c_int
     lib.moss_skin_backward.argtypes = [vp, C.POINTER(MossSkin)] + [vp] * 8
+    lib.moss_smpl_frame_scratch_bytes.restype = C.c_size_t
+    lib.moss_smpl_frame_scratch_bytes.argtypes = [C.c_int]
+    lib.moss_sizeof_smpl_frame.restype = C.c_size_t
+    lib.moss_smpl_frame_forward.restype = C.c_int
+    lib.moss_smpl_frame_forward.argtypes = [vp, C.POINTER(MossSmplFrame)] + [vp] * 5
+    lib.moss_smpl_joint_tables.restype = C.c_int
+    lib.moss_smpl_joint_tables.argtypes = [vp, C.c_int, C.c_int] + [vp] * 5
+    lib.moss_smpl_frame_backward.restype = C.c_int
+    lib.moss_smpl_frame_backward.argtypes = [vp, C.POINTER(MossSmplFrame)] + [vp] * 6
+    if lib.moss_sizeof_smpl_frame() != C.sizeof(MossSmplFrame):
+        raise RuntimeError("moss_b200: MossSmplFrame layout mismatch between _abi.py and the library; rebuild")
     if lib.moss_sizeof_adam_group() != C.sizeof(MossAdamGroup):
         raise RuntimeError("MossAdamGroup layout differs between include/moss_splat.h and moss_b200/_abi.py")
     if lib.moss_sizeof_skin() != C.sizeof(MossSkin):

@@ -26,6 +26,7 @@
 #include "adamw.cuh"
 #include "peer_reduce.cuh"
 #include "push_exchange.cuh"
+#include "smpl_frame.cuh"
 
 using namespace moss;
 
@@ -150,6 +151,7 @@ struct SlotLease {             // releases the slot on every return path of the 
 
 // cudaFuncSetAttribute is per device: remember where the sort kernel's dynamic shared memory was already raised
 std::atomic<bool> g_sort_attr_set[MAX_DEVICES];
+std::atomic<bool> g_smpl_attr_set[MAX_DEVICES];
 
 inline bool scene_valid(const MossScene* sc, bool own_camera = true)
 {
@@ -264,7 +266,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step", "sum_views", "push_gather"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step", "sum_views", "push_gather", "smpl_frame_forward", "smpl_frame_backward"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -786,6 +788,77 @@ int moss_skin_backward(void* stream_, const MossSkin* k, const float* g_means3D,
 	{ MOSS_STAGE(MOSS_STAGE_SKIN_BWD, stream);
 		skin_backward_kernel<<<(k->P + SKIN_THREADS - 1) / SKIN_THREADS, SKIN_THREADS, 0, stream>>>(
 			make_skin(k), g_means3D, g_cov3D, d_xyz, d_scaling, d_rotation, d_lbs_delta, d_A_tgt, d_poseoff_tgt); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+// ---- per-frame SMPL tables -------------------------------------------------------------------------------------------
+// scratch layout (backward only): [0,16) ticket (zero between calls), chain dL/dR [24*9 floats], partial sums [pose_blocks][208]
+static int smpl_shape_blocks(int V) { return (V + SMPL_THREADS - 1) / SMPL_THREADS; }
+static int smpl_pose_blocks(int V) { return (3 * V + SMPL_ROWS_PER_BLOCK - 1) / SMPL_ROWS_PER_BLOCK; }
+static int smpl_bwd_blocks(int V) { return (3 * V + SMPL_BWD_STAGES * SMPL_ROWS_PER_BLOCK - 1) / (SMPL_BWD_STAGES * SMPL_ROWS_PER_BLOCK); }
+size_t moss_smpl_frame_scratch_bytes(int V)
+{
+	if (V < 1) return 16;
+	return 16 + ((size_t)NJ * 9 + (size_t)smpl_bwd_blocks(V) * (NPF + 1)) * sizeof(float);
+}
+size_t moss_sizeof_smpl_frame(void) { return sizeof(MossSmplFrame); }
+static bool smpl_frame_valid(const MossSmplFrame* f)
+{
+	return f && f->V >= 1 && f->n_shapes >= 0 && f->n_shapes <= f->shape_stride && f->parents && f->poses &&
+		(f->shapes || f->n_shapes == 0);
+}
+
+int moss_smpl_joint_tables(void* stream_, int V, int S, const float* v_template, const float* shapedirs,
+	const float* J_regressor, float* J_template, float* J_shapedirs)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (V < 1 || S < 0 || !v_template || !J_regressor || !J_template || (S > 0 && (!shapedirs || !J_shapedirs)))
+		return MOSS_ERR_INVALID_ARGUMENT;
+	{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
+		smpl_joint_tables_kernel<<<dim3(NJ, 1 + S), SMPL_THREADS, 0, stream>>>(V, S, v_template, shapedirs, J_regressor, J_template, J_shapedirs); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+int moss_smpl_frame_forward(void* stream_, const MossSmplFrame* f, float* A, float* rot_mats, float* joints,
+	float* poseoff, float* shapeoff)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!smpl_frame_valid(f) || !A || !f->J_template || (f->n_shapes > 0 && !f->J_shapedirs) || (poseoff && !f->posedirs) ||
+		(shapeoff && f->n_shapes > 0 && !f->shapedirs)) return MOSS_ERR_INVALID_ARGUMENT;
+	SmplFrameArgs a;
+	a.V = f->V; a.n_shapes = f->n_shapes; a.shape_stride = f->shape_stride;
+	a.shapedirs = f->shapedirs; a.posedirs = f->posedirs; a.J_template = f->J_template; a.J_shapedirs = f->J_shapedirs;
+	a.parents = f->parents; a.poses = f->poses; a.shapes = f->shapes; a.correct_Rs = f->correct_Rs;
+	a.A = A; a.rot_mats = rot_mats; a.joints = joints; a.poseoff = poseoff; a.shapeoff = shapeoff;
+	a.shape_blocks = shapeoff ? smpl_shape_blocks(f->V) : 0;
+	const int blocks = 1 + a.shape_blocks + (poseoff ? smpl_pose_blocks(f->V) : 0);
+	{ MOSS_STAGE(MOSS_STAGE_SMPL_FRAME, stream);
+		smpl_frame_forward_kernel<<<blocks, SMPL_THREADS, 0, stream>>>(a); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+int moss_smpl_frame_backward(void* stream_, const MossSmplFrame* f, const float* A, const float* joints,
+	const float* d_A, const float* d_poseoff, float* d_poses, float* d_correct_Rs)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!smpl_frame_valid(f) || !A || !joints || !d_poses || (d_poseoff && !f->posedirs) || !f->scratch ||
+		f->scratch_bytes < moss_smpl_frame_scratch_bytes(f->V) || ((uintptr_t)f->scratch & 15)) return MOSS_ERR_INVALID_ARGUMENT;
+	int dev = 0;                            // opt in to > 48 KB of dynamic shared memory (the attribute is per device)
+	MOSS_CUDA_TRY(cudaGetDevice(&dev));
+	if (dev >= 0 && dev < MAX_DEVICES && !g_smpl_attr_set[dev].load(std::memory_order_acquire)) {
+		MOSS_CUDA_TRY(cudaFuncSetAttribute(smpl_frame_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMPL_BWD_DYN_SMEM));
+		g_smpl_attr_set[dev].store(true, std::memory_order_release);
+	}
+	SmplFrameBwdArgs a;
+	a.V = f->V; a.posedirs = f->posedirs; a.parents = f->parents; a.poses = f->poses; a.correct_Rs = f->correct_Rs;
+	a.A = A; a.joints = joints; a.d_A = d_A; a.d_poseoff = d_poseoff; a.d_poses = d_poses; a.d_correct_Rs = d_correct_Rs;
+	a.ticket = (unsigned*)f->scratch; a.chain_dR = (float*)((char*)f->scratch + 16); a.partial = a.chain_dR + NJ * 9;
+	a.pose_blocks = d_poseoff ? smpl_bwd_blocks(f->V) : 0;
+	{ MOSS_STAGE(MOSS_STAGE_SMPL_FRAME_BWD, stream);
+		smpl_frame_backward_kernel<<<1 + a.pose_blocks, SMPL_THREADS, a.pose_blocks ? SMPL_BWD_DYN_SMEM : 0, stream>>>(a); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }

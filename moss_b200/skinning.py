@@ -14,9 +14,9 @@ becomes
 
 ``skin_and_covariance`` is ONE kernel forward and ONE backward through the C ABI (``moss_skin_forward`` /
 ``moss_skin_backward``, include/moss_splat.h); there is no torch fallback.  ``frame_tables`` is the 24-joint
-kinematic chain and the blend-shape offset tables (scene/gaussian_model.py:838-892, 965-1064) -- O(24) work per
-frame, kept as differentiable torch ops on the device (SURVEY.md section 8(f) rank 1, the next row to go native);
-its big-pose half is constant over a run and is cached by ``FrameCache``.
+kinematic chain and the blend-shape offset tables (scene/gaussian_model.py:838-892, 965-1064): ONE launch forward
+and ONE backward as well (``moss_smpl_frame_forward`` / ``moss_smpl_frame_backward``, csrc/smpl_frame.cuh; SURVEY.md
+section 8(f) rank 1); its big-pose half is constant over a run and is cached by ``FrameCache``.
 """
 import ctypes as C
 from typing import NamedTuple, Optional
@@ -46,51 +46,156 @@ class FrameTables(NamedTuple):
     Th: torch.Tensor           # [3]
 
 
-def batch_rodrigues(rot_vecs):
-    """scene/gaussian_model.py:1033-1064 ([N,3] -> [N,3,3]; the +1e-8 sits inside the norm as in the reference)."""
-    n = rot_vecs.shape[0]
-    angle = torch.norm(rot_vecs + 1e-8, dim=1, keepdim=True)
-    rot_dir = rot_vecs / angle
-    cos = torch.cos(angle)[:, None]
-    sin = torch.sin(angle)[:, None]
-    rx, ry, rz = torch.split(rot_dir, 1, dim=1)
-    zeros = torch.zeros((n, 1), dtype=rot_vecs.dtype, device=rot_vecs.device)
-    K = torch.cat([zeros, -rz, ry, rz, zeros, -rx, -ry, rx, zeros], dim=1).view(n, 3, 3)
-    ident = torch.eye(3, dtype=rot_vecs.dtype, device=rot_vecs.device)[None]
-    return ident + sin * K + (1 - cos) * torch.bmm(K, K)
+def _dev_f32(t, name):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (moss_b200 has no CPU path)")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32")
+    return t.contiguous()
 
 
-def _rigid_chain(rot_mats, joints, parents):
-    """scene/gaussian_model.py:965-995 for one frame: [24,3,3], [24,3] -> A [24,4,4]."""
-    nj = joints.shape[0]
-    plist = [int(p) for p in parents.tolist()]
-    rel = torch.cat([joints[:1], joints[1:] - joints[plist[1:]]], dim=0)
-    tm = torch.cat([rot_mats, rel[..., None]], dim=-1)
-    pad = torch.zeros((nj, 1, 4), dtype=rot_mats.dtype, device=rot_mats.device)
-    pad[..., 3] = 1
-    tm = torch.cat([tm, pad], dim=-2)
-    chain = [tm[0]]
-    for i in range(1, nj):
-        chain.append(chain[plist[i]] @ tm[i])
-    tr = torch.stack(chain, dim=0)
-    jh = torch.cat([joints, torch.zeros((nj, 1), dtype=joints.dtype, device=joints.device)], dim=-1)
-    relj = torch.sum(tr * jh[:, None], dim=2)
-    return torch.cat([tr[..., :3], (tr[..., 3] - relj)[..., None]], dim=-1)
+def _p(t):
+    return None if t is None else t.data_ptr()
 
 
-def _joint_transforms(smpl: Smpl, shapes, rot_mats):
-    """get_transform_params_torch (scene/gaussian_model.py:998-1031) for one frame."""
-    v_shaped = smpl.v_template + torch.sum(smpl.shapedirs[..., :shapes.shape[-1]] * shapes.reshape(1, 1, -1), dim=-1)
-    joints = smpl.J_regressor @ v_shaped
-    return _rigid_chain(rot_mats, joints, smpl.parents)
+_frame_scratch = {}     # (device index, stream handle) -> zero-initialised scratch of the frame kernels (self-cleaning)
+_parents_i32 = {}       # (data_ptr, version) -> (source tensor kept alive, int32 copy)
 
 
-def _pose_offsets(smpl: Smpl, rot_mats):
-    """scene/gaussian_model.py:849-856 / :872-888: [24,3,3] -> [V,3]."""
-    nv = smpl.posedirs.shape[0]
-    ident = torch.eye(3, dtype=rot_mats.dtype, device=rot_mats.device)
-    pf = (rot_mats[1:] - ident).reshape(1, -1)
-    return (pf @ smpl.posedirs.reshape(nv * 3, -1).t()).view(nv, 3)
+def _scratch_for(dev, stream, nbytes):
+    key = (dev.index, stream)
+    t = _frame_scratch.get(key)
+    if t is None or t.numel() < nbytes:
+        t = torch.zeros((nbytes,), dtype=torch.uint8, device=dev)
+        _frame_scratch[key] = t
+    return t
+
+
+def _parents32(parents):
+    if parents.dtype == torch.int32 and parents.is_contiguous():
+        return parents
+    key = (parents.data_ptr(), parents._version)
+    hit = _parents_i32.get(key)
+    if hit is None or hit[0] is not parents:
+        if len(_parents_i32) > 16:
+            _parents_i32.clear()
+        hit = (parents, parents.to(torch.int32).contiguous())
+        _parents_i32[key] = hit
+    return hit[1]
+
+
+_joint_tables = {}      # (data_ptr, version) of the three source tables -> (sources kept alive, J_template, J_shapedirs)
+
+
+def joint_tables(smpl):
+    """J_template [24,3] = J_regressor . v_template and J_shapedirs [24,3,S] = J_regressor . shapedirs: constants of an SMPL
+    model (``moss_smpl_joint_tables``, one launch, cached), so that the per-frame kernel regresses the joints
+    (scene/gaussian_model.py:1007, :1021) without a pass over the vertices."""
+    src = (smpl.v_template, smpl.shapedirs, smpl.J_regressor)
+    key = tuple((t.data_ptr(), t._version) for t in src)
+    hit = _joint_tables.get(key)
+    if hit is not None and all(a is b for a, b in zip(hit[0], src)):
+        return hit[1], hit[2]
+    for name, t in zip(("v_template", "shapedirs", "J_regressor"), src):
+        if not t.is_cuda:
+            raise RuntimeError(f"smpl.{name} must be a CUDA tensor (moss_b200 has no CPU path)")
+        if not (t.dtype == torch.float32 and t.is_contiguous() and t.device == src[0].device):
+            raise RuntimeError(f"smpl.{name} must be a contiguous float32 CUDA tensor on one device")
+    V, S = smpl.v_template.shape[0], smpl.shapedirs.shape[-1]
+    if smpl.J_regressor.shape != (24, V) or smpl.shapedirs.shape[:2] != (V, 3):
+        raise RuntimeError("SMPL table shapes do not match (v_template [V,3], shapedirs [V,3,S], J_regressor [24,V])")
+    dev = smpl.v_template.device
+    with torch.cuda.device(dev):
+        jt = torch.empty((24, 3), dtype=torch.float32, device=dev)
+        js = torch.empty((24, 3, S), dtype=torch.float32, device=dev)
+        st = _abi.load().moss_smpl_joint_tables(torch.cuda.current_stream(dev).cuda_stream, V, S, _p(smpl.v_template),
+                                                _p(smpl.shapedirs), _p(smpl.J_regressor), _p(jt), _p(js))
+    _abi.check(st, "moss_smpl_joint_tables")
+    torch.cuda.current_stream(dev).synchronize()      # once per model: later frames may run on any stream
+    if len(_joint_tables) > 8:
+        _joint_tables.clear()
+    _joint_tables[key] = (src, jt, js)
+    return jt, js
+
+
+def _fill_frame(smpl, poses, shapes, correct_Rs, scratch, parents, tables=None):
+    jt, js = tables if tables is not None else joint_tables(smpl)
+    f = _abi.MossSmplFrame()
+    f.V, f.n_shapes, f.shape_stride = smpl.v_template.shape[0], shapes.numel(), smpl.shapedirs.shape[-1]
+    f.shapedirs, f.posedirs, f.J_template, f.J_shapedirs = _p(smpl.shapedirs), _p(smpl.posedirs), _p(jt), _p(js)
+    f.parents, f.poses, f.shapes, f.correct_Rs = _p(parents), _p(poses), _p(shapes), _p(correct_Rs)
+    f.scratch, f.scratch_bytes = _p(scratch), (0 if scratch is None else scratch.numel())
+    return f
+
+
+class _SmplFrame(torch.autograd.Function):
+    """poses [72] (and correct_Rs [23,3,3]) -> A [24,4,4], pose_offsets [V,3], shape_offset [V,3]: ONE launch forward
+    (``moss_smpl_frame_forward``) and ONE backward (``moss_smpl_frame_backward``); shapes and the SMPL tables are
+    constants of a run.  Replaces scene/gaussian_model.py:855-861, 870-871, 878-893, 965-1064 for one frame."""
+
+    @staticmethod
+    def forward(ctx, poses, correct_Rs, shapes, smpl):
+        lib = _abi.load()
+        ctx.in_shapes = (tuple(poses.shape), None if correct_Rs is None else tuple(correct_Rs.shape))
+        poses = _dev_f32(poses.reshape(-1), "poses")
+        if poses.numel() != 72:
+            raise RuntimeError("poses must hold 24 axis-angle vectors (72 floats)")
+        dev = poses.device
+        shapes = _dev_f32(shapes.reshape(-1), "shapes")
+        if correct_Rs is not None:
+            correct_Rs = _dev_f32(correct_Rs.reshape(-1), "correct_Rs")
+            if correct_Rs.numel() != 23 * 9:
+                raise RuntimeError("correct_Rs must hold 23 3x3 matrices")
+        tables = joint_tables(smpl)             # validates v_template / shapedirs / J_regressor
+        t = smpl.posedirs
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.device == dev):
+            raise RuntimeError("smpl.posedirs must be a contiguous float32 CUDA tensor on the device of poses")
+        V = smpl.v_template.shape[0]
+        if shapes.numel() > smpl.shapedirs.shape[-1] or smpl.posedirs.numel() != V * 3 * 207:
+            raise RuntimeError("SMPL table shapes do not match (shapedirs [V,3,S] with S >= len(shapes), posedirs [V,3,207])")
+        parents = _parents32(smpl.parents)
+        with torch.cuda.device(dev):
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            out = torch.empty((24 * 16 + 24 * 3 + 6 * V,), dtype=torch.float32, device=dev)
+            A, joints = out[:384].view(24, 4, 4), out[384:456]
+            poseoff, shapeoff = out[456:456 + 3 * V].view(V, 3), out[456 + 3 * V:].view(V, 3)
+            f = _fill_frame(smpl, poses, shapes, correct_Rs, None, parents, tables)
+            st = lib.moss_smpl_frame_forward(stream, C.byref(f), _p(A), None, _p(joints), _p(poseoff), _p(shapeoff))
+        _abi.check(st, "moss_smpl_frame_forward")
+        ctx.smpl = smpl
+        ctx.has_cr = correct_Rs is not None
+        ctx.save_for_backward(poses, shapes, A, joints, *([correct_Rs] if correct_Rs is not None else []))
+        ctx.mark_non_differentiable(shapeoff)
+        return A, poseoff, shapeoff
+
+    @staticmethod
+    def backward(ctx, d_A, d_poseoff, _ds):
+        lib = _abi.load()
+        sv = ctx.saved_tensors
+        poses, shapes, A, joints = sv[:4]
+        correct_Rs = sv[4] if ctx.has_cr else None
+        smpl, dev = ctx.smpl, poses.device
+        V = smpl.v_template.shape[0]
+        d_A = _dev_f32(d_A, "grad A") if d_A is not None else None
+        d_poseoff = _dev_f32(d_poseoff, "grad pose_offsets") if d_poseoff is not None else None
+        with torch.cuda.device(dev):
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            scratch = _scratch_for(dev, stream, lib.moss_smpl_frame_scratch_bytes(V))
+            d_poses = torch.empty((72,), dtype=torch.float32, device=dev)
+            d_cr = torch.empty((23, 3, 3), dtype=torch.float32, device=dev) if (ctx.has_cr and ctx.needs_input_grad[1]) else None
+            f = _fill_frame(smpl, poses, shapes, correct_Rs, scratch, _parents32(smpl.parents))
+            st = lib.moss_smpl_frame_backward(stream, C.byref(f), _p(A), _p(joints), _p(d_A), _p(d_poseoff), _p(d_poses), _p(d_cr))
+        _abi.check(st, "moss_smpl_frame_backward")
+        return d_poses.view(ctx.in_shapes[0]), (None if d_cr is None else d_cr.view(ctx.in_shapes[1])), None, None
+
+
+def smpl_frame(smpl: Smpl, poses, shapes, correct_Rs=None):
+    """-> (A [24,4,4], pose_offsets [V,3], shape_offset [V,3]) of one frame; differentiable w.r.t. ``poses`` and
+    ``correct_Rs``.  The values get_transform_params_torch(...)[0] (scene/gaussian_model.py:998-1031) and the two
+    blend-shape tables of coarse_deform_c2source (:855-861 / :878-893, :870-871) hold before the per-Gaussian gather."""
+    return _SmplFrame.apply(poses, correct_Rs, shapes, smpl)
 
 
 class FrameCache:
@@ -107,8 +212,8 @@ class FrameCache:
         key = tuple((t.data_ptr(), t._version, tuple(t.shape)) for t in src)
         if self.key != key:
             with torch.no_grad():
-                rm = batch_rodrigues(t_params["poses"].reshape(-1, 3))
-                self.val = (_joint_transforms(smpl, t_params["shapes"], rm).contiguous(), _pose_offsets(smpl, rm).contiguous())
+                A, po, _ = smpl_frame(smpl, t_params["poses"], t_params["shapes"])
+            self.val = (A, po)
             self.key = key
             self.src = src
         return self.val
@@ -116,34 +221,16 @@ class FrameCache:
 
 def frame_tables(smpl: Smpl, params, t_params, correct_Rs=None, cache: Optional[FrameCache] = None) -> FrameTables:
     """Per-frame half of coarse_deform_c2source (scene/gaussian_model.py:838-892).  ``params`` / ``t_params`` are the
-    reference's ``smpl_param`` / ``big_pose_smpl_param`` dicts (poses [1,72], shapes [1,10], R [3,3], Th [1,3])."""
+    reference's ``smpl_param`` / ``big_pose_smpl_param`` dicts (poses [1,72], shapes [1,10], R [3,3], Th [1,3]).
+    Two launches without a cache (big pose, target pose), one with it; gradients flow to ``params['poses']`` and
+    ``correct_Rs`` through the native backward."""
     if cache is not None:
         A_big, po_big = cache.get(smpl, t_params)
     else:
-        rm_big = batch_rodrigues(t_params["poses"].reshape(-1, 3))
-        A_big, po_big = _joint_transforms(smpl, t_params["shapes"], rm_big), _pose_offsets(smpl, rm_big)
-    nsh = params["shapes"].shape[-1]
-    so = (smpl.shapedirs[..., :nsh] @ params["shapes"].reshape(-1, 1)).squeeze(-1)
-    rm = batch_rodrigues(params["poses"].reshape(-1, 3))
-    if correct_Rs is not None:
-        rm = torch.cat([rm[0:1], torch.matmul(rm[1:], correct_Rs.reshape(-1, 3, 3))], dim=0)
-    po = _pose_offsets(smpl, rm)
-    A = _joint_transforms(smpl, params["shapes"], rm)
+        with torch.no_grad():
+            A_big, po_big, _ = smpl_frame(smpl, t_params["poses"], t_params["shapes"])
+    A, po, so = smpl_frame(smpl, params["poses"], params["shapes"], correct_Rs)
     return FrameTables(A_big, A, po_big, so, po, params["R"].reshape(3, 3), params["Th"].reshape(-1))
-
-
-def _dev_f32(t, name):
-    if t is None:
-        return None
-    if not t.is_cuda:
-        raise RuntimeError(f"{name} must be a CUDA tensor (moss_b200 has no CPU path)")
-    if t.dtype != torch.float32:
-        raise RuntimeError(f"{name} must be float32")
-    return t.contiguous()
-
-
-def _p(t):
-    return None if t is None else t.data_ptr()
 
 
 def _fill_skin(xyz, vert_ids, weights, lbs_delta, A_big, A_tgt, po_big, so, po_tgt, R, Th, scaling, rotation, mod):

@@ -28,7 +28,7 @@ def test_header_symbols_exported(lib):
 
 
 def test_versions_and_strings(lib):
-    assert lib.moss_abi_version() == 9
+    assert lib.moss_abi_version() == 10
     assert lib.moss_error_string(0) == b"ok"
     assert b"binning" in lib.moss_error_string(_abi.MOSS_ERR_BINNING_OVERFLOW)
 
@@ -120,9 +120,10 @@ def test_adamw_entry_point_validates_without_a_gpu(lib):
         opt.step()                                             # no CPU path
 
 
-def test_skinning_host_tables_match_oracle_and_refuse_cpu_compute():
-    """frame_tables (host logic, torch) == the oracle's restatement of the reference; the per-Gaussian kernel has no
-    CPU path."""
+def test_skinning_refuses_cpu_compute_and_frame_abi_validates():
+    """Neither the per-Gaussian kernel nor the per-frame table kernel has a CPU path; argument validation of the frame
+    entry points happens before any launch."""
+    import ctypes as C
     from moss_b200 import skinning as K, synth
     from oracle import lbs_oracle as L
     from tests.lbs_cases import oracle_smpl
@@ -131,14 +132,18 @@ def test_skinning_host_tables_match_oracle_and_refuse_cpu_compute():
     smpl = K.Smpl(body.verts, body.shapedirs, body.posedirs.t().reshape(V, 3, 207).contiguous(), body.J_regressor,
                   body.weights, body.parents)
     fr = synth.frame_params(3)
-    cr = L.batch_rodrigues(0.05 * torch.randn(23, 3, generator=torch.Generator().manual_seed(1))).reshape(1, 23, 3, 3)
-    a = K.frame_tables(smpl, fr.params, fr.big_params, cr, cache=K.FrameCache())
-    b = L.frame_tables(oracle_smpl(body), fr.params, fr.big_params, cr)
-    for x, y in zip(a, b):
-        assert float((x - y.reshape(x.shape)).abs().max()) <= 2e-6 * max(1.0, float(y.abs().max()))
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        K.frame_tables(smpl, fr.params, fr.big_params)
+    ft = L.frame_tables(oracle_smpl(body), fr.params, fr.big_params)
     g = synth.gaussians(64, body)
     with pytest.raises(RuntimeError, match="no CPU path"):
-        K.skin_and_covariance(g.xyz, g.vert_ids, body.weights, a, g.scales, g.rotations)
+        K.skin_and_covariance(g.xyz, g.vert_ids, body.weights, K.FrameTables(*ft), g.scales, g.rotations)
+    lib = _abi.load()
+    assert lib.moss_smpl_frame_scratch_bytes(6890) == 16 + 4 * (24 * 9 + 216 * 208)
+    f = _abi.MossSmplFrame()
+    assert lib.moss_smpl_frame_forward(None, C.byref(f), None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    assert lib.moss_smpl_frame_backward(None, C.byref(f), None, None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    assert lib.moss_smpl_joint_tables(None, 0, 10, None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
 
 
 def test_api_validation_and_no_cpu_fallback():

@@ -1,10 +1,13 @@
 """CPU: the LBS / covariance oracle restatement reproduces what the REAL reference functions computed
 (tests/golden/lbs_*.npz, made by tests/golden/make_lbs_golden.py in the build container)."""
+import os
+
+import numpy as np
 import pytest
 import torch
 
 from oracle import lbs_oracle as L
-from tests.lbs_cases import LBS_CASES, load_case
+from tests.lbs_cases import GOLD, LBS_CASES, load_case
 
 TOL = 2e-6      # fp32; both sides are the same torch ops up to matmul association
 
@@ -45,3 +48,34 @@ def test_backward_matches_reference(name):
     for got, key in zip(g, ["d_xyz", "d_scaling", "d_rotation", "d_lbs_delta"]):
         rel = float((got - d[key]).norm() / d[key].norm())
         assert rel < 1e-4, (key, rel)
+
+
+FRAME_CASES = ["plain", "correct", "shapes6"]
+
+
+def load_frame_case(name):
+    z = np.load(os.path.join(GOLD, f"smpl_frame_{name}.npz"))
+    return {k: torch.from_numpy(np.asarray(z[k])) if getattr(z[k], "ndim", 0) > 0 else z[k].item() for k in z.files}
+
+
+@pytest.mark.parametrize("name", FRAME_CASES)
+def test_oracle_frame_tables_match_reference_golden(name):
+    """oracle/lbs_oracle.py's per-frame tables (and their autograd gradients w.r.t. poses / correct_Rs) against the real
+    reference run by tests/golden/make_lbs_golden.py::make_frame_case."""
+    from oracle import lbs_oracle as L
+    from moss_b200 import synth
+    from tests.lbs_cases import oracle_smpl
+    d = load_frame_case(name)
+    body = synth.body()
+    fr = synth.frame_params(int(d["seed"]))
+    poses = d["poses"].clone().requires_grad_(True)
+    cr = d["correct_Rs"].reshape(1, 23, 3, 3).clone().requires_grad_(True) if "correct_Rs" in d else None
+    params = dict(fr.params, poses=poses, shapes=d["shapes"])
+    ft = L.frame_tables(oracle_smpl(body), params, fr.big_params, cr)
+    for got, key in ((ft.A_tgt, "A"), (ft.poseoff_tgt, "pose_offsets"), (ft.shapeoff, "shape_offset")):
+        assert float((got.detach() - d[key]).abs().max()) <= 2e-6 * max(1.0, float(d[key].abs().max())), key
+    leaves = [poses] + ([cr] if cr is not None else [])
+    grads = torch.autograd.grad([ft.A_tgt, ft.poseoff_tgt], leaves, [d["g_A"], d["g_pose_offsets"]])
+    assert float((grads[0] - d["d_poses"]).norm() / d["d_poses"].norm()) < 1e-5
+    if cr is not None:
+        assert float((grads[1][0] - d["d_correct_Rs"]).norm() / d["d_correct_Rs"].norm()) < 1e-5

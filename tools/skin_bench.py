@@ -13,7 +13,76 @@ from tests.lbs_cases import oracle_smpl
 dev = torch.device("cuda:0")
 lib = _abi.load()
 body = synth.body()
-peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json"))) if os.path.exists("MEASURED_PEAKS.json") else {"hbm_gbs": 6650.0}
+_pk = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")
+peaks = json.load(open(_pk)) if os.path.exists(_pk) else {"hbm_gbs": 6650.0}
+
+
+def _frame_tables_line():
+    """Per-frame SMPL tables: ours = ONE launch forward + ONE backward; reference = the
+    reference's python ops (oracle restatement) as torch kernels on the same GPU with autograd."""
+    V = body.verts.shape[0]
+    smpl = K.Smpl(body.verts.to(dev), body.shapedirs.to(dev), body.posedirs.t().reshape(V, 3, 207).contiguous().to(dev),
+                  body.J_regressor.to(dev), body.weights.to(dev), body.parents.to(dev))
+    osm = L.Smpl(*[t.to(dev) for t in oracle_smpl(body)])
+    fr = synth.frame_params(7)
+    params = {k: v.to(dev) for k, v in fr.params.items()}
+    big = {k: v.to(dev) for k, v in fr.big_params.items()}
+    cr = L.batch_rodrigues(0.05 * torch.randn(23, 3)).reshape(1, 23, 3, 3).to(dev).requires_grad_(True)
+    params["poses"].requires_grad_(True)
+    gA, gpo = torch.randn(24, 4, 4, device=dev), torch.randn(V, 3, device=dev)
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+    cache = K.FrameCache()
+
+    def ours():
+        params["poses"].grad = None; cr.grad = None
+        ft = K.frame_tables(smpl, params, big, cr, cache=cache)
+        torch.autograd.backward([ft.A_tgt, ft.poseoff_tgt], [gA, gpo])
+
+    def ref():
+        params["poses"].grad = None; cr.grad = None
+        ft = L.frame_tables(osm, params, big, cr)       # the reference recomputes the big-pose half every render too
+        torch.autograd.backward([ft.A_tgt, ft.poseoff_tgt], [gA, gpo])
+
+    def gpu_time(step, n, cold):
+        for _ in range(5): step()
+        torch.cuda.synchronize()
+        tot = 0.0
+        for _ in range(n):
+            if cold: flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); step(); e1.record(); torch.cuda.synchronize()
+            tot += e0.elapsed_time(e1)
+        return tot / n
+    out = {"metric": "per-frame SMPL tables fwd+bwd", "vertices": V}
+    for cold in (True, False):
+        tag = "cold_l2" if cold else "warm_l2"
+        t_ours = gpu_time(ours, 100, cold)
+        lib.moss_profile_enable(1)
+        for _ in range(50):
+            if cold: flush.zero_()
+            ours()
+        torch.cuda.synchronize()
+        prof = _abi.profile_read(); lib.moss_profile_enable(0)
+        kf = prof["smpl_frame_forward"][0] / prof["smpl_frame_forward"][1] * 1e3
+        kb = prof["smpl_frame_backward"][0] / prof["smpl_frame_backward"][1] * 1e3
+        # algorithmic bytes: posedirs 207*3V*4 (both ways), forward also shapedirs 3V*10*4 + J_regressor 24*V*4 + v_template,
+        # writes 2 x 3V*4; backward reads d_poseoff 3V*4
+        bytes_f = 4 * (207 * 3 * V + 30 * V + 24 * V + 3 * V + 6 * V)
+        bytes_b = 4 * (207 * 3 * V + 3 * V)
+        out[tag] = {"ours_ms": round(t_ours, 4), "kernel_us": {"smpl_frame_forward": round(kf, 2), "smpl_frame_backward": round(kb, 2)},
+                    "launches_per_step": (prof["smpl_frame_forward"][1] + prof["smpl_frame_backward"][1]) / 50,
+                    "roofline": {"bound": "hbm" if cold else "l2", "kernel": "smpl_frame_forward", "algorithmic_bytes": bytes_f,
+                                 "achieved": round(bytes_f / (kf * 1e-6) / 1e9, 1), "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                 "frac": round(bytes_f / (kf * 1e-6) / 1e9 / peaks["hbm_gbs"], 4)},
+                    "roofline_backward": {"algorithmic_bytes": bytes_b, "achieved": round(bytes_b / (kb * 1e-6) / 1e9, 1),
+                                          "frac": round(bytes_b / (kb * 1e-6) / 1e9 / peaks["hbm_gbs"], 4)}}
+    t_ref = gpu_time(ref, 30, False)
+    out["reference_torch_ops_on_gpu_ms"] = round(t_ref, 4)
+    out["speedup_vs_reference_python_path"] = round(t_ref / out["warm_l2"]["ours_ms"], 1)
+    print(json.dumps(out))
+
+
+_frame_tables_line()
 for P in [int(a) for a in sys.argv[1:]] or [20000, 100000]:
     g = synth.gaussians(P, body, seed=synth.SEED + 5)
     fr = synth.frame_params(7)
