@@ -238,6 +238,36 @@ int moss_smpl_frame_forward(void* stream, const MossSmplFrame* frame, float* A, 
 int moss_smpl_frame_backward(void* stream, const MossSmplFrame* frame, const float* A, const float* joints,
                              const float* d_A, const float* d_poseoff, float* d_poses, float* d_correct_Rs);
 
+/* Image-space losses fused behind the rasterizer.  Replaces, per iteration, the masked
+ * L1 / L2 terms, the SSIM and the S3IM loss of train_ZJU.py:107-128 (utils/loss_utils.py:16-87: l1_loss, l2_loss, ssim
+ * with an 11x11 sigma-1.5 window, s3im_fun) AND their autograd backward: ONE launch writes the loss values and
+ * dL/dimage, dL/dalpha -- the upstream gradients moss_rasterize_backward() takes -- for
+ *     loss = w_l1 * Ll1 + w_mask * mask_loss + w_ssim * (1 - ssim) + w_s3im * s3im_loss   (1, 0.5, 0.2, 0.3 at :131).
+ * LPIPS (a VGG network) and the pose NLL stay on the caller's side and add their own gradient. */
+typedef struct MossImageLoss {
+    int W, H;
+    const float* image;         /* [3,H,W] render */
+    const float* alpha;         /* [H,W] render_alpha, or NULL (no mask loss) */
+    const float* gt_image;      /* [3,H,W] viewpoint_cam.original_image */
+    const float* bkgd_mask;     /* [H,W] float, or NULL (no mask loss) */
+    const float* bound_mask;    /* [H,W] float; pixels equal to 1 enter Ll1 / mask_loss (:111-112); NULL = all pixels */
+    const int*   rect;          /* DEVICE int[5]: crop x, y, w, h (cv2.boundingRect of bound_mask, :115) and the number of
+                                   bound_mask == 1 pixels -- what moss_mask_bounds() writes; constant per camera */
+    float w_l1, w_mask, w_ssim, w_s3im;     /* a zero weight skips that term's work */
+    void* scratch;              /* >= moss_image_losses_scratch_bytes(W,H), zeroed ONCE by the caller (self-cleaning) */
+    size_t scratch_bytes;
+} MossImageLoss;
+size_t moss_image_losses_scratch_bytes(int W, int H);
+size_t moss_sizeof_image_loss(void);
+/* losses: DEVICE float[5] = Ll1, mask_loss, ssim, s3im_loss, weighted total.  dL_dimage [3,H,W] and dL_dalpha [H,W] are
+ * fully written (zero where no term reaches), either may be NULL. */
+int moss_image_losses(void* stream, const MossImageLoss* loss, float* losses, float* dL_dimage, float* dL_dalpha);
+/* out: DEVICE int[8]; out[0..4] = x, y, w, h of the bounding rectangle of the non-zero pixels of mask (as
+ * cv2.boundingRect(mask.astype(np.uint8)), (0,0,0,0) if none) and the number of pixels equal to 1; out[5..7] scratch. */
+int moss_mask_bounds(void* stream, int W, int H, const float* mask, int* out);
+/* a[0..na) and b[0..nb) *= *scale_dev unless it is exactly 1: the autograd backward of a loss node, without a host read. */
+int moss_scale_gradients(void* stream, const float* scale_dev, float* a, size_t na, float* b, size_t nb);
+
 /* Densification statistics of one iteration, for the Gaussians with radii > 0 (the reference's visibility_filter,
  * gaussian_renderer/__init__.py:128): max_radii2D = max(max_radii2D, radii) (train_ZJU.py:173), xyz_gradient_accum +=
  * |dL_dmean2D[:, :2]|, denom += 1 (GaussianModel.add_densification_stats, scene/gaussian_model.py:816-818).  All
@@ -368,7 +398,8 @@ long long moss_export_state_batch(void* stream, const MossScene* scene, int V, i
 #define MOSS_STAGE_PUSH_GATHER     15
 #define MOSS_STAGE_SMPL_FRAME      16
 #define MOSS_STAGE_SMPL_FRAME_BWD  17
-#define MOSS_STAGE_COUNT           18
+#define MOSS_STAGE_IMAGE_LOSSES    18
+#define MOSS_STAGE_COUNT           19
 unsigned long long moss_kernel_launches(void);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);

@@ -40,8 +40,9 @@ SYMBOLS = [
     "moss_export_state_batch", "moss_push_slice_floats", "moss_sizeof_push", "moss_rasterize_backward_push", "moss_push_allreduce",
     "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
     "moss_smpl_frame_scratch_bytes", "moss_sizeof_smpl_frame", "moss_smpl_frame_forward", "moss_smpl_frame_backward", "moss_smpl_joint_tables",
+    "moss_image_losses_scratch_bytes", "moss_sizeof_image_loss", "moss_image_losses", "moss_mask_bounds", "moss_scale_gradients",
 ]
-STAGE_COUNT = 18
+STAGE_COUNT = 19
 
 
 class MossScene(C.Structure):
@@ -92,6 +93,16 @@ class MossSmplFrame(C.Structure):
         ("V", C.c_int), ("n_shapes", C.c_int), ("shape_stride", C.c_int),
         ("shapedirs", C.c_void_p), ("posedirs", C.c_void_p), ("J_template", C.c_void_p), ("J_shapedirs", C.c_void_p),
         ("parents", C.c_void_p), ("poses", C.c_void_p), ("shapes", C.c_void_p), ("correct_Rs", C.c_void_p),
+        ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+    ]
+
+
+class MossImageLoss(C.Structure):
+    _fields_ = [
+        ("W", C.c_int), ("H", C.c_int),
+        ("image", C.c_void_p), ("alpha", C.c_void_p), ("gt_image", C.c_void_p), ("bkgd_mask", C.c_void_p),
+        ("bound_mask", C.c_void_p), ("rect", C.c_void_p),
+        ("w_l1", C.c_float), ("w_mask", C.c_float), ("w_ssim", C.c_float), ("w_s3im", C.c_float),
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
     ]
 
@@ -198,6 +209,17 @@ def load():
     lib.moss_smpl_joint_tables.argtypes = [vp, C.c_int, C.c_int] + [vp] * 5
     lib.moss_smpl_frame_backward.restype = C.c_int
     lib.moss_smpl_frame_backward.argtypes = [vp, C.POINTER(MossSmplFrame)] + [vp] * 6
+    lib.moss_image_losses_scratch_bytes.restype = C.c_size_t
+    lib.moss_image_losses_scratch_bytes.argtypes = [C.c_int, C.c_int]
+    lib.moss_sizeof_image_loss.restype = C.c_size_t
+    lib.moss_image_losses.restype = C.c_int
+    lib.moss_image_losses.argtypes = [vp, C.POINTER(MossImageLoss), vp, vp, vp]
+    lib.moss_mask_bounds.restype = C.c_int
+    lib.moss_mask_bounds.argtypes = [vp, C.c_int, C.c_int, vp, vp]
+    lib.moss_scale_gradients.restype = C.c_int
+    lib.moss_scale_gradients.argtypes = [vp, vp, vp, C.c_size_t, vp, C.c_size_t]
+    if lib.moss_sizeof_image_loss() != C.sizeof(MossImageLoss):
+        raise RuntimeError("moss_b200: MossImageLoss layout mismatch between _abi.py and the library; rebuild")
     if lib.moss_sizeof_smpl_frame() != C.sizeof(MossSmplFrame):
         raise RuntimeError("moss_b200: MossSmplFrame layout mismatch between _abi.py and the library; rebuild")
     if lib.moss_sizeof_adam_group() != C.sizeof(MossAdamGroup):

@@ -27,6 +27,7 @@
 #include "peer_reduce.cuh"
 #include "push_exchange.cuh"
 #include "smpl_frame.cuh"
+#include "loss.cuh"
 
 using namespace moss;
 
@@ -152,6 +153,7 @@ struct SlotLease {             // releases the slot on every return path of the 
 // cudaFuncSetAttribute is per device: remember where the sort kernel's dynamic shared memory was already raised
 std::atomic<bool> g_sort_attr_set[MAX_DEVICES];
 std::atomic<bool> g_smpl_attr_set[MAX_DEVICES];
+std::atomic<bool> g_loss_attr_set[MAX_DEVICES];
 
 inline bool scene_valid(const MossScene* sc, bool own_camera = true)
 {
@@ -266,7 +268,7 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 const char* moss_stage_name(int stage)
 {
 	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step", "sum_views", "push_gather", "smpl_frame_forward", "smpl_frame_backward"};
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step", "sum_views", "push_gather", "smpl_frame_forward", "smpl_frame_backward", "image_losses"};
 	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
@@ -859,6 +861,84 @@ int moss_smpl_frame_backward(void* stream_, const MossSmplFrame* f, const float*
 	a.pose_blocks = d_poseoff ? smpl_bwd_blocks(f->V) : 0;
 	{ MOSS_STAGE(MOSS_STAGE_SMPL_FRAME_BWD, stream);
 		smpl_frame_backward_kernel<<<1 + a.pose_blocks, SMPL_THREADS, a.pose_blocks ? SMPL_BWD_DYN_SMEM : 0, stream>>>(a); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+// ---- image-space losses ------------------------------------------------------------------------------------------------
+static int loss_blocks(int W, int H) { return ((W + LOSS_T - 1) / LOSS_T) * ((H + LOSS_T - 1) / LOSS_T); }
+size_t moss_image_losses_scratch_bytes(int W, int H)
+{
+	if (W < 1 || H < 1) return 16;
+	return 16 + (size_t)loss_blocks(W, H) * 4 * sizeof(float);
+}
+size_t moss_sizeof_image_loss(void) { return sizeof(MossImageLoss); }
+
+// The 11-tap window as utils/loss_utils.py:47-49 builds it: float32 of exp(-(x-5)^2 / (2 * 1.5^2)), divided by their
+// float32 sum.  S3IM taps of replica r on (x-1, x, x+1): the window entries that fall on each source pixel when every
+// pixel is repeated ten times (stretched position 10x + r + d, d = -5..5).
+static void loss_window(float* g, float (*s3)[3])
+{
+	float sum = 0.f;
+	for (int x = 0; x < LOSS_WIN; x++) { g[x] = (float)exp(-(double)((x - LOSS_R) * (x - LOSS_R)) / (2.0 * 1.5 * 1.5)); sum += g[x]; }
+	for (int x = 0; x < LOSS_WIN; x++) g[x] /= sum;
+	for (int r = 0; r < LOSS_S3_REP; r++) {
+		s3[r][0] = s3[r][1] = s3[r][2] = 0.f;
+		for (int d = -LOSS_R; d <= LOSS_R; d++) {
+			const int pos = r + d;
+			s3[r][pos < 0 ? 0 : (pos < LOSS_S3_REP ? 1 : 2)] += g[d + LOSS_R];
+		}
+	}
+}
+
+int moss_image_losses(void* stream_, const MossImageLoss* k, float* losses, float* dL_dimage, float* dL_dalpha)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!k || k->W < 1 || k->H < 1 || !k->image || !k->gt_image || !k->rect || !losses || !k->scratch ||
+		k->scratch_bytes < moss_image_losses_scratch_bytes(k->W, k->H) || ((uintptr_t)k->scratch & 15)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (k->w_mask != 0.f && (!k->alpha || !k->bkgd_mask)) return MOSS_ERR_INVALID_ARGUMENT;
+	int dev = 0;                            // opt in to > 48 KB of dynamic shared memory (the attribute is per device)
+	MOSS_CUDA_TRY(cudaGetDevice(&dev));
+	if (dev >= 0 && dev < MAX_DEVICES && !g_loss_attr_set[dev].load(std::memory_order_acquire)) {
+		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
+		g_loss_attr_set[dev].store(true, std::memory_order_release);
+	}
+	LossArgs a;
+	a.W = k->W; a.H = k->H; a.image = k->image; a.alpha = k->alpha; a.gt = k->gt_image; a.bkgd = k->bkgd_mask; a.bound = k->bound_mask;
+	a.rect = k->rect; a.w_l1 = k->w_l1; a.w_mask = k->w_mask; a.w_ssim = k->w_ssim; a.w_s3im = k->w_s3im;
+	loss_window(a.g, a.s3);
+	a.dL_dimage = dL_dimage; a.dL_dalpha = dL_dalpha; a.losses = losses;
+	a.ticket = (unsigned*)k->scratch; a.partial = (float*)((char*)k->scratch + 16);
+	const dim3 grid((k->W + LOSS_T - 1) / LOSS_T, (k->H + LOSS_T - 1) / LOSS_T);
+	{ MOSS_STAGE(MOSS_STAGE_IMAGE_LOSSES, stream);
+		image_losses_kernel<<<grid, LOSS_THREADS, LOSS_DYN_SMEM, stream>>>(a); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+int moss_mask_bounds(void* stream_, int W, int H, const float* mask, int* out)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (W < 1 || H < 1 || !mask || !out) return MOSS_ERR_INVALID_ARGUMENT;
+	MOSS_CUDA_TRY(cudaMemsetAsync(out, 0x7f, 2 * sizeof(int), stream));
+	MOSS_CUDA_TRY(cudaMemsetAsync(out + 2, 0x80, 2 * sizeof(int), stream));
+	MOSS_CUDA_TRY(cudaMemsetAsync(out + 4, 0, 4 * sizeof(int), stream));
+	const size_t N = (size_t)W * H;
+	const int blocks = (int)std::min<size_t>((N + 255) / 256, 148 * 8);
+	{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
+		mask_bounds_kernel<<<blocks, 256, 0, stream>>>(W, H, mask, out); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+int moss_scale_gradients(void* stream_, const float* scale_dev, float* a, size_t na, float* b, size_t nb)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!scale_dev || (na && !a) || (nb && !b)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (na + nb == 0) return MOSS_OK;
+	const int blocks = (int)std::min<size_t>((na + nb + 255) / 256, 148 * 8);
+	{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
+		scale_inplace_kernel<<<blocks, 256, 0, stream>>>(scale_dev, a, na, b, nb); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }
