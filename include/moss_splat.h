@@ -197,6 +197,28 @@ int moss_skin_backward(void* stream, const MossSkin* skin, const float* g_means3
                        float* d_A_tgt, float* d_poseoff_tgt);
 size_t moss_sizeof_skin(void);
 
+/* Fused skin + rasterize (north_star subsystem 1): MOSS's one-view-per-iteration loop,
+ * gaussian_renderer/__init__.py:57-93 (coarse_deform_c2source + get_covariance) feeding the rasterizer's preprocess
+ * (DGR/cuda_rasterizer/forward.cu:155-256), with the skinned centre and the transformed covariance held in registers of
+ * ONE per-Gaussian kernel each way: means3D and cov3D_precomp (36 B per Gaussian, written and read back in the two-call
+ * form, both directions) never touch HBM, and one launch disappears from the forward and from the backward.
+ * `scene` carries the camera, colours (shs / colors_precomp), opacities and the workspaces; its means3D, scales, rotations
+ * and cov3D_precomp must be NULL.  `skin` as for moss_skin_forward() with scaling and rotation present, skin->P == scene->P.
+ * The remaining arguments are those of moss_rasterize_forward() plus two optional per-Gaussian outputs: means3D [P,3]
+ * (the skinned centres) and transforms [P,9] (render()'s "transforms"); NULL skips the store. */
+int moss_skin_rasterize_forward(void* stream, const MossScene* scene, const MossSkin* skin, unsigned flags,
+                                float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered,
+                                float* means3D, float* transforms);
+/* Backward of the fused call: the rasterizer's dL/dmeans3D and dL/dcov3D stay in registers and flow straight into the
+ * skinning backward.  Image-side arguments and dL_dmean2D / dL_dconic / dL_dopacity / dL_dcolor / dL_dsh as for
+ * moss_rasterize_backward(); front-end gradients as for moss_skin_backward() (d_xyz, d_scaling, d_rotation fully written;
+ * d_lbs_delta, d_A_tgt, d_poseoff_tgt optional, the last two cleared by this call). */
+int moss_skin_rasterize_backward(void* stream, const MossScene* scene, const MossSkin* skin, unsigned flags, const int* radii,
+                                 const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+                                 float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_dsh,
+                                 float* d_xyz, float* d_scaling, float* d_rotation, float* d_lbs_delta,
+                                 float* d_A_tgt, float* d_poseoff_tgt);
+
 /* Per-frame SMPL tables: what render() recomputes for every frame before it touches a
  * Gaussian, as ONE launch forward and ONE backward instead of ~60 torch launches and two Python loops over the joints.
  * Replaces batch_rodrigues (scene/gaussian_model.py:1033-1064), the optional pose correction rot[1:] @ correct_Rs

@@ -9,5 +9,6 @@ from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer, rast
                          add_densification_stats)
 
 from . import skinning  # noqa: F401,E402  (fused LBS + covariance front end: skinning.skin_and_covariance)
+from . import losses, fused  # noqa: F401,E402  (image losses behind the rasterizer; fused skin + rasterize)
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "rasterize_gaussians"]

@@ -39,7 +39,7 @@ SYMBOLS = [
     "moss_batch_grad_workspace_bytes", "moss_rasterize_forward_batch", "moss_rasterize_backward_batch", "moss_sizeof_view",
     "moss_export_state_batch", "moss_push_slice_floats", "moss_sizeof_push", "moss_rasterize_backward_push", "moss_push_allreduce",
     "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
-    "moss_smpl_frame_scratch_bytes", "moss_sizeof_smpl_frame", "moss_smpl_frame_forward", "moss_smpl_frame_backward", "moss_smpl_joint_tables",
+    "moss_smpl_frame_scratch_bytes", "moss_sizeof_smpl_frame", "moss_smpl_frame_forward", "moss_smpl_frame_backward", "moss_smpl_joint_tables", "moss_skin_rasterize_forward", "moss_skin_rasterize_backward",
     "moss_image_losses_scratch_bytes", "moss_sizeof_image_loss", "moss_image_losses", "moss_mask_bounds", "moss_scale_gradients",
 ]
 STAGE_COUNT = 19
@@ -205,6 +205,10 @@ def load():
     lib.moss_sizeof_smpl_frame.restype = C.c_size_t
     lib.moss_smpl_frame_forward.restype = C.c_int
     lib.moss_smpl_frame_forward.argtypes = [vp, C.POINTER(MossSmplFrame)] + [vp] * 5
+    lib.moss_skin_rasterize_forward.restype = C.c_int
+    lib.moss_skin_rasterize_forward.argtypes = [vp, C.POINTER(MossScene), C.POINTER(MossSkin), C.c_uint, vp, vp, vp, vp, C.POINTER(C.c_int), vp, vp]
+    lib.moss_skin_rasterize_backward.restype = C.c_int
+    lib.moss_skin_rasterize_backward.argtypes = [vp, C.POINTER(MossScene), C.POINTER(MossSkin), C.c_uint, vp] + [vp] * 14
     lib.moss_smpl_joint_tables.restype = C.c_int
     lib.moss_smpl_joint_tables.argtypes = [vp, C.c_int, C.c_int] + [vp] * 5
     lib.moss_smpl_frame_backward.restype = C.c_int

@@ -155,17 +155,42 @@ std::atomic<bool> g_sort_attr_set[MAX_DEVICES];
 std::atomic<bool> g_smpl_attr_set[MAX_DEVICES];
 std::atomic<bool> g_loss_attr_set[MAX_DEVICES];
 
-inline bool scene_valid(const MossScene* sc, bool own_camera = true)
+static inline bool skin_valid(const MossSkin* k)
+{
+	if (!k || k->P < 0 || k->V <= 0) return false;
+	if (k->P == 0) return true;
+	if (!k->xyz || !k->vert_ids || !k->weights || !k->A_big || !k->A_tgt || !k->Rg || !k->Th) return false;
+	if ((k->scaling != nullptr) != (k->rotation != nullptr)) return false;
+	if (((uintptr_t)k->weights & 15) || ((uintptr_t)k->lbs_delta & 15)) return false;
+	return true;
+}
+static inline SkinArgs make_skin(const MossSkin* k)
+{
+	SkinArgs a;
+	a.P = k->P; a.xyz = k->xyz; a.vert_ids = k->vert_ids; a.weights = k->weights; a.lbs_delta = k->lbs_delta;
+	a.A_big = k->A_big; a.A_tgt = k->A_tgt; a.poseoff_big = k->poseoff_big; a.shapeoff = k->shapeoff;
+	a.poseoff_tgt = k->poseoff_tgt; a.Rg = k->Rg; a.Th = k->Th; a.scaling = k->scaling; a.rotation = k->rotation;
+	a.scale_modifier = k->scale_modifier;
+	return a;
+}
+inline bool scene_valid(const MossScene* sc, bool own_camera = true, const MossSkin* skin = nullptr)
 {
 	if (!sc || sc->P < 0 || sc->W <= 0 || sc->H <= 0) return false;
 	if (own_camera && !sc->bg) return false;
 	if (sc->P == 0) return true;
-	if (!sc->means3D || !sc->opacities) return false;
+	if (!sc->opacities) return false;
 	if (own_camera && (!sc->viewmatrix || !sc->projmatrix)) return false;
 	if ((sc->shs != nullptr) == (sc->colors_precomp != nullptr)) return false;
-	const bool sr = (sc->scales != nullptr) && (sc->rotations != nullptr);
-	if (sr == (sc->cov3D_precomp != nullptr)) return false;
-	if (!sr && (sc->scales || sc->rotations)) return false;
+	if (skin) {
+		// fused skin + preprocess: position and covariance come from the skinning inputs
+		if (sc->means3D || sc->scales || sc->rotations || sc->cov3D_precomp) return false;
+		if (!skin_valid(skin) || skin->P != sc->P || !skin->scaling) return false;
+	} else {
+		if (!sc->means3D) return false;
+		const bool sr = (sc->scales != nullptr) && (sc->rotations != nullptr);
+		if (sr == (sc->cov3D_precomp != nullptr)) return false;
+		if (!sr && (sc->scales || sc->rotations)) return false;
+	}
 	if (sc->shs && ((own_camera && !sc->campos) || sc->D < 0 || sc->D > 3 || sc->M < (sc->D + 1) * (sc->D + 1))) return false;
 	if (((sc->W + TILE_X - 1) / TILE_X) > 65535 || ((sc->H + TILE_Y - 1) / TILE_Y) > 65535) return false;
 	return true;
@@ -370,7 +395,7 @@ int make_gather(const MossPush* push, PushCfg* pc, GatherArgs* ga, unsigned* gat
 	ga->err = push->error_word_dev;
 	ga->numel = pc->numel; ga->S = pc->S; ga->rank = push->rank; ga->world = push->world;
 	// every rank derives the same grid from (numel, world, pad size): the flag slots are indexed by it
-	size_t blocks = (S / 4 + (size_t)GATHER_THREADS * GATHER_ILP - 1) / ((size_t)GATHER_THREADS * GATHER_ILP);
+	size_t blocks = (S / 4 + (size_t)GATHER_THREADS - 1) / (size_t)GATHER_THREADS;      // one float4 per thread and owner, if the pads allow
 	const size_t pad_blocks = push->signal_pad_bytes / (sizeof(uint32_t) * 2 * (size_t)push->world);
 	blocks = std::min(blocks, std::min(pad_blocks, (size_t)PEER_MAX_BLOCKS));
 	*gather_blocks = (unsigned)std::max<size_t>(blocks, 1);
@@ -378,9 +403,11 @@ int make_gather(const MossPush* push, PushCfg* pc, GatherArgs* ga, unsigned* gat
 }
 
 int forward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossView* views, unsigned flags,
-	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
+	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered,
+	const MossSkin* skin = nullptr, float* sk_means3D = nullptr, float* sk_transforms = nullptr)
 {
-	if (!scene_valid(sc, views == nullptr) || !out_color || !out_depth || !out_alpha) return MOSS_ERR_INVALID_ARGUMENT;
+	if (!scene_valid(sc, views == nullptr, skin) || !out_color || !out_depth || !out_alpha) return MOSS_ERR_INVALID_ARGUMENT;
+	if (skin && V != 1) return MOSS_ERR_INVALID_ARGUMENT;
 	if (sc->P > 0 && !radii) return MOSS_ERR_INVALID_ARGUMENT;
 	if ((unsigned long long)sc->P * (unsigned long long)V >= 0xffffffffull) return MOSS_ERR_INVALID_ARGUMENT;   // id' = v*P + i is 32 bits
 	if (num_rendered) *num_rendered = (flags & MOSS_FLAG_ASYNC) ? -1 : 0;
@@ -420,9 +447,17 @@ int forward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossView
 	if (!(flags & MOSS_FLAG_REBIN)) {
 		MOSS_CUDA_TRY(cudaMemsetAsync(im.tile_count, 0, ((size_t)TV * TILE_SUB + VIEW_SYNC_WORDS) * sizeof(uint32_t), stream));
 		{ MOSS_STAGE(MOSS_STAGE_PREPROCESS, stream);
-		preprocess_forward_kernel<<<pre_grid, PRE_THREADS, 0, stream>>>(
-			vb, sc->means3D, sc->shs, sc->colors_precomp, sc->opacities, sc->scales, sc->rotations,
-			sc->cov3D_precomp, sc->prefiltered, g, im.tile_count, radii); }
+		SkinFused sk;
+		memset(&sk, 0, sizeof(sk));
+		if (skin) {
+			sk.a = make_skin(skin); sk.means3D = sk_means3D; sk.transforms = sk_transforms;
+			preprocess_forward_kernel<true><<<pre_grid, PRE_THREADS, 0, stream>>>(
+				vb, nullptr, sc->shs, sc->colors_precomp, sc->opacities, nullptr, nullptr, nullptr, sc->prefiltered, g, im.tile_count, radii, sk);
+		} else {
+			preprocess_forward_kernel<false><<<pre_grid, PRE_THREADS, 0, stream>>>(
+				vb, sc->means3D, sc->shs, sc->colors_precomp, sc->opacities, sc->scales, sc->rotations,
+				sc->cov3D_precomp, sc->prefiltered, g, im.tile_count, radii, sk);
+		} }
 		MOSS_CHECK_LAUNCH(stream, flags);
 		int* host_R = nullptr;
 		if (slot >= 0) MOSS_CUDA_TRY(cudaHostGetDevicePointer((void**)&host_R, lease.pool->host + slot, 0));
@@ -489,9 +524,10 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 	const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
 	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* tmp_ws, size_t tmp_bytes,
-	const MossPush* push = nullptr)
+	const MossPush* push = nullptr, const MossSkin* skin = nullptr, const SkinGradOut* skin_out = nullptr)
 {
-	if (!scene_valid(sc, views == nullptr)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (!scene_valid(sc, views == nullptr, skin)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (skin && (V != 1 || push || !skin_out)) return MOSS_ERR_INVALID_ARGUMENT;
 	PushCfg pc = no_push();
 	GatherArgs ga;
 	unsigned gather_blocks = 0;
@@ -502,8 +538,14 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 	const int P = sc->P, W = sc->W, H = sc->H, N = W * H;
 	if (P == 0) return MOSS_OK;
 	if (!radii || !dL_dpix || !dL_dmean2D || !dL_dopacity || !dL_dcolor ||
-		!dL_dmean3D || !dL_dcov3D || (sc->shs && !dL_dsh) || (sc->scales && (!dL_dscale || !dL_drot)))
+		(!skin && (!dL_dmean3D || !dL_dcov3D)) || (sc->shs && !dL_dsh) || (sc->scales && (!dL_dscale || !dL_drot)))
 		return MOSS_ERR_INVALID_ARGUMENT;
+	if (skin) {
+		if (!skin_out->d_xyz || !skin_out->d_scaling || !skin_out->d_rotation || (skin_out->d_lbs_delta && !skin->lbs_delta) ||
+			((uintptr_t)skin_out->d_rotation & 15) || ((uintptr_t)skin_out->d_lbs_delta & 15)) return MOSS_ERR_INVALID_ARGUMENT;
+		if (skin_out->d_A_tgt) MOSS_CUDA_TRY(cudaMemsetAsync(skin_out->d_A_tgt, 0, sizeof(float) * NJ * 16, stream));
+		if (skin_out->d_poseoff_tgt) MOSS_CUDA_TRY(cudaMemsetAsync(skin_out->d_poseoff_tgt, 0, sizeof(float) * 3 * (size_t)skin->V, stream));
+	}
 	ViewBatch vb;
 	if (!make_batch(sc, V, views, &vb)) return MOSS_ERR_INVALID_ARGUMENT;
 	const int T = vb.T, TV = T * V;
@@ -550,9 +592,18 @@ int backward_impl(cudaStream_t stream, const MossScene* sc, int V, const MossVie
 		po.view_stride = row.total;
 	}
 	{ MOSS_STAGE(MOSS_STAGE_PREPROCESS_BWD, stream);
-	preprocess_backward_kernel<<<dim3((P + PRE_THREADS - 1) / PRE_THREADS, V), PRE_THREADS, 0, stream>>>(
-		vb, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
-		dL_dmean2D, dL_dconic, po, det, im.counters, no_push()); }
+	SkinFused sk;
+	SkinGradOut sg;
+	memset(&sk, 0, sizeof(sk)); memset(&sg, 0, sizeof(sg));
+	if (skin) {
+		sk.a = make_skin(skin); sg = *skin_out;
+		preprocess_backward_kernel<true><<<dim3((P + PRE_THREADS - 1) / PRE_THREADS, V), PRE_THREADS, 0, stream>>>(
+			vb, nullptr, radii, sc->shs, nullptr, nullptr, nullptr, g, dL_dmean2D, dL_dconic, po, det, im.counters, no_push(), sk, sg);
+	} else {
+		preprocess_backward_kernel<false><<<dim3((P + PRE_THREADS - 1) / PRE_THREADS, V), PRE_THREADS, 0, stream>>>(
+			vb, sc->means3D, radii, sc->shs, sc->scales, sc->rotations, sc->cov3D_precomp, g,
+			dL_dmean2D, dL_dconic, po, det, im.counters, no_push(), sk, sg);
+	} }
 	MOSS_CHECK_LAUNCH(stream, flags);
 	if (V > 1) {
 		SumViewsArgs a;
@@ -622,6 +673,24 @@ int moss_rasterize_forward(void* stream, const MossScene* sc, unsigned flags,
 	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
 {
 	return forward_impl((cudaStream_t)stream, sc, 1, nullptr, flags, out_color, out_depth, out_alpha, radii, num_rendered);
+}
+int moss_skin_rasterize_forward(void* stream, const MossScene* sc, const MossSkin* skin, unsigned flags,
+	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered, float* means3D, float* transforms)
+{
+	if (!skin) return MOSS_ERR_INVALID_ARGUMENT;
+	return forward_impl((cudaStream_t)stream, sc, 1, nullptr, flags, out_color, out_depth, out_alpha, radii, num_rendered, skin, means3D, transforms);
+}
+int moss_skin_rasterize_backward(void* stream, const MossScene* sc, const MossSkin* skin, unsigned flags, const int* radii,
+	const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_dsh,
+	float* d_xyz, float* d_scaling, float* d_rotation, float* d_lbs_delta, float* d_A_tgt, float* d_poseoff_tgt)
+{
+	if (!skin) return MOSS_ERR_INVALID_ARGUMENT;
+	SkinGradOut sg;
+	sg.d_xyz = d_xyz; sg.d_scaling = d_scaling; sg.d_rotation = d_rotation; sg.d_lbs_delta = d_lbs_delta;
+	sg.d_A_tgt = d_A_tgt; sg.d_poseoff_tgt = d_poseoff_tgt;
+	return backward_impl((cudaStream_t)stream, sc, 1, nullptr, flags, radii, dL_dpix, dL_ddepth, dL_dalpha, dL_dmean2D, dL_dconic,
+		dL_dopacity, dL_dcolor, nullptr, nullptr, dL_dsh, nullptr, nullptr, nullptr, 0, nullptr, skin, &sg);
 }
 int moss_rasterize_forward_batch(void* stream, const MossScene* sc, int V, const MossView* views, unsigned flags,
 	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
@@ -741,24 +810,6 @@ long long moss_export_state(void* stream, const MossScene* sc, int which, void* 
 }
 
 // ---- fused skinning + covariance front end ---------------------------------------------------------------
-static inline bool skin_valid(const MossSkin* k)
-{
-	if (!k || k->P < 0 || k->V <= 0) return false;
-	if (k->P == 0) return true;
-	if (!k->xyz || !k->vert_ids || !k->weights || !k->A_big || !k->A_tgt || !k->Rg || !k->Th) return false;
-	if ((k->scaling != nullptr) != (k->rotation != nullptr)) return false;
-	if (((uintptr_t)k->weights & 15) || ((uintptr_t)k->lbs_delta & 15)) return false;
-	return true;
-}
-static inline SkinArgs make_skin(const MossSkin* k)
-{
-	SkinArgs a;
-	a.P = k->P; a.xyz = k->xyz; a.vert_ids = k->vert_ids; a.weights = k->weights; a.lbs_delta = k->lbs_delta;
-	a.A_big = k->A_big; a.A_tgt = k->A_tgt; a.poseoff_big = k->poseoff_big; a.shapeoff = k->shapeoff;
-	a.poseoff_tgt = k->poseoff_tgt; a.Rg = k->Rg; a.Th = k->Th; a.scaling = k->scaling; a.rotation = k->rotation;
-	a.scale_modifier = k->scale_modifier;
-	return a;
-}
 size_t moss_sizeof_skin(void) { return sizeof(MossSkin); }
 
 int moss_skin_forward(void* stream_, const MossSkin* k, float* means3D, float* cov3D, float* transforms,

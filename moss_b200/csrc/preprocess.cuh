@@ -9,6 +9,7 @@
 // or global radix sort is needed downstream, and colour+depth are packed into one float4 per Gaussian.
 #pragma once
 #include "common.cuh"
+#include "skin.cuh"
 
 namespace moss {
 
@@ -213,13 +214,24 @@ __device__ __forceinline__ float ndc_to_pix(float v, int S)
 
 constexpr int PRE_THREADS = 128;   // 20 k Gaussians -> 157 blocks: every SM gets work (256 left 69 of 148 idle)
 
+// What the fused skin + preprocess entry points add to the per-Gaussian kernels (SKIN = true; north_star subsystem 1,
+// SURVEY.md section 7 step 8): the Gaussian's world position and covariance come out of the skinning device functions
+// (skin.cuh) in registers instead of being read from HBM -- MOSS's one-view-per-iteration loop
+// (gaussian_renderer/__init__.py:57-93 feeding DGR forward.cu:155-256) never needs them in memory.
+struct SkinFused {
+	SkinArgs a;
+	float* means3D;      // forward: optional [P,3] copy of the skinned centres (NULL: never written)
+	float* transforms;   // forward: optional [P,9] (render()'s "transforms")
+};
+
 // grid = (ceil(P / PRE_THREADS), V): block row v preprocesses the Gaussians for view v ("virtual Gaussian" v*P + i).
+template <bool SKIN>
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_forward_kernel(const __grid_constant__ ViewBatch vb,
 	const float* __restrict__ means3D, const float* __restrict__ shs, const float* __restrict__ colors_precomp,
 	const float* __restrict__ opacities, const float* __restrict__ scales, const float* __restrict__ rotations,
 	const float* __restrict__ cov3D_precomp, int prefiltered,
-	GeomWS g, uint32_t* __restrict__ tile_count, int* __restrict__ radii)
+	GeomWS g, uint32_t* __restrict__ tile_count, int* __restrict__ radii, const SkinFused sk)
 {
 	// Every global read of the Gaussian is issued here, before the first data-dependent branch, so the kernel pays
 	// ONE DRAM round trip instead of a chain of four (position -> covariance -> SH -> opacity); with a cold L2 and
@@ -231,17 +243,26 @@ preprocess_forward_kernel(const __grid_constant__ ViewBatch vb,
 	const bool active = idx < P;
 	const int li = active ? idx : 0;
 	const size_t vid = (size_t)view * P + idx;            // virtual Gaussian: row of the per-view state
-	const float px = means3D[3 * li], py = means3D[3 * li + 1], pz = means3D[3 * li + 2];
+	float px, py, pz;
 	const float opac = opacities[li];
 	float c3[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 	float4 quat = make_float4(0.f, 0.f, 0.f, 0.f);
 	float sc3[3] = {0.f, 0.f, 0.f};
-	if (cov3D_precomp != nullptr) {
-#pragma unroll
-		for (int k = 0; k < 6; k++) c3[k] = cov3D_precomp[6 * li + k];
+	int sk_vid = 0;
+	SkinOwn sk_own;
+	if constexpr (SKIN) {
+		sk_vid = __ldg(sk.a.vert_ids + li);
+		sk_own = skin_own(sk.a, li);
+		px = py = pz = 0.f;
 	} else {
-		quat = load_quat(rotations, li);
-		sc3[0] = scales[3 * li]; sc3[1] = scales[3 * li + 1]; sc3[2] = scales[3 * li + 2];
+		px = means3D[3 * li]; py = means3D[3 * li + 1]; pz = means3D[3 * li + 2];
+		if (cov3D_precomp != nullptr) {
+#pragma unroll
+			for (int k = 0; k < 6; k++) c3[k] = cov3D_precomp[6 * li + k];
+		} else {
+			quat = load_quat(rotations, li);
+			sc3[0] = scales[3 * li]; sc3[1] = scales[3 * li + 1]; sc3[2] = scales[3 * li + 2];
+		}
 	}
 	float shl[48];
 	float rgb_in[3] = {0.f, 0.f, 0.f};
@@ -258,6 +279,26 @@ preprocess_forward_kernel(const __grid_constant__ ViewBatch vb,
 	else if (threadIdx.x < 32) s_proj[threadIdx.x - 16] = cam.proj[threadIdx.x - 16];
 	else if (threadIdx.x < 35 && colors_precomp == nullptr) s_cam[threadIdx.x - 32] = cam.campos[threadIdx.x - 32];
 	__syncthreads();
+	if constexpr (SKIN) {
+		// skinning in registers: blended joint transforms, offsets, world position, transformed covariance
+		__shared__ SkinShared sh;
+		skin_stage(sh, sk.a);
+		if (active) {
+			float bw[NJ];
+			skin_weights(sk.a, li, sk_vid, bw);
+			SkinFwd f;
+			skin_point(sh, sk.a, sk_own.x, sk_vid, bw, f);
+			float world[3];
+			skin_world(sh, f, world);
+			px = world[0]; py = world[1]; pz = world[2];
+			skin_cov(sk_own, f, c3);
+			if (sk.means3D) { sk.means3D[3 * (size_t)li] = px; sk.means3D[3 * (size_t)li + 1] = py; sk.means3D[3 * (size_t)li + 2] = pz; }
+			if (sk.transforms) {
+#pragma unroll
+				for (int i = 0; i < 9; i++) sk.transforms[9 * (size_t)li + i] = f.Tr.m[i];
+			}
+		}
+	}
 	if (!active) return;
 
 	int my_radius = 0;
@@ -278,10 +319,12 @@ preprocess_forward_kernel(const __grid_constant__ ViewBatch vb,
 		const float p_w = frcp(fadd(hw, 0.0000001f));
 		const float ndc_x = fmul(hx, p_w), ndc_y = fmul(hy, p_w);
 
-		if (cov3D_precomp == nullptr) {
-			cov3d_from_scale_rot(sc3[0], sc3[1], sc3[2], vb.scale_modifier, quat.x, quat.y, quat.z, quat.w, c3);
+		if constexpr (!SKIN) {
+			if (cov3D_precomp == nullptr) {
+				cov3d_from_scale_rot(sc3[0], sc3[1], sc3[2], vb.scale_modifier, quat.x, quat.y, quat.z, quat.w, c3);
 #pragma unroll
-			for (int k = 0; k < 6; k++) g.cov3D[6 * vid + k] = c3[k];
+				for (int k = 0; k < 6; k++) g.cov3D[6 * vid + k] = c3[k];
+			}
 		}
 
 		const float tx = affine_row(px, py, pz, s_view[0], s_view[4], s_view[8], s_view[12]);

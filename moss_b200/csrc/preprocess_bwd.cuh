@@ -30,14 +30,28 @@ struct ParamGradOut {
 	size_t view_stride;   // floats between consecutive views' rows (0 for a single view)
 };
 
-// grid = (ceil(P / PRE_THREADS), V)
+// Where the fused skin + preprocess backward (SKIN = true) puts the front end's gradients: rows per Gaussian, and the two
+// accumulators of the per-frame tables (cleared by the caller).
+struct SkinGradOut {
+	float* d_xyz;          // [P,3]
+	float* d_scaling;      // [P,3]
+	float* d_rotation;     // [P,4]
+	float* d_lbs_delta;    // [P,24] or null
+	float* d_A_tgt;        // [24,16] or null
+	float* d_poseoff_tgt;  // [V,3] or null
+};
+
+// grid = (ceil(P / PRE_THREADS), V).  SKIN: single view, no exchange; means3D / cov3D are recomputed from the skinning
+// inputs and dL/dmeans3D, dL/dcov3D go straight into the skinning backward (skin.cuh) without touching HBM.
+template <bool SKIN>
 __global__ void __launch_bounds__(PRE_THREADS)
 preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	const float* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
 	const float* __restrict__ scales, const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
 	GeomWS g,
 	float* __restrict__ dL_dmean2D_all, float* __restrict__ dL_dconic_all, ParamGradOut po,
-	int deterministic, const uint32_t* __restrict__ counters, const __grid_constant__ PushCfg pc)
+	int deterministic, const uint32_t* __restrict__ counters, const __grid_constant__ PushCfg pc,
+	const SkinFused sk, const SkinGradOut sg)
 {
 	// All global reads of the Gaussian are issued before the first data-dependent branch (one DRAM round trip instead
 	// of a chain; see preprocess_forward_kernel) -- except the accumulator row, which only visible Gaussians own.
@@ -55,8 +69,8 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	float* __restrict__ dL_dconic = dL_dconic_all ? dL_dconic_all + 4 * (size_t)view * P : nullptr;
 	float* __restrict__ dL_dcolor = po.color + vo;
 	float* __restrict__ dL_dopacity = po.opacity + vo;
-	float* __restrict__ dL_dmean3D = po.mean3D + vo;
-	float* __restrict__ dL_dcov3D = po.cov3D + vo;
+	float* __restrict__ dL_dmean3D = SKIN ? nullptr : po.mean3D + vo;
+	float* __restrict__ dL_dcov3D = SKIN ? nullptr : po.cov3D + vo;
 	float* __restrict__ dL_dsh = po.sh ? po.sh + vo : nullptr;
 	float* __restrict__ dL_dscale = po.scale ? po.scale + vo : nullptr;
 	float* __restrict__ dL_drot = po.rot ? po.rot + vo : nullptr;
@@ -76,9 +90,17 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 			acc2 = (float)e[2] * inv;
 		}
 	}
-	const float mx = means3D[3 * li], my = means3D[3 * li + 1], mz = means3D[3 * li + 2];
-	const float* c3 = cov3D_precomp ? (cov3D_precomp + 6 * (size_t)li) : (g.cov3D + 6 * vid);
-	const float V0 = c3[0], V1 = c3[1], V2 = c3[2], V3 = c3[3], V4 = c3[4], V5 = c3[5];
+	float mx = 0.f, my = 0.f, mz = 0.f, V0 = 0.f, V1 = 0.f, V2 = 0.f, V3 = 0.f, V4 = 0.f, V5 = 0.f;
+	int sk_vid = 0;
+	SkinOwn sk_own;
+	if constexpr (SKIN) {
+		sk_vid = __ldg(sk.a.vert_ids + li);
+		sk_own = skin_own(sk.a, li);
+	} else {
+		mx = means3D[3 * li]; my = means3D[3 * li + 1]; mz = means3D[3 * li + 2];
+		const float* c3 = cov3D_precomp ? (cov3D_precomp + 6 * (size_t)li) : (g.cov3D + 6 * vid);
+		V0 = c3[0]; V1 = c3[1]; V2 = c3[2]; V3 = c3[3]; V4 = c3[4]; V5 = c3[5];
+	}
 	const uint8_t cl = g.clamped[vid];
 	const bool sh_vec = shs && ((reinterpret_cast<uintptr_t>(shs) & 15) == 0) && ((3 * M) % 4 == 0);
 	const bool dsh_vec = shs && M == 16 && ((reinterpret_cast<uintptr_t>(dL_dsh) & 15) == 0);
@@ -96,7 +118,30 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	else if (threadIdx.x < 32) pr[threadIdx.x - 16] = cam.proj[threadIdx.x - 16];
 	else if (threadIdx.x < 35 && shs) s_cam[threadIdx.x - 32] = cam.campos[threadIdx.x - 32];
 	__syncthreads();
+	__shared__ SkinShared sk_sh;         // SKIN only (unused allocations are dropped by the compiler otherwise)
+	__shared__ float accA[NJ * 12];
+	if constexpr (SKIN) {
+		skin_stage(sk_sh, sk.a);
+		if (sg.d_A_tgt) {
+			for (int i = threadIdx.x; i < NJ * 12; i += blockDim.x) accA[i] = 0.f;
+			__syncthreads();
+		}
+	}
+	// the per-Gaussian body; in the fused form every thread comes back for the block-level flush of dL/dA_tgt
+	auto body = [&]() {
 	if (!active) return;
+	float sk_bw[NJ];
+	SkinFwd sk_f;
+	if constexpr (SKIN) {
+		// recompute the front end's forward (nothing of it was stored): world position and covariance
+		skin_weights(sk.a, li, sk_vid, sk_bw);
+		skin_point(sk_sh, sk.a, sk_own.x, sk_vid, sk_bw, sk_f);
+		float world[3], c6[6];
+		skin_world(sk_sh, sk_f, world);
+		skin_cov(sk_own, sk_f, c6);
+		mx = world[0]; my = world[1]; mz = world[2];
+		V0 = c6[0]; V1 = c6[1]; V2 = c6[2]; V3 = c6[3]; V4 = c6[4]; V5 = c6[5];
+	}
 
 	// The blend backward accumulated into g.grad_acc (vector atomics); unpack it into the caller's tensors, which are
 	// therefore fully written here (no zero-fill beforehand), and leave the accumulators zero for the next backward.
@@ -116,10 +161,21 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	if (dL_dconic) { dL_dconic[4 * idx] = acc1.z; dL_dconic[4 * idx + 1] = acc1.w; dL_dconic[4 * idx + 2] = 0.f; dL_dconic[4 * idx + 3] = acc2; }
 
 	if (!(radius > 0)) {
+		if constexpr (SKIN) {
+			// a culled Gaussian: every front-end gradient row is zero
 #pragma unroll
-		for (int k = 0; k < 3; k++) *route(pc, dL_dmean3D + 3 * idx + k) = 0.f;
+			for (int k = 0; k < 3; k++) { sg.d_xyz[3 * (size_t)idx + k] = 0.f; sg.d_scaling[3 * (size_t)idx + k] = 0.f; }
+			*reinterpret_cast<float4*>(sg.d_rotation + 4 * (size_t)idx) = make_float4(0.f, 0.f, 0.f, 0.f);
+			if (sg.d_lbs_delta) {
 #pragma unroll
-		for (int k = 0; k < 6; k++) *route(pc, dL_dcov3D + 6 * idx + k) = 0.f;
+				for (int k = 0; k < NJ / 4; k++) reinterpret_cast<float4*>(sg.d_lbs_delta + (size_t)idx * NJ)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+			}
+		} else {
+#pragma unroll
+			for (int k = 0; k < 3; k++) *route(pc, dL_dmean3D + 3 * idx + k) = 0.f;
+#pragma unroll
+			for (int k = 0; k < 6; k++) *route(pc, dL_dcov3D + 6 * idx + k) = 0.f;
+		}
 		if (shs) {
 			if (dsh_vec) {
 				float* d = dL_dsh + (size_t)idx * 48;
@@ -182,8 +238,10 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 		dcov[2] = 2 * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + 2 * T10 * T12 * dL_dc;
 		dcov[4] = 2 * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2 * T11 * T12 * dL_dc;
 	}
+	if constexpr (!SKIN) {
 #pragma unroll
-	for (int k = 0; k < 6; k++) *route(pc, dL_dcov3D + 6 * idx + k) = dcov[k];
+		for (int k = 0; k < 6; k++) *route(pc, dL_dcov3D + 6 * idx + k) = dcov[k];
+	}
 
 	const float dT00 = 2 * VT00 * dL_da + VT10 * dL_db;
 	const float dT01 = 2 * VT01 * dL_da + VT11 * dL_db;
@@ -308,7 +366,14 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 		gmy += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * invsum32;
 		gmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
 	}
-	*route(pc, dL_dmean3D + 3 * idx) = gmx; *route(pc, dL_dmean3D + 3 * idx + 1) = gmy; *route(pc, dL_dmean3D + 3 * idx + 2) = gmz;
+	if constexpr (SKIN) {
+		// dL/dmeans3D and dL/dcov3D never leave the registers: straight into the skinning backward
+		const float gw[3] = {gmx, gmy, gmz};
+		skin_backward_point(sk_sh, sk.a, idx, sk_vid, sk_own, sk_bw, sk_f, gw, dcov, true, sg.d_xyz, sg.d_scaling, sg.d_rotation,
+			sg.d_lbs_delta, accA, sg.d_A_tgt != nullptr, sg.d_poseoff_tgt);
+	} else {
+		*route(pc, dL_dmean3D + 3 * idx) = gmx; *route(pc, dL_dmean3D + 3 * idx + 1) = gmy; *route(pc, dL_dmean3D + 3 * idx + 2) = gmz;
+	}
 
 	// ---- cov3D -> scale, (un-normalised) quaternion --------------------------------------------------
 	if (scales) {
@@ -344,6 +409,17 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 		store_quat_routed(pc, dL_drot, idx, dq);   // no normalisation Jacobian (DGR backward.cu:340)
 	}
 	if (pc.numel) __threadfence_system();   // pushed rows are on their way before this thread retires
+	};
+	body();
+	if constexpr (SKIN) {
+		if (sg.d_A_tgt) {
+			__syncthreads();
+			for (int i = threadIdx.x; i < NJ * 12; i += blockDim.x) {
+				const float v = accA[i];
+				if (v != 0.f) atomicAdd(sg.d_A_tgt + (i / 12) * 16 + (i % 12), v);
+			}
+		}
+	}
 }
 
 // Batched backward, V > 1: out[j] = sum_v rows[v*stride + j] over the views, in view order (fixed order: the sum is

@@ -224,6 +224,32 @@ __device__ __forceinline__ void quat_rot(const float qr[4], float inv_norm, Mat3
 	R.m[6] = 2.f * (x * z - r * y); R.m[7] = 2.f * (y * z + r * x); R.m[8] = 1.f - 2.f * (x * x + y * y);
 }
 
+// world = smpl_pts @ inverse(R) + Th   (scene/gaussian_model.py:911-912)
+__device__ __forceinline__ void skin_world(const SkinShared& sh, const SkinFwd& f, float world[3])
+{
+#pragma unroll
+	for (int i = 0; i < 3; i++)
+		world[i] = (f.s[0] * sh.Rgi[i] + f.s[1] * sh.Rgi[3 + i] + f.s[2] * sh.Rgi[6 + i]) + sh.Th[i];
+}
+
+// cov3D_precomp = strip_symmetric(T (L L^T) T^T), L = R(q / |q|) diag(mod * s)   (scene/gaussian_model.py:37-44)
+__device__ __forceinline__ void skin_cov(const SkinOwn& own, const SkinFwd& f, float c6[6])
+{
+	const float (&qr)[4] = own.qr;
+	const float (&sc)[3] = own.sc;
+	const float inv_norm = 1.0f / sqrtf(qr[0] * qr[0] + qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
+	Mat3 Rq, L;
+	quat_rot(qr, inv_norm, Rq);
+#pragma unroll
+	for (int i = 0; i < 3; i++)
+#pragma unroll
+		for (int k = 0; k < 3; k++) L.m[3 * i + k] = Rq.m[3 * i + k] * sc[k];
+	const Mat3 S = mat3_mul_nt(L, L);              // L L^T
+	const Mat3 TS = mat3_mul(f.Tr, S);             // transform @ cov
+	const Mat3 C = mat3_mul_nt(TS, f.Tr);          // ... @ transform^T
+	c6[0] = C.m[0]; c6[1] = C.m[1]; c6[2] = C.m[2]; c6[3] = C.m[4]; c6[4] = C.m[5]; c6[5] = C.m[8];   // upper triangle
+}
+
 __global__ void __launch_bounds__(SKIN_THREADS)
 skin_forward_kernel(SkinArgs a, float* __restrict__ means3D, float* __restrict__ cov3D, float* __restrict__ transforms,
                     float* __restrict__ bweights, float* __restrict__ translation)
@@ -238,10 +264,10 @@ skin_forward_kernel(SkinArgs a, float* __restrict__ means3D, float* __restrict__
 	skin_weights(a, idx, vid, bw);
 	SkinFwd f;
 	skin_point(sh, a, own.x, vid, bw, f);
-	// world = smpl_pts @ inverse(R) + Th   (scene/gaussian_model.py:911-912)
+	float world[3];
+	skin_world(sh, f, world);
 #pragma unroll
-	for (int i = 0; i < 3; i++)
-		means3D[3 * (size_t)idx + i] = (f.s[0] * sh.Rgi[i] + f.s[1] * sh.Rgi[3 + i] + f.s[2] * sh.Rgi[6 + i]) + sh.Th[i];
+	for (int i = 0; i < 3; i++) means3D[3 * (size_t)idx + i] = world[i];
 	if (transforms) {
 #pragma unroll
 		for (int i = 0; i < 9; i++) transforms[9 * (size_t)idx + i] = f.Tr.m[i];
@@ -271,20 +297,11 @@ skin_forward_kernel(SkinArgs a, float* __restrict__ means3D, float* __restrict__
 			translation[3 * (size_t)idx + i] = (r2[0] * sh.Rgi[i] + r2[1] * sh.Rgi[3 + i] + r2[2] * sh.Rgi[6 + i]) + sh.Th[i];
 	}
 	if (cov3D && a.scaling) {
-		const float (&qr)[4] = own.qr;
-		const float (&sc)[3] = own.sc;
-		const float inv_norm = 1.0f / sqrtf(qr[0] * qr[0] + qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
-		Mat3 Rq, L;
-		quat_rot(qr, inv_norm, Rq);
+		float c6[6];
+		skin_cov(own, f, c6);
+		float* o = cov3D + 6 * (size_t)idx;
 #pragma unroll
-		for (int i = 0; i < 3; i++)
-#pragma unroll
-			for (int k = 0; k < 3; k++) L.m[3 * i + k] = Rq.m[3 * i + k] * sc[k];
-		const Mat3 S = mat3_mul_nt(L, L);              // L L^T
-		const Mat3 TS = mat3_mul(f.Tr, S);             // transform @ cov
-		const Mat3 C = mat3_mul_nt(TS, f.Tr);          // ... @ transform^T
-		float* o = cov3D + 6 * (size_t)idx;            // strip_symmetric: upper triangle of the full product
-		o[0] = C.m[0]; o[1] = C.m[1]; o[2] = C.m[2]; o[3] = C.m[4]; o[4] = C.m[5]; o[5] = C.m[8];
+		for (int k = 0; k < 6; k++) o[k] = c6[k];
 	}
 }
 
@@ -295,6 +312,139 @@ skin_forward_kernel(SkinArgs a, float* __restrict__ means3D, float* __restrict__
 // normalisation Jacobian), d_lbs_delta [P,24] (only with lbs_delta).  Accumulated (caller-zeroed):
 // d_A_tgt [24,16] (row-major 4x4 per joint like A_tgt; bottom rows stay 0 -> pose-correction MLP) and
 // d_poseoff_tgt [V,3] (scatter by vert_id).
+// The per-Gaussian backward of the front end: upstream gw = dL/dmeans3D, gcv = dL/dcov3D (has_gcov: whether it is there).
+// Writes d_xyz / d_scaling / d_rotation / d_lbs_delta rows, adds into d_poseoff_tgt (global atomics) and into the block's
+// shared accA [24*12] (dL/dA_tgt; the caller flushes it).  `f` and `bw` are the recomputed forward.
+__device__ __forceinline__ void skin_backward_point(const SkinShared& sh, const SkinArgs& a, int idx, int vid, const SkinOwn& own,
+	const float bw[NJ], const SkinFwd& f, const float gw[3], const float gcv[6], bool has_gcov,
+	float* __restrict__ d_xyz, float* __restrict__ d_scaling, float* __restrict__ d_rotation, float* __restrict__ d_lbs_delta,
+	float* accA, bool want_dA, float* __restrict__ d_poseoff_tgt)
+{
+	float* const d_A_tgt = want_dA ? accA : nullptr;
+	Mat3 dTr;
+#pragma unroll
+	for (int i = 0; i < 9; i++) dTr.m[i] = 0.f;
+	if (a.scaling && has_gcov) {
+		const float (&qr)[4] = own.qr;
+		const float (&sc)[3] = own.sc;
+		const float inv_norm = 1.0f / sqrtf(qr[0] * qr[0] + qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
+		Mat3 Rq, L;
+		quat_rot(qr, inv_norm, Rq);
+#pragma unroll
+		for (int i = 0; i < 3; i++)
+#pragma unroll
+			for (int k = 0; k < 3; k++) L.m[3 * i + k] = Rq.m[3 * i + k] * sc[k];
+		const Mat3 S = mat3_mul_nt(L, L);
+		Mat3 G;      // gradient w.r.t. the full 3x3 product: only the upper triangle is read (strip_symmetric)
+		G.m[0] = gcv[0]; G.m[1] = gcv[1]; G.m[2] = gcv[2]; G.m[3] = 0.f; G.m[4] = gcv[3];
+		G.m[5] = gcv[4]; G.m[6] = 0.f; G.m[7] = 0.f; G.m[8] = gcv[5];
+		Mat3 Gs;     // G + G^T
+#pragma unroll
+		for (int i = 0; i < 3; i++)
+#pragma unroll
+			for (int j = 0; j < 3; j++) Gs.m[3 * i + j] = G.m[3 * i + j] + G.m[3 * j + i];
+		const Mat3 TS = mat3_mul(f.Tr, S);
+		dTr = mat3_mul(Gs, TS);                              // d(T S T^T)/dT, S symmetric
+		const Mat3 dS = mat3_mul(mat3_mul_tn(f.Tr, G), f.Tr); // T^T G T
+		Mat3 dSs;
+#pragma unroll
+		for (int i = 0; i < 3; i++)
+#pragma unroll
+			for (int j = 0; j < 3; j++) dSs.m[3 * i + j] = dS.m[3 * i + j] + dS.m[3 * j + i];
+		const Mat3 dL = mat3_mul(dSs, L);
+		Mat3 dR;
+#pragma unroll
+		for (int k = 0; k < 3; k++) {
+			const float ds = Rq.m[k] * dL.m[k] + Rq.m[3 + k] * dL.m[3 + k] + Rq.m[6 + k] * dL.m[6 + k];
+			d_scaling[3 * (size_t)idx + k] = a.scale_modifier * ds;
+#pragma unroll
+			for (int i = 0; i < 3; i++) dR.m[3 * i + k] = dL.m[3 * i + k] * sc[k];
+		}
+		const float r = qr[0] * inv_norm, x = qr[1] * inv_norm, y = qr[2] * inv_norm, z = qr[3] * inv_norm;
+		const float dr = 2.f * (z * (dR.m[3] - dR.m[1]) + y * (dR.m[2] - dR.m[6]) + x * (dR.m[7] - dR.m[5]));
+		const float dx = 2.f * (y * (dR.m[1] + dR.m[3]) + z * (dR.m[2] + dR.m[6]) + r * (dR.m[7] - dR.m[5])) - 4.f * x * (dR.m[4] + dR.m[8]);
+		const float dy = 2.f * (x * (dR.m[1] + dR.m[3]) + r * (dR.m[2] - dR.m[6]) + z * (dR.m[5] + dR.m[7])) - 4.f * y * (dR.m[0] + dR.m[8]);
+		const float dz = 2.f * (r * (dR.m[3] - dR.m[1]) + x * (dR.m[2] + dR.m[6]) + y * (dR.m[5] + dR.m[7])) - 4.f * z * (dR.m[0] + dR.m[4]);
+		const float dot = r * dr + x * dx + y * dy + z * dz;
+		float4 o;
+		o.x = (dr - r * dot) * inv_norm; o.y = (dx - x * dot) * inv_norm;
+		o.z = (dy - y * dot) * inv_norm; o.w = (dz - z * dot) * inv_norm;
+		*reinterpret_cast<float4*>(d_rotation + 4 * (size_t)idx) = o;
+	} else {
+		if (d_scaling) { d_scaling[3 * (size_t)idx] = 0.f; d_scaling[3 * (size_t)idx + 1] = 0.f; d_scaling[3 * (size_t)idx + 2] = 0.f; }
+		if (d_rotation) *reinterpret_cast<float4*>(d_rotation + 4 * (size_t)idx) = make_float4(0.f, 0.f, 0.f, 0.f);
+	}
+
+	// ---- skinning chain --------------------------------------------------------------------------------
+	float gs[3];
+#pragma unroll
+	for (int j = 0; j < 3; j++) gs[j] = sh.Rgi[3 * j] * gw[0] + sh.Rgi[3 * j + 1] * gw[1] + sh.Rgi[3 * j + 2] * gw[2];
+	Mat3 Rg;
+#pragma unroll
+	for (int i = 0; i < 9; i++) Rg.m[i] = sh.Rg[i];
+	const Mat3 gTr0 = mat3_mul_tn(Rg, dTr);
+	Mat3 gRt = mat3_mul_nt(gTr0, f.Rbi);
+#pragma unroll
+	for (int i = 0; i < 3; i++)
+#pragma unroll
+		for (int j = 0; j < 3; j++) gRt.m[3 * i + j] += gs[i] * f.q[j];
+	float gq[3];
+	mat3_tvec(f.Rt, gs, gq);
+	Mat3 gRbi = mat3_mul_tn(f.Rt, gTr0);
+#pragma unroll
+	for (int i = 0; i < 3; i++)
+#pragma unroll
+		for (int j = 0; j < 3; j++) gRbi.m[3 * i + j] += gq[i] * f.xb[j];
+	float gx[3];
+	mat3_tvec(f.Rbi, gq, gx);
+#pragma unroll
+	for (int i = 0; i < 3; i++) d_xyz[3 * (size_t)idx + i] = gx[i];
+	if (d_poseoff_tgt) {
+#pragma unroll
+		for (int i = 0; i < 3; i++) atomicAdd(d_poseoff_tgt + 3 * (size_t)vid + i, gq[i]);
+	}
+	if (d_lbs_delta || d_A_tgt) {
+		// gradient w.r.t. the blended 3x4 transforms, laid out like the table rows (r00 r01 r02 t0 | ...)
+		const Mat3 tmp = mat3_mul_tn(f.Rbi, gRbi);
+		const Mat3 gRb = mat3_mul_nt(tmp, f.Rbi);     // Rbi^T gRbi Rbi^T, sign applied below
+		float gAb[12], gAt[12];
+#pragma unroll
+		for (int i = 0; i < 3; i++) {
+#pragma unroll
+			for (int j = 0; j < 3; j++) { gAb[4 * i + j] = -gRb.m[3 * i + j]; gAt[4 * i + j] = gRt.m[3 * i + j]; }
+			gAb[4 * i + 3] = -gx[i];
+			gAt[4 * i + 3] = gs[i];
+		}
+		if (d_A_tgt) {
+#pragma unroll
+			for (int j = 0; j < NJ; j++) {
+				const float w = bw[j];
+				if (w != 0.f) {
+#pragma unroll
+					for (int e = 0; e < 12; e++) atomicAdd(&accA[j * 12 + e], w * gAt[e]);
+				}
+			}
+		}
+		if (d_lbs_delta) {
+			float gb[NJ];
+			float mean = 0.f;
+#pragma unroll
+			for (int j = 0; j < NJ; j++) {
+				float acc = 0.f;
+#pragma unroll
+				for (int e = 0; e < 12; e++) acc += gAb[e] * sh.Ab[j][e] + gAt[e] * sh.At[j][e];
+				gb[j] = acc;
+				mean += bw[j] * acc;
+			}
+			float4* o = reinterpret_cast<float4*>(d_lbs_delta + (size_t)idx * NJ);
+#pragma unroll
+			for (int k = 0; k < NJ / 4; k++)
+				o[k] = make_float4(bw[4 * k] * (gb[4 * k] - mean), bw[4 * k + 1] * (gb[4 * k + 1] - mean),
+				                   bw[4 * k + 2] * (gb[4 * k + 2] - mean), bw[4 * k + 3] * (gb[4 * k + 3] - mean));
+		}
+	}
+}
+
 __global__ void __launch_bounds__(SKIN_THREADS)
 skin_backward_kernel(SkinArgs a, const float* __restrict__ g_means3D, const float* __restrict__ g_cov3D,
                      float* __restrict__ d_xyz, float* __restrict__ d_scaling, float* __restrict__ d_rotation,
@@ -320,129 +470,8 @@ skin_backward_kernel(SkinArgs a, const float* __restrict__ g_means3D, const floa
 		skin_weights(a, idx, vid, bw);
 		SkinFwd f;
 		skin_point(sh, a, own.x, vid, bw, f);
-
-		Mat3 dTr;
-#pragma unroll
-		for (int i = 0; i < 9; i++) dTr.m[i] = 0.f;
-		if (a.scaling && g_cov3D) {
-			const float (&qr)[4] = own.qr;
-			const float (&sc)[3] = own.sc;
-			const float inv_norm = 1.0f / sqrtf(qr[0] * qr[0] + qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
-			Mat3 Rq, L;
-			quat_rot(qr, inv_norm, Rq);
-#pragma unroll
-			for (int i = 0; i < 3; i++)
-#pragma unroll
-				for (int k = 0; k < 3; k++) L.m[3 * i + k] = Rq.m[3 * i + k] * sc[k];
-			const Mat3 S = mat3_mul_nt(L, L);
-			Mat3 G;      // gradient w.r.t. the full 3x3 product: only the upper triangle is read (strip_symmetric)
-			G.m[0] = gcv[0]; G.m[1] = gcv[1]; G.m[2] = gcv[2]; G.m[3] = 0.f; G.m[4] = gcv[3];
-			G.m[5] = gcv[4]; G.m[6] = 0.f; G.m[7] = 0.f; G.m[8] = gcv[5];
-			Mat3 Gs;     // G + G^T
-#pragma unroll
-			for (int i = 0; i < 3; i++)
-#pragma unroll
-				for (int j = 0; j < 3; j++) Gs.m[3 * i + j] = G.m[3 * i + j] + G.m[3 * j + i];
-			const Mat3 TS = mat3_mul(f.Tr, S);
-			dTr = mat3_mul(Gs, TS);                              // d(T S T^T)/dT, S symmetric
-			const Mat3 dS = mat3_mul(mat3_mul_tn(f.Tr, G), f.Tr); // T^T G T
-			Mat3 dSs;
-#pragma unroll
-			for (int i = 0; i < 3; i++)
-#pragma unroll
-				for (int j = 0; j < 3; j++) dSs.m[3 * i + j] = dS.m[3 * i + j] + dS.m[3 * j + i];
-			const Mat3 dL = mat3_mul(dSs, L);
-			Mat3 dR;
-#pragma unroll
-			for (int k = 0; k < 3; k++) {
-				const float ds = Rq.m[k] * dL.m[k] + Rq.m[3 + k] * dL.m[3 + k] + Rq.m[6 + k] * dL.m[6 + k];
-				d_scaling[3 * (size_t)idx + k] = a.scale_modifier * ds;
-#pragma unroll
-				for (int i = 0; i < 3; i++) dR.m[3 * i + k] = dL.m[3 * i + k] * sc[k];
-			}
-			const float r = qr[0] * inv_norm, x = qr[1] * inv_norm, y = qr[2] * inv_norm, z = qr[3] * inv_norm;
-			const float dr = 2.f * (z * (dR.m[3] - dR.m[1]) + y * (dR.m[2] - dR.m[6]) + x * (dR.m[7] - dR.m[5]));
-			const float dx = 2.f * (y * (dR.m[1] + dR.m[3]) + z * (dR.m[2] + dR.m[6]) + r * (dR.m[7] - dR.m[5])) - 4.f * x * (dR.m[4] + dR.m[8]);
-			const float dy = 2.f * (x * (dR.m[1] + dR.m[3]) + r * (dR.m[2] - dR.m[6]) + z * (dR.m[5] + dR.m[7])) - 4.f * y * (dR.m[0] + dR.m[8]);
-			const float dz = 2.f * (r * (dR.m[3] - dR.m[1]) + x * (dR.m[2] + dR.m[6]) + y * (dR.m[5] + dR.m[7])) - 4.f * z * (dR.m[0] + dR.m[4]);
-			const float dot = r * dr + x * dx + y * dy + z * dz;
-			float4 o;
-			o.x = (dr - r * dot) * inv_norm; o.y = (dx - x * dot) * inv_norm;
-			o.z = (dy - y * dot) * inv_norm; o.w = (dz - z * dot) * inv_norm;
-			*reinterpret_cast<float4*>(d_rotation + 4 * (size_t)idx) = o;
-		} else {
-			if (d_scaling) { d_scaling[3 * (size_t)idx] = 0.f; d_scaling[3 * (size_t)idx + 1] = 0.f; d_scaling[3 * (size_t)idx + 2] = 0.f; }
-			if (d_rotation) *reinterpret_cast<float4*>(d_rotation + 4 * (size_t)idx) = make_float4(0.f, 0.f, 0.f, 0.f);
-		}
-
-		// ---- skinning chain --------------------------------------------------------------------------------
-		float gs[3];
-#pragma unroll
-		for (int j = 0; j < 3; j++) gs[j] = sh.Rgi[3 * j] * gw[0] + sh.Rgi[3 * j + 1] * gw[1] + sh.Rgi[3 * j + 2] * gw[2];
-		Mat3 Rg;
-#pragma unroll
-		for (int i = 0; i < 9; i++) Rg.m[i] = sh.Rg[i];
-		const Mat3 gTr0 = mat3_mul_tn(Rg, dTr);
-		Mat3 gRt = mat3_mul_nt(gTr0, f.Rbi);
-#pragma unroll
-		for (int i = 0; i < 3; i++)
-#pragma unroll
-			for (int j = 0; j < 3; j++) gRt.m[3 * i + j] += gs[i] * f.q[j];
-		float gq[3];
-		mat3_tvec(f.Rt, gs, gq);
-		Mat3 gRbi = mat3_mul_tn(f.Rt, gTr0);
-#pragma unroll
-		for (int i = 0; i < 3; i++)
-#pragma unroll
-			for (int j = 0; j < 3; j++) gRbi.m[3 * i + j] += gq[i] * f.xb[j];
-		float gx[3];
-		mat3_tvec(f.Rbi, gq, gx);
-#pragma unroll
-		for (int i = 0; i < 3; i++) d_xyz[3 * (size_t)idx + i] = gx[i];
-		if (d_poseoff_tgt) {
-#pragma unroll
-			for (int i = 0; i < 3; i++) atomicAdd(d_poseoff_tgt + 3 * (size_t)vid + i, gq[i]);
-		}
-		if (d_lbs_delta || d_A_tgt) {
-			// gradient w.r.t. the blended 3x4 transforms, laid out like the table rows (r00 r01 r02 t0 | ...)
-			const Mat3 tmp = mat3_mul_tn(f.Rbi, gRbi);
-			const Mat3 gRb = mat3_mul_nt(tmp, f.Rbi);     // Rbi^T gRbi Rbi^T, sign applied below
-			float gAb[12], gAt[12];
-#pragma unroll
-			for (int i = 0; i < 3; i++) {
-#pragma unroll
-				for (int j = 0; j < 3; j++) { gAb[4 * i + j] = -gRb.m[3 * i + j]; gAt[4 * i + j] = gRt.m[3 * i + j]; }
-				gAb[4 * i + 3] = -gx[i];
-				gAt[4 * i + 3] = gs[i];
-			}
-			if (d_A_tgt) {
-#pragma unroll
-				for (int j = 0; j < NJ; j++) {
-					const float w = bw[j];
-					if (w != 0.f) {
-#pragma unroll
-						for (int e = 0; e < 12; e++) atomicAdd(&accA[j * 12 + e], w * gAt[e]);
-					}
-				}
-			}
-			if (d_lbs_delta) {
-				float gb[NJ];
-				float mean = 0.f;
-#pragma unroll
-				for (int j = 0; j < NJ; j++) {
-					float acc = 0.f;
-#pragma unroll
-					for (int e = 0; e < 12; e++) acc += gAb[e] * sh.Ab[j][e] + gAt[e] * sh.At[j][e];
-					gb[j] = acc;
-					mean += bw[j] * acc;
-				}
-				float4* o = reinterpret_cast<float4*>(d_lbs_delta + (size_t)idx * NJ);
-#pragma unroll
-				for (int k = 0; k < NJ / 4; k++)
-					o[k] = make_float4(bw[4 * k] * (gb[4 * k] - mean), bw[4 * k + 1] * (gb[4 * k + 1] - mean),
-					                   bw[4 * k + 2] * (gb[4 * k + 2] - mean), bw[4 * k + 3] * (gb[4 * k + 3] - mean));
-			}
-		}
+		skin_backward_point(sh, a, idx, vid, own, bw, f, gw, gcv, g_cov3D != nullptr, d_xyz, d_scaling, d_rotation, d_lbs_delta,
+			accA, d_A_tgt != nullptr, d_poseoff_tgt);
 	}
 	if (d_A_tgt) {
 		__syncthreads();

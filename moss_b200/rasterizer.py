@@ -106,7 +106,10 @@ class RasterState:
         self.batched = False
 
 
-def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, settings_list, flags, batched):
+def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, settings_list, flags, batched,
+             skin=None):
+    """``skin``: (filled _abi.MossSkin, tensors to keep alive, means3D_out or None, transforms_out or None) -- the fused
+    skin + rasterize call (moss_skin_rasterize_forward); ``means3D`` then only names the device and the Gaussian count."""
     lib = _abi.load()
     rs = settings_list[0]
     V = len(settings_list)
@@ -154,7 +157,8 @@ def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_p
         st.V, st.batched = V, batched
         sc = st.scene
         sc.P, sc.D, sc.M, sc.W, sc.H = P, int(rs.sh_degree), M, W, H
-        sc.means3D = _ptr(means3D); sc.shs = _ptr(sh); sc.colors_precomp = _ptr(colors_precomp)
+        sc.means3D = None if skin is not None else _ptr(means3D)
+        sc.shs = _ptr(sh); sc.colors_precomp = _ptr(colors_precomp)
         sc.opacities = _ptr(opacities); sc.scales = _ptr(scales); sc.rotations = _ptr(rotations)
         sc.cov3D_precomp = _ptr(cov3Ds_precomp)
         sc.scale_modifier = float(rs.scale_modifier)
@@ -184,7 +188,12 @@ def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_p
                 cbytes = lib.moss_ckpt_workspace_bytes_batch(lib.moss_binning_capacity(bbytes, export), W, H, V)
                 ckpt = torch.empty((cbytes,), dtype=torch.uint8, device=dev)
                 sc.ckpt_ws = ckpt.data_ptr(); sc.ckpt_bytes = cbytes
-            if batched:
+            if skin is not None:
+                status = lib.moss_skin_rasterize_forward(stream, C.byref(sc), C.byref(skin[0]), call_flags, color.data_ptr(),
+                                                         depth.data_ptr(), alpha.data_ptr(), _ptr(radii), C.byref(nr),
+                                                         _ptr(skin[2]) if skin[2] is not None else None,
+                                                         _ptr(skin[3]) if skin[3] is not None else None)
+            elif batched:
                 status = lib.moss_rasterize_forward_batch(stream, C.byref(sc), V, st.views, call_flags, color.data_ptr(),
                                                           depth.data_ptr(), alpha.data_ptr(), _ptr(radii), C.byref(nr))
             else:
@@ -201,6 +210,8 @@ def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_p
         st.ws, st.binning, st.ckpt, st.flags, st.num_rendered = ws, binning, ckpt, flags, nr.value
         # tensors whose device pointers sit in the scene struct must outlive the backward
         st.keep = (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp) + tuple(t for c in cams for t in c)
+        if skin is not None:
+            st.keep = st.keep + (skin[0],) + tuple(skin[1])
     return color, radii, depth, alpha, st
 
 
