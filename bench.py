@@ -296,6 +296,34 @@ class OursHarness:
             if float(ok) == 0.0:
                 self.peer = None
             self.collective_kind = self.peer.kind if self.peer is not None else "nccl all_reduce"
+            # Two peer-memory exchanges exist: "push" (fused into the backward: rows stored into their owner's staging area,
+            # one gather kernel) and "pull" (one kernel behind the backward: flag barrier, NVLS multimem.ld_reduce / peer
+            # loads, multimem.st, flag barrier).  Both are two NVLink hops and two flag phases; which one is shorter depends
+            # on the world size and the switch, so MOSS_EXCHANGE=auto times both on this job's payload and keeps the faster.
+            self.exchange_mode, self.exchange_us = "push", None
+            if self.peer is not None:
+                want = os.environ.get("MOSS_EXCHANGE", "auto")
+                if want == "auto":
+                    n = grad_layout(self.P, 16 if has_sh else 0, has_sh, has_sr, V)[1]
+                    t = torch.zeros(2, device=dev, dtype=torch.float64)
+                    for k, fn in enumerate((lambda: self.peer.push_allreduce(n), lambda: self.peer.allreduce(n))):
+                        for _ in range(10):
+                            fn()
+                        torch.cuda.synchronize(dev); dist.barrier(); torch.cuda.synchronize(dev)
+                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        e0.record()
+                        for _ in range(50):
+                            fn()
+                        e1.record(); torch.cuda.synchronize(dev)
+                        t[k] = e0.elapsed_time(e1) / 50 * 1e3
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)          # the same numbers, hence the same choice, on every rank
+                    self.exchange_us = {"push": round(float(t[0]), 2), "pull": round(float(t[1]), 2)}
+                    want = "pull" if float(t[1]) < float(t[0]) else "push"
+                self.exchange_mode = want
+                if want == "pull":
+                    self.collective_kind = ("one exchange kernel behind the backward (flag barrier, "
+                                            + ("multimem.ld_reduce + multimem.st through the switch" if self.peer.multicast_ptr else "peer loads + stores")
+                                            + ", flag barrier)")
 
     # which group does this rank render at step i?  N = 1: the ring in order.  N > 1: a cost-balanced schedule
     # (parallel.balanced_view_schedule) from a short calibration pass, so that the ranks of one step wait for views of
@@ -320,8 +348,11 @@ class OursHarness:
         """One step as stream launches of the raw C ABI."""
         color, radii, depth, alpha, st = self.forward(self.rs_of(self.group_of(i)))
         if not self.forward_only:
-            if self.peer is not None and collective:
+            if self.peer is not None and collective and self.exchange_mode == "push":
                 self.M.backward_raw(st, radii, self.gc, self.gd, self.ga, push=self.peer)      # exchange fused into the backward
+            elif self.peer is not None and collective:
+                self.M.backward_raw(st, radii, self.gc, self.gd, self.ga, out=self.peer.tensor)
+                self.peer.allreduce(st.param_grad_numel)
             else:
                 self.M.backward_raw(st, radii, self.gc, self.gd, self.ga)
                 if self.world > 1 and collective:
@@ -338,7 +369,11 @@ class OursHarness:
         g = self.group_of(i)
         gs = self.graphs.get(g)
         if gs is None:
-            gs = self.graphs[g] = GraphedStep(self.devt, self.rs_of(g), (self.gc, self.gd, self.ga), push=self.peer,
+            pull = self.peer is not None and self.exchange_mode == "pull"
+            gs = self.graphs[g] = GraphedStep(self.devt, self.rs_of(g), (self.gc, self.gd, self.ga),
+                                              push=None if pull else self.peer,
+                                              grad_out=self.peer.tensor if pull else None,
+                                              after=(lambda st: self.peer.allreduce(st.param_grad_numel)) if pull else None,
                                               forward_only=self.forward_only)
         gs.replay()
         self.state["st"], self.state["radii"] = gs.state, gs.out[1]
@@ -542,8 +577,11 @@ def run_ours(args, rank, world, dev):
         k = st.param_grad_numel
         ref = st.grad_buf[:k].clone()
         dist.all_reduce(ref)                   # the yardstick: NCCL on the rank-local gradient
-        if h.peer is not None:
+        if h.peer is not None and h.exchange_mode == "push":
             M.backward_raw(st, radii_, h.gc, h.gd, h.ga, flags=det, push=h.peer)
+        elif h.peer is not None:
+            M.backward_raw(st, radii_, h.gc, h.gd, h.ga, flags=det, out=h.peer.tensor)
+            h.peer.allreduce(st.param_grad_numel)
         else:
             h.exchange(st)
         torch.cuda.synchronize(dev)
@@ -557,7 +595,8 @@ def run_ours(args, rank, world, dev):
         exchange_check = {"max_abs_err": err, "max_abs_ref": scale, "rel": err / max(scale, 1e-30),
                           "bit_identical_to_nccl": bool(torch.equal(got, ref)),
                           "bit_identical_across_ranks": bool(float(ident) == 1.0),
-                          "path": ("fused push + gather, " + h.peer.path) if h.peer is not None else "nccl", "numel": int(k)}
+                          "path": (("fused push + gather, " if h.exchange_mode == "push" else "pull kernel, ") + h.peer.path) if h.peer is not None else "nccl",
+                          "standalone_us": getattr(h, "exchange_us", None), "numel": int(k)}
 
     stop.set()
     if h.peer is not None:
