@@ -33,7 +33,7 @@ constexpr int LOSS_R = 5;                        // window radius (window_size =
 constexpr int LOSS_WIN = 2 * LOSS_R + 1;
 constexpr int LOSS_IN = LOSS_T + 4 * LOSS_R;     // 52: input tile edge, two window passes deep
 constexpr int LOSS_MID = LOSS_T + 2 * LOSS_R;    // 42: where the statistics and the derivative maps live
-constexpr int LOSS_THREADS = 256;
+constexpr int LOSS_THREADS = 512;                // 16 warps per tile: the passes are latency-bound, more warps hide it
 constexpr int LOSS_PIX = LOSS_T * LOSS_T / LOSS_THREADS;     // output pixels per thread (4)
 constexpr int LOSS_S3_REP = 10;                  // repeat_time (loss_utils.py:16)
 constexpr int LOSS_S3_W = LOSS_T + 2;            // 34: S3IM map points per row (tile + 1 pixel each side)
@@ -322,14 +322,15 @@ image_losses_kernel(const __grid_constant__ LossArgs a)
 	__syncthreads();
 	if (!s_last) return;
 	__threadfence();
-	// 64 threads per loss: thread t adds blocks t, t+64, ... then a fixed-order tree over the 64 sums
+	// a quarter of the block per loss: thread t adds blocks t, t+G, ... then a fixed-order tree over the G sums
 	{
-		const int q = tid >> 6, t = tid & 63;
+		constexpr int G = LOSS_THREADS / 4;
+		const int q = tid / G, t = tid % G;
 		float s = 0.f;
-		for (int b0 = t; b0 < nblocks; b0 += 64 * 8) {
+		for (int b0 = t; b0 < nblocks; b0 += G * 8) {
 			float x[8];
 #pragma unroll
-			for (int i = 0; i < 8; i++) x[i] = b0 + 64 * i < nblocks ? __ldcg(a.partial + 4 * (size_t)(b0 + 64 * i) + q) : 0.f;
+			for (int i = 0; i < 8; i++) x[i] = b0 + G * i < nblocks ? __ldcg(a.partial + 4 * (size_t)(b0 + G * i) + q) : 0.f;
 #pragma unroll
 			for (int i = 0; i < 8; i++) s += x[i];
 		}
@@ -340,7 +341,15 @@ image_losses_kernel(const __grid_constant__ LossArgs a)
 	__syncthreads();
 	if (tid == 0) {
 		*a.ticket = 0u;
-		const float S1 = s_red[0][0] + s_red[1][0], S2 = s_red[2][0] + s_red[3][0], S3 = s_red[4][0] + s_red[5][0], S4 = s_red[6][0] + s_red[7][0];
+		constexpr int WG = LOSS_THREADS / 32 / 4;       // warps per loss
+		float S[4];
+#pragma unroll
+		for (int q = 0; q < 4; q++) {
+			S[q] = 0.f;
+#pragma unroll
+			for (int w = 0; w < WG; w++) S[q] += s_red[q * WG + w][0];
+		}
+		const float S1 = S[0], S2 = S[1], S3 = S[2], S4 = S[3];
 		const float crop = 3.f * (float)rw * (float)rh;
 		const float l1 = S1 / (3.f * (float)count), l2 = (a.alpha && a.bkgd) ? S2 / (float)count : 0.f;
 		const float ssim = S3 / crop, s3im = 1.f - S4 / (crop * (float)LOSS_S3_REP);
@@ -405,6 +414,7 @@ scale_inplace_kernel(const float* __restrict__ scale, float* __restrict__ a, siz
 	}
 }
 
+static_assert(LOSS_T * LOSS_T % LOSS_THREADS == 0 && (LOSS_THREADS / 4) % 32 == 0, "whole pixels per thread, whole warps per loss");
 static_assert(9 * LOSS_MID * LOSS_S3_W <= LOSS_SM_H + LOSS_SM_D, "the nine S3IM sum maps fit the pass + derivative buffers");
 
 } // namespace moss
