@@ -21,7 +21,7 @@ library's own exchange kernels over NVLink peer memory (weak scaling: views/step
                      reads image + gradients back.  `e2e.value` blocks the host on every call (forward outputs are read
                      back on a side stream during the backward); `e2e.pipelined` keeps two calls in flight.  Both arms
                      run the same two loops (e2e_step / e2e_pipelined).
-  roofline / cpu_baseline / clocks / gpu_launches / extra_workloads / exchange_check: see DESIGN.md "Measurement".
+  roofline / cpu_baseline / clocks / gpu_launches / extra_workloads / front_end / exchange_check: see DESIGN.md "Measurement".
 
 --impl reference : the UNMODIFIED reference CUDA rasterizer (oracle/_ref/diff_gaussian_rasterization, rebuilt for
                    sm_100) through its own Python API on the same inputs, same e2e protocol (the reference has no CPU
@@ -729,6 +729,97 @@ def extra_workloads(dev, steps=20, warmup=3):
     return out
 
 
+def front_end_numbers(dev, iters=30):
+    """The rows of SURVEY.md section 8 around the rasterizer, at ZJU size, so that the driver-recorded line carries them:
+    per-frame SMPL tables (f1), image losses (f3), and the fused skin + rasterize call against the two-call form (NS-a).
+    Kernel times from the library's own event brackets (stream launches, cold L2); every entry point is the public one."""
+    import moss_b200 as M
+    from moss_b200 import _abi, fused as F, losses as ML, skinning as K, synth
+    from tests.scenes import upstream_grads
+    lib = _abi.load()
+    out = {}
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+
+    def measure(step):
+        for _ in range(5):
+            step()
+        torch.cuda.synchronize(dev)
+        lib.moss_profile_enable(1)
+        for _ in range(iters):
+            flush.zero_(); step()
+        torch.cuda.synchronize(dev)
+        prof = _abi.profile_read(); lib.moss_profile_enable(0)
+        return {k: round(v[0] / v[1] * 1e3, 2) for k, v in prof.items() if v[1]}
+    try:
+        body = synth.body()
+        V = body.verts.shape[0]
+        smpl = K.Smpl(body.verts.to(dev), body.shapedirs.to(dev), body.posedirs.t().reshape(V, 3, 207).contiguous().to(dev),
+                      body.J_regressor.to(dev), body.weights.to(dev), body.parents.to(dev))
+        fr = synth.frame_params(9)
+        fr.params["Th"] = torch.zeros(1, 3); fr.params["R"] = torch.eye(3)
+        params = {k: v.to(dev) for k, v in fr.params.items()}
+        big = {k: v.to(dev) for k, v in fr.big_params.items()}
+        params["poses"].requires_grad_(True)
+        cache = K.FrameCache()
+        gA, gpo = torch.randn(24, 4, 4, device=dev), torch.randn(V, 3, device=dev)
+
+        def frame():
+            params["poses"].grad = None
+            ft = K.frame_tables(smpl, params, big, cache=cache)
+            torch.autograd.backward([ft.A_tgt, ft.poseoff_tgt], [gA, gpo])
+        u = measure(frame)
+        out["smpl_frame_tables"] = {"kernel_us": {k: u[k] for k in ("smpl_frame_forward", "smpl_frame_backward")}, "launches": 2,
+                                    "algorithmic_bytes_forward": 4 * (207 * 3 * V + 30 * V + 24 * V + 3 * V + 6 * V)}
+        # fused skin + rasterize vs skin kernel -> HBM -> rasterizer (20 k Gaussians on the SMPL body, 512 x 512)
+        P, W, H = 20000, 512, 512
+        g = synth.gaussians(P, body, seed=synth.SEED + 9)
+        with torch.no_grad():
+            ft = K.frame_tables(smpl, params, big, cache=cache)
+        cam = synth.ring_cameras(23, W, H)[2]
+        rs = M.GaussianRasterizationSettings(**synth.settings_kwargs(cam, torch.zeros(3), 3, 1.0, device=dev))
+        gc = upstream_grads(W, H, depth=False)[0].to(dev)
+        leaf = lambda t: t.to(dev).clone().requires_grad_(True)  # noqa: E731
+        xyz, sc, rot, shs, opac = leaf(g.xyz), leaf(g.scales), leaf(g.rotations), leaf(g.shs), leaf(g.opacities)
+        vid, wts = g.vert_ids.to(dev), body.weights.to(dev)
+        rast = M.GaussianRasterizer(rs)
+
+        def two_call():
+            for t in (xyz, sc, rot, shs, opac):
+                t.grad = None
+            m, cov, _, _, _ = K.skin_and_covariance(xyz, vid, wts, ft, sc, rot, 1.0)
+            c, _, _, _ = rast(means3D=m, means2D=torch.zeros_like(m), shs=shs, colors_precomp=None, opacities=opac, scales=None,
+                              rotations=None, cov3D_precomp=cov)
+            c.backward(gc)
+
+        def one_call():
+            for t in (xyz, sc, rot, shs, opac):
+                t.grad = None
+            c, _, _, _, _ = F.skin_and_rasterize(rs, xyz, vid, wts, ft, sc, rot, opac, shs=shs, return_transforms=False)
+            c.backward(gc)
+        u2, u1 = measure(two_call), measure(one_call)
+        out["fused_skin_rasterize"] = {
+            "two_call_per_gaussian_kernels_us": round(u2["skin_forward"] + u2["preprocess_forward"] + u2["preprocess_backward"] + u2["skin_backward"], 2),
+            "fused_per_gaussian_kernels_us": round(u1["preprocess_forward"] + u1["preprocess_backward"], 2),
+            "two_call_launches": len(u2), "fused_launches": len(u1), "two_call_kernels_sum_us": round(sum(u2.values()), 2),
+            "fused_kernels_sum_us": round(sum(u1.values()), 2), "hbm_bytes_not_moved": P * 36 * 4}
+        # image losses on a render-sized pair with a person-sized crop
+        from tests.golden.make_loss_golden import synth_case
+        box = (W // 4 + 1, H // 9, W - W // 4 - 2, H - H // 7 - 1)
+        image, alpha, gt, bkgd, bound = (torch.from_numpy(a).to(dev) for a in synth_case(W, H, 11, box))
+        bounds = ML.mask_bounds(bound)
+
+        def loss():
+            ig, ag = image.detach().requires_grad_(True), alpha.detach().requires_grad_(True)
+            l, _ = ML.image_losses(ig, ag, gt, bkgd, bound, bounds)
+            l.backward()
+        u = measure(loss)
+        out["image_losses"] = {"kernel_us": u["image_losses"], "image": [W, H], "crop": bounds[:4].tolist(),
+                               "terms": "masked L1 + mask L2 + SSIM + S3IM, values and dL/dimage, dL/dalpha in one launch"}
+    except Exception as e:            # never let an extra take the headline line down
+        out["error"] = f"{type(e).__name__}: {e}"
+    return out
+
+
 # ---------------------------------------------------------------------------------------------------------
 def cpu_baseline(workload, budget_s=25.0):
     """The CPU oracle port on the host cores (reported baseline, not the target).
@@ -1034,6 +1125,7 @@ def main():
         if (args.impl == "ours" and rank == 0 and line is not None and world == 1 and args.workload == "zju"
                 and args.views_per_step == 1 and not args.forward_only and not args.quick and not args.no_extra):
             line["extra_workloads"] = extra_workloads(dev)
+            line["front_end"] = front_end_numbers(dev)
         if rank == 0 and line is not None:
             print(json.dumps(line), flush=True)
     finally:

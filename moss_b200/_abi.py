@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_lib", "libmoss_splat.so")
+LIB_PATH = os.environ.get("MOSS_SPLAT_LIB") or os.path.join(_HERE, "_lib", "libmoss_splat.so")    # override: A/B builds of the same ABI
 
 MOSS_OK = 0
 MOSS_ERR_BINNING_OVERFLOW = 1

@@ -114,8 +114,22 @@ __device__ __forceinline__ int compact_hits(const uint8_t* mask, uint8_t* hits, 
 	return nh;
 }
 
+// Register caps (A/B on B200, tools/ab_libs.sh, profiles/r02_h_ab_regcaps.txt): the compiler's own choice is 96-98
+// registers forward and 128 backward.  80 forward costs nothing (no spills) and buys a resident block: Stress blend
+// forward 412 -> 369 us.  Backward: 96 is spill-free; 80 spills 16-64 bytes but still wins where the blocks are large
+// (4 / 8 warps: 23-view batch 634 -> 595 us, Stress 1004 -> 950 us) and loses on the 2-warp blocks of a single ZJU view
+// (54.5 -> 56.7 us), which therefore stay at 96.  64 forward spills and loses 11 % at ZJU.  -DMOSS_BLEND_*_MAXREG overrides.
+#ifndef MOSS_BLEND_FWD_MAXREG
+#define MOSS_BLEND_FWD_MAXREG 80
+#endif
+#ifndef MOSS_BLEND_BWD_MAXREG
+#define MOSS_BLEND_BWD_MAXREG (NW == 2 ? 96 : 80)
+#endif
+#define MOSS_FWD_REGCAP __maxnreg__(MOSS_BLEND_FWD_MAXREG)
+#define MOSS_BWD_REGCAP __maxnreg__(MOSS_BLEND_BWD_MAXREG)
+
 template <bool CULL, int NW>
-__global__ void __launch_bounds__(32 * NW)
+__global__ void MOSS_FWD_REGCAP
 blend_forward_kernel(const __grid_constant__ ViewBatch vb, GeomWS g, ImageWS im, BinWS b, CkptWS ck,
 	float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_alpha)
 {
@@ -394,7 +408,7 @@ struct BwdSmem {
 };
 
 template <int NW>
-__global__ void __launch_bounds__(32 * NW)
+__global__ void MOSS_BWD_REGCAP
 blend_backward_kernel(const __grid_constant__ ViewBatch vb, GeomWS g, ImageWS im, BinWS b, CkptWS ck,
 	const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepths, const float* __restrict__ dL_dalphas,
 	int deterministic)

@@ -33,12 +33,11 @@ constexpr int LOSS_R = 5;                        // window radius (window_size =
 constexpr int LOSS_WIN = 2 * LOSS_R + 1;
 constexpr int LOSS_IN = LOSS_T + 4 * LOSS_R;     // 52: input tile edge, two window passes deep
 constexpr int LOSS_MID = LOSS_T + 2 * LOSS_R;    // 42: where the statistics and the derivative maps live
-constexpr int LOSS_THREADS = 512;                // 16 warps per tile: the passes are latency-bound, more warps hide it
-constexpr int LOSS_PIX = LOSS_T * LOSS_T / LOSS_THREADS;     // output pixels per thread (4)
+// threads per tile: a template parameter.  The passes are latency-bound, so with few tiles (ZJU: <= 2 per SM) 16 warps
+// per tile hide more of it (116 -> 74 us); with many tiles two resident 8-warp blocks per SM do better (1080p: 328 vs 381 us).
 constexpr int LOSS_S3_REP = 10;                  // repeat_time (loss_utils.py:16)
 constexpr int LOSS_S3_W = LOSS_T + 2;            // 34: S3IM map points per row (tile + 1 pixel each side)
 constexpr int LOSS_S3_VW = LOSS_T + 4;           // 36: columns of the vertical pass the S3IM maps read
-constexpr int LOSS_S3_PTS = (LOSS_MID * LOSS_S3_W + LOSS_THREADS - 1) / LOSS_THREADS;   // S3IM map points per thread (6)
 // shared memory (floats): the two input tiles, the pass buffer (5 maps of 52x42), the derivative maps (3 of 42x42)
 constexpr int LOSS_SM_IN = LOSS_IN * LOSS_IN;
 constexpr int LOSS_SM_H = 5 * LOSS_IN * LOSS_MID;
@@ -83,9 +82,13 @@ __device__ __forceinline__ float ssim_point(float mu1, float mu2, float e11, flo
 	return map;
 }
 
+template <int LOSS_THREADS>
 __global__ void __launch_bounds__(LOSS_THREADS)
 image_losses_kernel(const __grid_constant__ LossArgs a)
 {
+	constexpr int LOSS_PIX = LOSS_T * LOSS_T / LOSS_THREADS;                                  // output pixels per thread
+	constexpr int LOSS_S3_PTS = (LOSS_MID * LOSS_S3_W + LOSS_THREADS - 1) / LOSS_THREADS;     // S3IM map points per thread
+	static_assert(LOSS_T * LOSS_T % LOSS_THREADS == 0 && (LOSS_THREADS / 4) % 32 == 0, "whole pixels per thread, whole warps per loss");
 	extern __shared__ __align__(16) float sm[];
 	float* s_in1 = sm;                                  // [52][52] image tile, zero outside the crop
 	float* s_in2 = s_in1 + LOSS_SM_IN;                  // [52][52] ground truth tile
@@ -414,7 +417,6 @@ scale_inplace_kernel(const float* __restrict__ scale, float* __restrict__ a, siz
 	}
 }
 
-static_assert(LOSS_T * LOSS_T % LOSS_THREADS == 0 && (LOSS_THREADS / 4) % 32 == 0, "whole pixels per thread, whole warps per loss");
 static_assert(9 * LOSS_MID * LOSS_S3_W <= LOSS_SM_H + LOSS_SM_D, "the nine S3IM sum maps fit the pass + derivative buffers");
 
 } // namespace moss

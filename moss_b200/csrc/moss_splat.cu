@@ -951,7 +951,8 @@ int moss_image_losses(void* stream_, const MossImageLoss* k, float* losses, floa
 	int dev = 0;                            // opt in to > 48 KB of dynamic shared memory (the attribute is per device)
 	MOSS_CUDA_TRY(cudaGetDevice(&dev));
 	if (dev >= 0 && dev < MAX_DEVICES && !g_loss_attr_set[dev].load(std::memory_order_acquire)) {
-		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
+		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
+		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
 		g_loss_attr_set[dev].store(true, std::memory_order_release);
 	}
 	LossArgs a;
@@ -962,7 +963,9 @@ int moss_image_losses(void* stream_, const MossImageLoss* k, float* losses, floa
 	a.ticket = (unsigned*)k->scratch; a.partial = (float*)((char*)k->scratch + 16);
 	const dim3 grid((k->W + LOSS_T - 1) / LOSS_T, (k->H + LOSS_T - 1) / LOSS_T);
 	{ MOSS_STAGE(MOSS_STAGE_IMAGE_LOSSES, stream);
-		image_losses_kernel<<<grid, LOSS_THREADS, LOSS_DYN_SMEM, stream>>>(a); }
+		// few tiles (<= two per SM): 16 warps per tile; many tiles: two resident 8-warp blocks per SM
+		if (grid.x * grid.y <= 2 * 148) image_losses_kernel<512><<<grid, 512, LOSS_DYN_SMEM, stream>>>(a);
+		else image_losses_kernel<256><<<grid, 256, LOSS_DYN_SMEM, stream>>>(a); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }

@@ -225,8 +225,16 @@ struct SkinFused {
 };
 
 // grid = (ceil(P / PRE_THREADS), V): block row v preprocesses the Gaussians for view v ("virtual Gaussian" v*P + i).
+#ifndef MOSS_PRE_FWD_MAXREG
+#define MOSS_PRE_FWD_MAXREG 0
+#endif
+#if MOSS_PRE_FWD_MAXREG > 0
+#define MOSS_PRE_FWD_REGCAP __maxnreg__(SKIN ? 255 : MOSS_PRE_FWD_MAXREG)
+#else
+#define MOSS_PRE_FWD_REGCAP __launch_bounds__(PRE_THREADS)
+#endif
 template <bool SKIN>
-__global__ void __launch_bounds__(PRE_THREADS)
+__global__ void MOSS_PRE_FWD_REGCAP
 preprocess_forward_kernel(const __grid_constant__ ViewBatch vb,
 	const float* __restrict__ means3D, const float* __restrict__ shs, const float* __restrict__ colors_precomp,
 	const float* __restrict__ opacities, const float* __restrict__ scales, const float* __restrict__ rotations,

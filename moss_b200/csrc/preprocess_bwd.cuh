@@ -43,8 +43,16 @@ struct SkinGradOut {
 
 // grid = (ceil(P / PRE_THREADS), V).  SKIN: single view, no exchange; means3D / cov3D are recomputed from the skinning
 // inputs and dL/dmeans3D, dL/dcov3D go straight into the skinning backward (skin.cuh) without touching HBM.
+#ifndef MOSS_PRE_BWD_MAXREG
+#define MOSS_PRE_BWD_MAXREG 0
+#endif
+#if MOSS_PRE_BWD_MAXREG > 0
+#define MOSS_PRE_BWD_REGCAP __maxnreg__(SKIN ? 255 : MOSS_PRE_BWD_MAXREG)
+#else
+#define MOSS_PRE_BWD_REGCAP __launch_bounds__(PRE_THREADS)
+#endif
 template <bool SKIN>
-__global__ void __launch_bounds__(PRE_THREADS)
+__global__ void MOSS_PRE_BWD_REGCAP
 preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	const float* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
 	const float* __restrict__ scales, const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,

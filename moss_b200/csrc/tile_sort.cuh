@@ -320,7 +320,15 @@ __device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 ra
 
 // One block per tile: block b sorts the (b / V)-th deepest tile of view b % V (deepest tiles of every view first).
 // `tile` handed to the sort is the tile's index INSIDE its view (what the reference's 64-bit keys carry).
-__global__ void __launch_bounds__(TILE_PIX)
+#ifndef MOSS_SORT_MAXREG
+#define MOSS_SORT_MAXREG 0
+#endif
+#if MOSS_SORT_MAXREG > 0
+#define MOSS_SORT_REGCAP __maxnreg__(MOSS_SORT_MAXREG)
+#else
+#define MOSS_SORT_REGCAP __launch_bounds__(TILE_PIX)
+#endif
+__global__ void MOSS_SORT_REGCAP
 tile_sort_kernel(ImageWS im, BinWS b, CkptWS ck, int T, int V)
 {
 	extern __shared__ __align__(16) unsigned char sort_smem_raw[];

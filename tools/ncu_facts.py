@@ -5,7 +5,8 @@ import collections, csv, io, json, os, subprocess, sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NAMES = ("preprocess_forward", "tile_scan", "scatter_keys", "tile_sort", "blend_forward", "blend_backward", "preprocess_backward",
-         "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw")
+         "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw", "sum_views", "smpl_frame_forward",
+         "smpl_frame_backward", "image_losses")
 FACTS = {"issue_active_pct": "smsp__issue_active.avg.pct_of_peak_sustained_active",
          "warps_active_pct": "sm__warps_active.avg.pct_of_peak_sustained_active",
          "pipe_fma_pct": "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
@@ -16,7 +17,8 @@ SCALE = {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6, "byte": 1.0, "Kbyte": 1e3, 
 
 def main():
     rep, workload = sys.argv[1], sys.argv[2]
-    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    # a report, or its `ncu -i report --page raw --csv` export (what travels back from the GPU box when reports are large)
+    out = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     hdr, units = rows[0], rows[1]
     ki = hdr.index("Kernel Name")
