@@ -287,8 +287,10 @@ public:
 		Tensor dopacity = view_of(l.opacity, P, {P, 1}), dcolors = view_of(l.colors, 3 * P, {P, 3});
 		Tensor dmeans2D = view_of(l.means2D, 3 * P * V, shape({P, 3})), dconic = view_of(l.conic, 4 * P * V, shape({P, 2, 2}));
 		Tensor dsh = has_sh ? view_of(l.sh, 3 * M * P, {P, M, 3}) : torch::zeros({P, 0, 3}, f32);
-		Tensor dscales = has_sr ? view_of(l.scales, 3 * P, {P, 3}) : torch::zeros({P, 3}, f32);
-		Tensor drot = has_sr ? view_of(l.rot, 4 * P, {P, 4}) : torch::zeros({P, 4}, f32);
+		// absent inputs get an undefined gradient (the reference zero-fills two tensors per backward for them,
+		// DGR/rasterize_points.cu:164-165: two fill launches nobody reads)
+		Tensor dscales = has_sr ? view_of(l.scales, 3 * P, {P, 3}) : Tensor();
+		Tensor drot = has_sr ? view_of(l.rot, 4 * P, {P, 4}) : Tensor();
 		void* stream = (void*)c10::cuda::getCurrentCUDAStream(dev.index()).stream();
 		Tensor tmp;
 		size_t tbytes = 0;
