@@ -143,13 +143,13 @@ def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_p
         # three independent output tensors, like the reference (DGR/rasterize_points.cu:68-71): callers edit renders
         # in place (render_ZJU.py), which autograd refuses on views of a shared multi-output buffer
         lead = (V,) if batched else ()
-        color = torch.empty(lead + (3, H, W), dtype=torch.float32, device=dev)
-        depth = torch.empty(lead + (1, H, W), dtype=torch.float32, device=dev)
-        alpha = torch.empty(lead + (1, H, W), dtype=torch.float32, device=dev)
-        radii = torch.empty(lead + (P,), dtype=torch.int32, device=dev)
+        color = _alloc(lead + (3, H, W), torch.float32, dev)
+        depth = _alloc(lead + (1, H, W), torch.float32, dev)
+        alpha = _alloc(lead + (1, H, W), torch.float32, dev)
+        radii = _alloc(lead + (P,), torch.int32, dev)
         gbytes = _align(lib.moss_geom_workspace_bytes_batch(P, V))
         ibytes = lib.moss_image_workspace_bytes_batch(W, H, V)
-        ws = torch.empty((gbytes + ibytes,), dtype=torch.uint8, device=dev)
+        ws = _alloc((gbytes + ibytes,), torch.uint8, dev)
         key = (P, W, H, V, dev.index)
         cap = _capacity_hint.get(key, 0)
         cap = max(int(cap * 1.25) + 4096, (4 * P + 4096) * V)
@@ -181,12 +181,12 @@ def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_p
         want_ckpt = _want_ckpt(W, H, V)
         while True:
             bbytes = lib.moss_binning_workspace_bytes_ex(cap, export)
-            binning = torch.empty((bbytes,), dtype=torch.uint8, device=dev)
+            binning = _alloc((bbytes,), torch.uint8, dev)
             sc.binning_ws = binning.data_ptr(); sc.binning_bytes = bbytes
             ckpt = None
             if want_ckpt:
                 cbytes = lib.moss_ckpt_workspace_bytes_batch(lib.moss_binning_capacity(bbytes, export), W, H, V)
-                ckpt = torch.empty((cbytes,), dtype=torch.uint8, device=dev)
+                ckpt = _alloc((cbytes,), torch.uint8, dev)
                 sc.ckpt_ws = ckpt.data_ptr(); sc.ckpt_bytes = cbytes
             if skin is not None:
                 status = lib.moss_skin_rasterize_forward(stream, C.byref(sc), C.byref(skin[0]), call_flags, color.data_ptr(),
@@ -249,6 +249,12 @@ def grad_layout(P, M, has_sh, has_sr, V=1):
     return lay, param_numel, zero_from, o
 
 
+def _alloc(shape, dtype, dev):
+    """Every buffer the kernels write is allocated here; tests/test_guard_gpu.py swaps in an allocator that surrounds each
+    one with sentinel bytes (the stand-in for compute-sanitizer's memcheck, which is closed on this pool)."""
+    return torch.empty(shape, dtype=dtype, device=dev)
+
+
 _zeros = {}
 
 
@@ -296,7 +302,7 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
             if push.tensor.numel() < total:
                 raise RuntimeError(f"PeerGradBuffer holds {push.tensor.numel()} floats, this call needs {total}")
             out = push.tensor
-        buf = out if out is not None else torch.empty((total,), dtype=torch.float32, device=dev)
+        buf = out if out is not None else _alloc((total,), torch.float32, dev)
 
         def v(name, *shape):
             o, n = lay[name]
@@ -316,14 +322,14 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
                 _ptr(dsh) if has_sh else None, _ptr(dscales) if has_sr else None, _ptr(drot) if has_sr else None)
         if push is not None:
             tbytes = lib.moss_batch_grad_workspace_bytes(P, M, V) if st.batched else 0
-            tmp = torch.empty((max(tbytes, 16),), dtype=torch.uint8, device=dev)
+            tmp = _alloc((max(tbytes, 16),), torch.uint8, dev)
             status = lib.moss_rasterize_backward_push(
                 stream, C.byref(sc), V, st.views if st.batched else None, flags | st.flags, _ptr(radii),
                 grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha), *outs, tmp.data_ptr(), tbytes,
                 C.byref(push.descriptor(param_numel)))
         elif st.batched:
             tbytes = lib.moss_batch_grad_workspace_bytes(P, M, V)
-            tmp = torch.empty((max(tbytes, 16),), dtype=torch.uint8, device=dev)
+            tmp = _alloc((max(tbytes, 16),), torch.uint8, dev)
             status = lib.moss_rasterize_backward_batch(
                 stream, C.byref(sc), V, st.views, flags | st.flags, _ptr(radii),
                 grad_color.data_ptr(), _ptr(grad_depth), _ptr(grad_alpha), *outs, tmp.data_ptr(), tbytes)
