@@ -43,14 +43,13 @@ struct SkinGradOut {
 
 // grid = (ceil(P / PRE_THREADS), V).  SKIN: single view, no exchange; means3D / cov3D are recomputed from the skinning
 // inputs and dL/dmeans3D, dL/dcov3D go straight into the skinning backward (skin.cuh) without touching HBM.
-#ifndef MOSS_PRE_BWD_MAXREG
-#define MOSS_PRE_BWD_MAXREG 0
+// Register caps: none below the architectural 255 pays.  Plain kernel: 80-96 spill and lose 6-13 % at Stress
+// (profiles/r02_h_ab_regcaps_preprocess_sort.txt).  Fused (SKIN) variant: 233 registers = two resident blocks; a cap
+// of 168 buys a third, spills 136 bytes and trades 100 k Gaussians 54.8 -> 49.7 us for 20 k 25.3 -> 27.2 us.
+#ifndef MOSS_PRE_BWD_SKIN_MAXREG
+#define MOSS_PRE_BWD_SKIN_MAXREG 255
 #endif
-#if MOSS_PRE_BWD_MAXREG > 0
-#define MOSS_PRE_BWD_REGCAP __maxnreg__(SKIN ? 255 : MOSS_PRE_BWD_MAXREG)
-#else
-#define MOSS_PRE_BWD_REGCAP __launch_bounds__(PRE_THREADS)
-#endif
+#define MOSS_PRE_BWD_REGCAP __maxnreg__(SKIN ? MOSS_PRE_BWD_SKIN_MAXREG : 255)
 template <bool SKIN>
 __global__ void MOSS_PRE_BWD_REGCAP
 preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,

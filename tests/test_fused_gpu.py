@@ -40,7 +40,7 @@ def _rel(a, b):
     return float((a - b).norm() / b.norm().clamp_min(1e-30))
 
 
-CASES = [(20000, 512, 512, 9, False), (5001, 200, 120, 4, True), (129, 64, 48, 5, True)]
+CASES = [(20000, 512, 512, 9, False), (5001, 200, 120, 4, True), (129, 64, 48, 5, True), (100000, 1024, 1024, 3, True)]
 
 
 @pytest.mark.parametrize("P,W,H,seed,with_delta", CASES)
