@@ -321,6 +321,14 @@ size_t moss_sizeof_adam_group(void);
  * search, smallest squared distance, lowest index on ties.  xyz [P,3], verts [V,3] -> vert_ids int32 [P] and,
  * optionally (NULL to skip), dist float [P] (Euclidean).  V >= 1. */
 int moss_nearest_vertex(void* stream, int P, const float* xyz, int V, const float* verts, int* vert_ids, float* dist);
+/* The same search through a uniform 32^3 grid over the vertices (constant for a run: build once, query every render).
+ * Identical answers to moss_nearest_vertex() -- same distance expression, same (distance, index) order, ties included --
+ * while a Gaussian near the surface examines a few dozen vertices instead of all V.  `grid`: caller-owned device
+ * buffer of >= moss_vertex_grid_bytes(V) bytes, 16-byte aligned, written by the build and read by the queries. */
+size_t moss_vertex_grid_bytes(int V);
+int moss_vertex_grid_build(void* stream, int V, const float* verts, void* grid, size_t grid_bytes);
+int moss_nearest_vertex_grid(void* stream, int P, const float* xyz, int V, const void* grid, size_t grid_bytes,
+                             int* vert_ids, float* dist);
 
 /* Data-parallel exchange step (no reference counterpart: MOSS trains on one GPU).  Sum, in
  * place and on every rank, `numel` floats starting `offset_floats` (multiple of 4) into a SYMMETRIC buffer: the same

@@ -38,7 +38,7 @@ SYMBOLS = [
     "moss_geom_workspace_bytes_batch", "moss_image_workspace_bytes_batch", "moss_ckpt_workspace_bytes_batch",
     "moss_batch_grad_workspace_bytes", "moss_rasterize_forward_batch", "moss_rasterize_backward_batch", "moss_sizeof_view",
     "moss_export_state_batch", "moss_push_slice_floats", "moss_sizeof_push", "moss_rasterize_backward_push", "moss_push_allreduce",
-    "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
+    "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_vertex_grid_bytes", "moss_vertex_grid_build", "moss_nearest_vertex_grid", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
     "moss_smpl_frame_scratch_bytes", "moss_sizeof_smpl_frame", "moss_smpl_frame_forward", "moss_smpl_frame_backward", "moss_smpl_joint_tables", "moss_skin_rasterize_forward", "moss_skin_rasterize_backward",
     "moss_image_losses_scratch_bytes", "moss_sizeof_image_loss", "moss_image_losses", "moss_mask_bounds", "moss_scale_gradients",
 ]
@@ -196,6 +196,12 @@ def load():
     lib.moss_densify_stats.argtypes = [vp, C.c_int, vp, vp, vp, vp, vp]
     lib.moss_nearest_vertex.restype = C.c_int
     lib.moss_nearest_vertex.argtypes = [vp, C.c_int, vp, C.c_int, vp, vp, vp]
+    lib.moss_vertex_grid_bytes.restype = C.c_size_t
+    lib.moss_vertex_grid_bytes.argtypes = [C.c_int]
+    lib.moss_vertex_grid_build.restype = C.c_int
+    lib.moss_vertex_grid_build.argtypes = [vp, C.c_int, vp, vp, C.c_size_t]
+    lib.moss_nearest_vertex_grid.restype = C.c_int
+    lib.moss_nearest_vertex_grid.argtypes = [vp, C.c_int, vp, C.c_int, vp, C.c_size_t, vp, vp]
     lib.moss_skin_forward.restype = C.c_int
     lib.moss_skin_forward.argtypes = [vp, C.POINTER(MossSkin)] + [vp] * 5
     lib.moss_skin_backward.restype = C.c_int

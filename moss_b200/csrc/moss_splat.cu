@@ -1009,6 +1009,31 @@ int moss_nearest_vertex(void* stream_, int P, const float* xyz, int V, const flo
 	return MOSS_OK;
 }
 
+size_t moss_vertex_grid_bytes(int V) { return V < 1 ? 0 : vertex_grid_bytes(V); }
+
+int moss_vertex_grid_build(void* stream_, int V, const float* verts, void* grid, size_t grid_bytes)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (V < 1 || !verts || !grid || ((uintptr_t)grid & 15) || grid_bytes < vertex_grid_bytes(V)) return MOSS_ERR_INVALID_ARGUMENT;
+	{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
+		vertex_grid_build_kernel<<<1, GRID_BUILD_THREADS, 0, stream>>>(V, verts, vertex_grid_view(grid, V)); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+int moss_nearest_vertex_grid(void* stream_, int P, const float* xyz, int V, const void* grid, size_t grid_bytes,
+	int* vert_ids, float* dist)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (P < 0 || V < 1 || !grid || ((uintptr_t)grid & 15) || grid_bytes < vertex_grid_bytes(V)) return MOSS_ERR_INVALID_ARGUMENT;
+	if (P == 0) return MOSS_OK;
+	if (!xyz || !vert_ids) return MOSS_ERR_INVALID_ARGUMENT;
+	{ MOSS_STAGE(MOSS_STAGE_NEAREST, stream);
+		nearest_vertex_grid_kernel<<<(unsigned)(((size_t)P * GRID_GW + GRID_QUERY_THREADS - 1) / GRID_QUERY_THREADS), GRID_QUERY_THREADS, 0, stream>>>(P, xyz, vertex_grid_view(const_cast<void*>(grid), V), vert_ids, dist); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
 int moss_densify_stats(void* stream_, int P, const int* radii, const float* dL_dmean2D, float* xyz_gradient_accum,
 	float* denom, float* max_radii2D)
 {

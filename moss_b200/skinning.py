@@ -346,13 +346,48 @@ def skin_and_covariance(xyz, vert_ids, weights, ft: FrameTables, scaling=None, r
     return m, (c if c.numel() else None), tr, bw, (tl if return_transl else None)
 
 
-def nearest_vertex(xyz, t_vertices, return_distance=False):
+class VertexGrid:
+    """A uniform grid over a vertex set (``moss_vertex_grid_build``): build once for the big-pose world vertices -- they are
+    constants of a run (scene/dataset_readers.py:586-601) -- and every later nearest-vertex query examines a few dozen
+    vertices instead of all of them, with answers identical to the exhaustive search."""
+
+    def __init__(self, t_vertices):
+        lib = _abi.load()
+        v = _dev_f32(t_vertices.detach().reshape(-1, 3), "t_vertices")
+        if v.shape[0] < 1:
+            raise RuntimeError("t_vertices is empty")
+        self.V, self.device = v.shape[0], v.device
+        nbytes = lib.moss_vertex_grid_bytes(self.V)
+        with torch.cuda.device(v.device):
+            self.buf = torch.empty((nbytes,), dtype=torch.uint8, device=v.device)
+            st = lib.moss_vertex_grid_build(torch.cuda.current_stream(v.device).cuda_stream, self.V, _p(v), _p(self.buf), nbytes)
+        _abi.check(st, "moss_vertex_grid_build")
+        self.src = t_vertices            # keeps the identity the cache is keyed on alive
+
+
+_vertex_grids = {}      # (data_ptr, version, shape) of a vertex tensor -> VertexGrid
+
+
+def _grid_for(t_vertices):
+    key = (t_vertices.data_ptr(), t_vertices._version, tuple(t_vertices.shape))
+    g = _vertex_grids.get(key)
+    if g is None or g.src is not t_vertices:
+        if len(_vertex_grids) > 8:
+            _vertex_grids.clear()
+        g = _vertex_grids[key] = VertexGrid(t_vertices)
+    return g
+
+
+def nearest_vertex(xyz, t_vertices, return_distance=False, grid="auto"):
     """int32 [P]: index of the nearest SMPL vertex of every Gaussian -- what the reference asks knn_cuda for on every
     render, ``_, vert_ids = self.knn(smpl_pts.float(), query_pts.float())`` with ``KNN(k=1, transpose_mode=True)``
     (scene/gaussian_model.py:85, :827).  ``xyz`` [P,3] or [1,P,3], ``t_vertices`` [V,3] or [1,V,3] (the big-pose world
     vertices).  With ``return_distance`` also the Euclidean distance [P] (``distance, _ = self.knn(...)``, :657).
     Gaussians move little between densifications, so a training loop may keep the result and refresh it only when the
-    set of Gaussians changes."""
+    set of Gaussians changes.
+    ``grid``: "auto" (default) searches through a ``VertexGrid`` of ``t_vertices``, built on first use and cached while the
+    same tensor object is passed unmodified; a ``VertexGrid`` instance uses that one; None runs the exhaustive kernel.
+    All three give the same answer."""
     lib = _abi.load()
     q = _dev_f32(xyz.detach().reshape(-1, 3), "xyz")
     v = _dev_f32(t_vertices.detach().reshape(-1, 3), "t_vertices")
@@ -363,7 +398,15 @@ def nearest_vertex(xyz, t_vertices, return_distance=False):
         raise RuntimeError("t_vertices is empty")
     ids = torch.empty((P,), dtype=torch.int32, device=q.device)
     dist = torch.empty((P,), dtype=torch.float32, device=q.device) if return_distance else None
+    if isinstance(grid, str) and grid == "auto":
+        grid = _grid_for(t_vertices) if V >= 64 else None
     with torch.cuda.device(q.device):
-        status = lib.moss_nearest_vertex(torch.cuda.current_stream(q.device).cuda_stream, P, _p(q), V, _p(v), _p(ids), _p(dist))
+        stream = torch.cuda.current_stream(q.device).cuda_stream
+        if grid is not None:
+            if grid.V != V or grid.device != q.device:
+                raise RuntimeError("the VertexGrid was built for another vertex set")
+            status = lib.moss_nearest_vertex_grid(stream, P, _p(q), V, _p(grid.buf), grid.buf.numel(), _p(ids), _p(dist))
+        else:
+            status = lib.moss_nearest_vertex(stream, P, _p(q), V, _p(v), _p(ids), _p(dist))
     _abi.check(status, "moss_nearest_vertex")
     return (ids, dist) if return_distance else ids

@@ -184,3 +184,52 @@ def test_nearest_vertex_ties_take_the_lowest_index():
     assert ids == [1, 1, 0, 8, 6]
     # equidistant from vertex 0 and vertex 1 (exactly representable): lowest index
     assert K.nearest_vertex(torch.tensor([[0.5, 0., 0.]], device=DEV), v.to(DEV)).item() == 0
+
+
+# ---- the grid search gives the exhaustive search's answers ---------------------------------------------------------------
+def _both(q, v):
+    qd, vd = q.to(DEV), v.to(DEV)
+    a, da = K.nearest_vertex(qd, vd, return_distance=True, grid=None)
+    g = K.VertexGrid(vd)
+    b, db = K.nearest_vertex(qd, vd, return_distance=True, grid=g)
+    assert torch.equal(a, b), int((a != b).sum())
+    assert torch.equal(da, db)
+    return a
+
+
+@pytest.mark.parametrize("P,V,spread", [(20000, 6890, 0.03), (100000, 6890, 0.03), (5000, 6890, 2.0), (3000, 64, 0.5), (1000, 1, 1.0),
+                                        (4097, 1025, 0.0)])
+def test_grid_search_equals_exhaustive_search(P, V, spread):
+    """Near-surface queries (what training sees), far-away queries (rings out to the whole grid), a grid of one vertex,
+    and queries ON the vertices (zero distance, the lowest index among duplicates)."""
+    body = synth.body()
+    g = torch.Generator().manual_seed(P + 31 * V)
+    v = body.verts[torch.randperm(body.verts.shape[0], generator=g)[:V]].clone() if V <= body.verts.shape[0] else torch.randn(V, 3, generator=g)
+    if V >= 1025:
+        v[V // 2:V // 2 + 50] = v[:50]                          # duplicated vertices: ties by index
+    q = v[torch.randint(0, V, (P,), generator=g)] + spread * torch.randn(P, 3, generator=g)
+    ids = _both(q, v)
+    if P * V <= 150_000_000:            # the fp64 yardstick builds a P x V matrix on the host
+        _check_nearest(q, v, ids)
+
+
+def test_grid_search_degenerate_sets_and_auto_cache():
+    # all vertices in one plane / on one point; NaN and infinite queries
+    v = torch.zeros(300, 3); v[:, 0] = torch.linspace(-1, 1, 300)
+    q = torch.randn(500, 3)
+    q[0] = float("nan"); q[1, 2] = float("inf"); q[2] = torch.tensor([1e20, -1e20, 0.0])
+    _both(q, v)
+    _both(torch.randn(100, 3), torch.ones(70, 3))
+    # the default path builds the grid once per vertex tensor and rebuilds it after an in-place edit
+    body = synth.body()
+    vd = body.verts.to(DEV)
+    qd = (body.verts[:4000] + 0.02 * torch.randn(4000, 3)).to(DEV)
+    a = K.nearest_vertex(qd, vd)
+    g1 = K._grid_for(vd)
+    assert K._grid_for(vd) is g1
+    assert torch.equal(a, K.nearest_vertex(qd, vd, grid=None))
+    vd.add_(0.5)
+    assert K._grid_for(vd) is not g1
+    assert torch.equal(K.nearest_vertex(qd, vd), K.nearest_vertex(qd, vd, grid=None))
+    with pytest.raises(RuntimeError, match="another vertex set"):
+        K.nearest_vertex(qd, vd[:100], grid=g1)
