@@ -32,6 +32,7 @@ extern "C" {
 #define MOSS_ERR_INVALID_ARGUMENT 2
 #define MOSS_ERR_WORKSPACE_TOO_SMALL 3
 #define MOSS_ERR_CUDA            4   /* a CUDA runtime error; see moss_last_cuda_error() */
+#define MOSS_ERR_STATIC_SCRATCH_LIMIT 5  /* moss_image_losses_static(): image larger than the library's static scratch */
 
 /* flags */
 #define MOSS_FLAG_ASYNC       1u  /* never block the host: *num_rendered is set to -1; the instance count and an
@@ -284,6 +285,21 @@ size_t moss_sizeof_image_loss(void);
 /* losses: DEVICE float[5] = Ll1, mask_loss, ssim, s3im_loss, weighted total.  dL_dimage [3,H,W] and dL_dalpha [H,W] are
  * fully written (zero where no term reaches), either may be NULL. */
 int moss_image_losses(void* stream, const MossImageLoss* loss, float* losses, float* dL_dimage, float* dL_dalpha);
+/* moss_image_losses() for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  This entry point has NO counterpart in the reference.
+ * Same inputs, outputs and results as moss_image_losses(), but the scratch memory
+ * (ticket + per-tile partial sums) is a file-scope static __device__ array inside the library instead of a caller
+ * buffer: loss->scratch and loss->scratch_bytes are IGNORED (may be NULL / 0), and the call performs no cudaMalloc,
+ * cudaFree or any other allocating call.  Limit: at most MOSS_IMAGE_LOSSES_STATIC_MAX_TILES tiles of 32x32 pixels,
+ * ceil(W/32) * ceil(H/32) <= 4096 (e.g. 2048 x 2048); a larger image returns MOSS_ERR_STATIC_SCRATCH_LIMIT and launches
+ * nothing.  Every GPU that loads the library holds the array (MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES = 65 792 bytes)
+ * until the process exits.  All calls on one device share it: calls that may OVERLAP on the GPU (different streams
+ * without an ordering between them) race on it and give undefined results -- serialise them or use moss_image_losses()
+ * with one scratch buffer per stream.  The part that must start at zero (the ticket) is cleared on `stream` by every
+ * call, so an aborted earlier call leaves nothing behind. */
+#define MOSS_IMAGE_LOSSES_STATIC_MAX_TILES 4096
+#define MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES (256 + 16 * MOSS_IMAGE_LOSSES_STATIC_MAX_TILES)
+int moss_image_losses_static(void* stream, const MossImageLoss* loss, float* losses, float* dL_dimage, float* dL_dalpha);
 /* out: DEVICE int[8]; out[0..4] = x, y, w, h of the bounding rectangle of the non-zero pixels of mask (as
  * cv2.boundingRect(mask.astype(np.uint8)), (0,0,0,0) if none) and the number of pixels equal to 1; out[5..7] scratch. */
 int moss_mask_bounds(void* stream, int W, int H, const float* mask, int* out);

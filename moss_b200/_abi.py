@@ -15,6 +15,7 @@ MOSS_ERR_BINNING_OVERFLOW = 1
 MOSS_ERR_INVALID_ARGUMENT = 2
 MOSS_ERR_WORKSPACE_TOO_SMALL = 3
 MOSS_ERR_CUDA = 4
+MOSS_ERR_STATIC_SCRATCH_LIMIT = 5
 
 FLAG_ASYNC = 1
 FLAG_REBIN = 2
@@ -40,7 +41,7 @@ SYMBOLS = [
     "moss_export_state_batch", "moss_push_slice_floats", "moss_sizeof_push", "moss_rasterize_backward_push", "moss_push_allreduce",
     "moss_skin_forward", "moss_skin_backward", "moss_sizeof_skin", "moss_nearest_vertex", "moss_vertex_grid_bytes", "moss_vertex_grid_build", "moss_nearest_vertex_grid", "moss_densify_stats", "moss_adamw_step", "moss_sizeof_adam_group", "moss_peer_signal_bytes", "moss_peer_allreduce",
     "moss_smpl_frame_scratch_bytes", "moss_sizeof_smpl_frame", "moss_smpl_frame_forward", "moss_smpl_frame_backward", "moss_smpl_joint_tables", "moss_skin_rasterize_forward", "moss_skin_rasterize_backward",
-    "moss_image_losses_scratch_bytes", "moss_sizeof_image_loss", "moss_image_losses", "moss_mask_bounds", "moss_scale_gradients",
+    "moss_image_losses_scratch_bytes", "moss_sizeof_image_loss", "moss_image_losses", "moss_image_losses_static", "moss_mask_bounds", "moss_scale_gradients",
 ]
 STAGE_COUNT = 19
 
@@ -224,6 +225,8 @@ def load():
     lib.moss_sizeof_image_loss.restype = C.c_size_t
     lib.moss_image_losses.restype = C.c_int
     lib.moss_image_losses.argtypes = [vp, C.POINTER(MossImageLoss), vp, vp, vp]
+    lib.moss_image_losses_static.restype = C.c_int
+    lib.moss_image_losses_static.argtypes = [vp, C.POINTER(MossImageLoss), vp, vp, vp]
     lib.moss_mask_bounds.restype = C.c_int
     lib.moss_mask_bounds.argtypes = [vp, C.c_int, C.c_int, vp, vp]
     lib.moss_scale_gradients.restype = C.c_int

@@ -306,6 +306,7 @@ const char* moss_error_string(int status)
 	case MOSS_ERR_INVALID_ARGUMENT: return "invalid argument";
 	case MOSS_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
 	case MOSS_ERR_CUDA: return "CUDA runtime error";
+	case MOSS_ERR_STATIC_SCRATCH_LIMIT: return "image exceeds the static scratch of moss_image_losses_static (at most 4096 tiles of 32x32 pixels, e.g. 2048 x 2048); use moss_image_losses with a caller buffer";
 	default: return "unknown status";
 	}
 }
@@ -966,6 +967,50 @@ int moss_image_losses(void* stream_, const MossImageLoss* k, float* losses, floa
 		// few tiles (<= two per SM): 16 warps per tile; many tiles: two resident 8-warp blocks per SM
 		if (grid.x * grid.y <= 2 * 148) image_losses_kernel<512><<<grid, 512, LOSS_DYN_SMEM, stream>>>(a);
 		else image_losses_kernel<256><<<grid, 256, LOSS_DYN_SMEM, stream>>>(a); }
+	MOSS_CHECK_LAUNCH(stream, 0);
+	return MOSS_OK;
+}
+
+// ---- image losses without any allocation (no reference counterpart) ----
+// The scratch of image_losses_kernel (ticket at +0, per-tile partial sums at +16) lives in a file-scope device array.
+// In host code `g_loss_static_scratch` is only a stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device with that device current, and is what the kernel receives.
+static __device__ __align__(256) unsigned char g_loss_static_scratch[MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES];
+static std::atomic<void*> g_loss_static_ptr[MAX_DEVICES];
+static_assert(MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES >= 16 + 16 * MOSS_IMAGE_LOSSES_STATIC_MAX_TILES, "static scratch holds ticket + partial sums");
+
+int moss_image_losses_static(void* stream_, const MossImageLoss* k, float* losses, float* dL_dimage, float* dL_dalpha)
+{
+	cudaStream_t stream = (cudaStream_t)stream_;
+	if (!k || k->W < 1 || k->H < 1 || !k->image || !k->gt_image || !k->rect || !losses) return MOSS_ERR_INVALID_ARGUMENT;
+	if (k->w_mask != 0.f && (!k->alpha || !k->bkgd_mask)) return MOSS_ERR_INVALID_ARGUMENT;
+	const long long tiles = (long long)((k->W + LOSS_T - 1) / LOSS_T) * (long long)((k->H + LOSS_T - 1) / LOSS_T);
+	if (tiles > MOSS_IMAGE_LOSSES_STATIC_MAX_TILES) return MOSS_ERR_STATIC_SCRATCH_LIMIT;
+	int dev = 0;
+	MOSS_CUDA_TRY(cudaGetDevice(&dev));
+	void* scratch = (dev >= 0 && dev < MAX_DEVICES) ? g_loss_static_ptr[dev].load(std::memory_order_acquire) : nullptr;
+	if (!scratch) {                         // set-up, once per device: the array's address ON THE CURRENT DEVICE
+		MOSS_CUDA_TRY(cudaGetSymbolAddress((void**)&scratch, g_loss_static_scratch));
+		if (!scratch) return MOSS_ERR_CUDA;
+		if (dev >= 0 && dev < MAX_DEVICES) g_loss_static_ptr[dev].store(scratch, std::memory_order_release);
+	}
+	if (dev >= 0 && dev < MAX_DEVICES && !g_loss_attr_set[dev].load(std::memory_order_acquire)) {
+		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
+		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
+		g_loss_attr_set[dev].store(true, std::memory_order_release);
+	}
+	LossArgs a;
+	a.W = k->W; a.H = k->H; a.image = k->image; a.alpha = k->alpha; a.gt = k->gt_image; a.bkgd = k->bkgd_mask; a.bound = k->bound_mask;
+	a.rect = k->rect; a.w_l1 = k->w_l1; a.w_mask = k->w_mask; a.w_ssim = k->w_ssim; a.w_s3im = k->w_s3im;
+	loss_window(a.g, a.s3);
+	a.dL_dimage = dL_dimage; a.dL_dalpha = dL_dalpha; a.losses = losses;
+	a.ticket = (unsigned*)scratch; a.partial = (float*)((char*)scratch + 16);
+	// the array keeps the last call's contents: the ticket must be zero on entry (the partial sums are fully rewritten)
+	MOSS_CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, stream));
+	const dim3 grid((k->W + LOSS_T - 1) / LOSS_T, (k->H + LOSS_T - 1) / LOSS_T);
+	g_launches.fetch_add(1, std::memory_order_relaxed);          // no MOSS_STAGE here: the profiler creates events
+	if (grid.x * grid.y <= 2 * 148) image_losses_kernel<512><<<grid, 512, LOSS_DYN_SMEM, stream>>>(a);
+	else image_losses_kernel<256><<<grid, 256, LOSS_DYN_SMEM, stream>>>(a);
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }
