@@ -115,7 +115,7 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	if (shs) sh_load(D, M, shs + (size_t)li * 3 * M, sh_vec, sh);
 	float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
 	float sc_in[3] = {0.f, 0.f, 0.f};
-	if (scales) {
+	if (!SKIN && scales) {
 		q = load_quat(rotations, li);
 		sc_in[0] = scales[3 * li]; sc_in[1] = scales[3 * li + 1]; sc_in[2] = scales[3 * li + 2];
 	}
@@ -127,6 +127,7 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	__syncthreads();
 	__shared__ SkinShared sk_sh;         // SKIN only (unused allocations are dropped by the compiler otherwise)
 	__shared__ float accA[NJ * 12];
+	__shared__ float dA_stage[SKIN ? (PRE_THREADS / 32) * SKIN_DA_STAGE : 1];
 	if constexpr (SKIN) {
 		skin_stage(sk_sh, sk.a);
 		if (sg.d_A_tgt) {
@@ -139,7 +140,7 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	// reference cost the plain kernel 11 registers and ~8 % at Stress.)
 	if constexpr (!SKIN) { if (!active) return; }
 	bool live = active;
-	float sk_bw[NJ];
+	float sk_bw[NJ], sk_gAt[12];
 	SkinFwd sk_f;
 	if (live) {
 	if constexpr (SKIN) {
@@ -195,7 +196,7 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 				for (int k = 0; k < 3 * M; k++) *route(pc, dL_dsh + (size_t)idx * 3 * M + k) = 0.f;
 			}
 		}
-		if (scales) {
+		if (!SKIN && scales) {
 #pragma unroll
 			for (int k = 0; k < 3; k++) *route(pc, dL_dscale + 3 * idx + k) = 0.f;
 			store_quat_routed(pc, dL_drot, idx, make_float4(0.f, 0.f, 0.f, 0.f));
@@ -381,13 +382,13 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 		// dL/dmeans3D and dL/dcov3D never leave the registers: straight into the skinning backward
 		const float gw[3] = {gmx, gmy, gmz};
 		skin_backward_point(sk_sh, sk.a, idx, sk_vid, sk_own, sk_bw, sk_f, gw, dcov, true, sg.d_xyz, sg.d_scaling, sg.d_rotation,
-			sg.d_lbs_delta, accA, sg.d_A_tgt != nullptr, sg.d_poseoff_tgt);
+			sg.d_lbs_delta, sk_gAt, sg.d_A_tgt != nullptr, sg.d_poseoff_tgt);
 	} else {
 		*route(pc, dL_dmean3D + 3 * idx) = gmx; *route(pc, dL_dmean3D + 3 * idx + 1) = gmy; *route(pc, dL_dmean3D + 3 * idx + 2) = gmz;
 	}
 
 	// ---- cov3D -> scale, (un-normalised) quaternion --------------------------------------------------
-	if (scales) {
+	if (!SKIN && scales) {
 		const float r = q.x, x = q.y, y = q.z, z = q.w;
 		const float s[3] = {vb.scale_modifier * sc_in[0], vb.scale_modifier * sc_in[1], vb.scale_modifier * sc_in[2]};
 		// R[i][j]: column i, row j (GLM listing of DGR backward.cu:288-292)
@@ -423,6 +424,7 @@ preprocess_backward_kernel(const __grid_constant__ ViewBatch vb,
 	}
 	if constexpr (SKIN) {
 		if (sg.d_A_tgt) {
+			skin_accumulate_dA(dA_stage + (threadIdx.x >> 5) * SKIN_DA_STAGE, accA, sk_bw, sk_gAt, live);
 			__syncthreads();
 			for (int i = threadIdx.x; i < NJ * 12; i += blockDim.x) {
 				const float v = accA[i];

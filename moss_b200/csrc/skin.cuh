@@ -313,14 +313,16 @@ skin_forward_kernel(SkinArgs a, float* __restrict__ means3D, float* __restrict__
 // d_A_tgt [24,16] (row-major 4x4 per joint like A_tgt; bottom rows stay 0 -> pose-correction MLP) and
 // d_poseoff_tgt [V,3] (scatter by vert_id).
 // The per-Gaussian backward of the front end: upstream gw = dL/dmeans3D, gcv = dL/dcov3D (has_gcov: whether it is there).
-// Writes d_xyz / d_scaling / d_rotation / d_lbs_delta rows, adds into d_poseoff_tgt (global atomics) and into the block's
-// shared accA [24*12] (dL/dA_tgt; the caller flushes it).  `f` and `bw` are the recomputed forward.
+// Writes d_xyz / d_scaling / d_rotation / d_lbs_delta rows, adds into d_poseoff_tgt (global atomics) and, with want_dA,
+// hands back gAt_out[12] = the gradient w.r.t. this Gaussian's blended target transform (rows r00 r01 r02 t0 | ...): its
+// contribution to dL/dA_tgt[j] is bw[j] * gAt_out, summed over the block by skin_accumulate_dA().  `f` and `bw` are the
+// recomputed forward.
 __device__ __forceinline__ void skin_backward_point(const SkinShared& sh, const SkinArgs& a, int idx, int vid, const SkinOwn& own,
 	const float bw[NJ], const SkinFwd& f, const float gw[3], const float gcv[6], bool has_gcov,
 	float* __restrict__ d_xyz, float* __restrict__ d_scaling, float* __restrict__ d_rotation, float* __restrict__ d_lbs_delta,
-	float* accA, bool want_dA, float* __restrict__ d_poseoff_tgt)
+	float gAt_out[12], bool want_dA, float* __restrict__ d_poseoff_tgt)
 {
-	float* const d_A_tgt = want_dA ? accA : nullptr;
+	const bool d_A_tgt = want_dA;
 	Mat3 dTr;
 #pragma unroll
 	for (int i = 0; i < 9; i++) dTr.m[i] = 0.f;
@@ -417,13 +419,7 @@ __device__ __forceinline__ void skin_backward_point(const SkinShared& sh, const 
 		}
 		if (d_A_tgt) {
 #pragma unroll
-			for (int j = 0; j < NJ; j++) {
-				const float w = bw[j];
-				if (w != 0.f) {
-#pragma unroll
-					for (int e = 0; e < 12; e++) atomicAdd(&accA[j * 12 + e], w * gAt[e]);
-				}
-			}
+			for (int e = 0; e < 12; e++) gAt_out[e] = gAt[e];
 		}
 		if (d_lbs_delta) {
 			float gb[NJ];
@@ -445,6 +441,48 @@ __device__ __forceinline__ void skin_backward_point(const SkinShared& sh, const 
 	}
 }
 
+// dL/dA_tgt[j][e] += sum over a warp's Gaussians of bw[j] * gAt[e]: a [24 x 32] . [32 x 12] product per warp.  The 32 weight
+// rows and gradient rows are staged in shared memory (row stride 37 floats: conflict-free stores, broadcast loads) and
+// every lane owns a 3 x 3 block of the 24 x 12 result (8 joint groups x 4 element groups): 32 x (6 loads + 9 FMA) per
+// lane, then nine shared atomics per lane on addresses no other lane of the warp touches.  (Before: every thread issued
+// 12 shared atomicAdd per joint it is bound to, the whole warp on the same 12 addresses -- a float atomicAdd on shared
+// memory is a compare-and-swap loop, so a 32-way collision costs 32 rounds: the fused backward preprocess took 123 us at
+// 20 k Gaussians with dL/dA_tgt wanted against 25 us without.)  Call with the whole warp converged; lanes without a
+// Gaussian pass contributes = false.
+constexpr int SKIN_DA_ROW = NJ + 12 + 1;
+constexpr int SKIN_DA_STAGE = 32 * SKIN_DA_ROW;          // floats of staging per warp
+__device__ __forceinline__ void skin_accumulate_dA(float* __restrict__ stage, float* accA, const float bw[NJ], const float gAt[12],
+	bool contributes)
+{
+	const unsigned full = 0xffffffffu;
+	if (!__any_sync(full, contributes)) return;
+	const int lane = threadIdx.x & 31;
+	float* row = stage + lane * SKIN_DA_ROW;
+#pragma unroll
+	for (int j = 0; j < NJ; j++) row[j] = contributes ? bw[j] : 0.f;
+#pragma unroll
+	for (int e = 0; e < 12; e++) row[NJ + e] = contributes ? gAt[e] : 0.f;
+	__syncwarp();
+	const int jg = 3 * (lane >> 2), eg = NJ + 3 * (lane & 3);
+	float acc[9];
+#pragma unroll
+	for (int k = 0; k < 9; k++) acc[k] = 0.f;
+#pragma unroll 8
+	for (int i = 0; i < 32; i++) {
+		const float* r = stage + i * SKIN_DA_ROW;
+		const float w0 = r[jg], w1 = r[jg + 1], w2 = r[jg + 2], g0 = r[eg], g1 = r[eg + 1], g2 = r[eg + 2];
+		acc[0] += w0 * g0; acc[1] += w0 * g1; acc[2] += w0 * g2;
+		acc[3] += w1 * g0; acc[4] += w1 * g1; acc[5] += w1 * g2;
+		acc[6] += w2 * g0; acc[7] += w2 * g1; acc[8] += w2 * g2;
+	}
+	__syncwarp();
+#pragma unroll
+	for (int a = 0; a < 3; a++)
+#pragma unroll
+		for (int b = 0; b < 3; b++)
+			if (acc[3 * a + b] != 0.f) atomicAdd(&accA[(jg + a) * 12 + (eg - NJ) + b], acc[3 * a + b]);
+}
+
 __global__ void __launch_bounds__(SKIN_THREADS)
 skin_backward_kernel(SkinArgs a, const float* __restrict__ g_means3D, const float* __restrict__ g_cov3D,
                      float* __restrict__ d_xyz, float* __restrict__ d_scaling, float* __restrict__ d_rotation,
@@ -452,12 +490,14 @@ skin_backward_kernel(SkinArgs a, const float* __restrict__ g_means3D, const floa
 {
 	__shared__ SkinShared sh;
 	__shared__ float accA[NJ * 12];
+	__shared__ float dA_stage[(SKIN_THREADS / 32) * SKIN_DA_STAGE];
 	skin_stage(sh, a);
 	if (d_A_tgt) {
 		for (int i = threadIdx.x; i < NJ * 12; i += blockDim.x) accA[i] = 0.f;
 		__syncthreads();
 	}
 	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+	float bw[NJ], gAt[12];
 	if (idx < a.P) {
 		const int vid = __ldg(a.vert_ids + idx);
 		const SkinOwn own = skin_own(a, idx);
@@ -466,14 +506,14 @@ skin_backward_kernel(SkinArgs a, const float* __restrict__ g_means3D, const floa
 		for (int i = 0; i < 3; i++) gw[i] = __ldg(g_means3D + 3 * (size_t)idx + i);
 #pragma unroll
 		for (int i = 0; i < 6; i++) gcv[i] = g_cov3D ? __ldg(g_cov3D + 6 * (size_t)idx + i) : 0.f;
-		float bw[NJ];
 		skin_weights(a, idx, vid, bw);
 		SkinFwd f;
 		skin_point(sh, a, own.x, vid, bw, f);
 		skin_backward_point(sh, a, idx, vid, own, bw, f, gw, gcv, g_cov3D != nullptr, d_xyz, d_scaling, d_rotation, d_lbs_delta,
-			accA, d_A_tgt != nullptr, d_poseoff_tgt);
+			gAt, d_A_tgt != nullptr, d_poseoff_tgt);
 	}
 	if (d_A_tgt) {
+		skin_accumulate_dA(dA_stage + (threadIdx.x >> 5) * SKIN_DA_STAGE, accA, bw, gAt, idx < a.P);
 		__syncthreads();
 		for (int i = threadIdx.x; i < NJ * 12; i += blockDim.x) {
 			const float v = accA[i];

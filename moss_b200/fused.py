@@ -55,12 +55,12 @@ class _SkinRasterize(torch.autograd.Function):
         rs = raster_settings
         k = K._fill_skin(xyz, vert_ids, weights, lbs_delta, A_big, A_tgt, poseoff_big, shapeoff, poseoff_tgt, Rg, Th,
                          scaling, rotation, float(rs.scale_modifier))
-        with torch.cuda.device(dev):
+        with _abi.on_device(dev):
             transforms = torch.empty((P, 3, 3), dtype=torch.float32, device=dev) if want_transforms else None
         keep = (xyz, vert_ids, weights, lbs_delta, A_big, A_tgt, poseoff_big, shapeoff, poseoff_tgt, Rg, Th, scaling, rotation)
         sh = shs if shs is not None else _EMPTY
         cp = colors_precomp if colors_precomp is not None else _EMPTY
-        color, radii, depth, alpha, st = R._forward(xyz, sh, cp, opacities, _EMPTY, _EMPTY, _EMPTY, [rs], 0, False,
+        color, radii, depth, alpha, st = R._forward(xyz, sh, cp, opacities, _EMPTY, _EMPTY, _EMPTY, [rs], R._default_flags, False,
                                                     skin=(k, keep, None, transforms))
         ctx.st, ctx.skin = st, k
         ctx.has = (lbs_delta is not None, poseoff_tgt is not None, shs is not None)
@@ -80,7 +80,7 @@ class _SkinRasterize(torch.autograd.Function):
         dev = radii.device
         has_delta, has_pt, has_sh = ctx.has
         need = ctx.needs_input_grad
-        with torch.cuda.device(dev):
+        with _abi.on_device(dev):
             def _g(t, shape, required=False):
                 if t is None:
                     return torch.zeros(shape, dtype=torch.float32, device=dev) if required else None
@@ -103,7 +103,7 @@ class _SkinRasterize(torch.autograd.Function):
             d_po = torch.empty((ctx.V_smpl, 3), dtype=torch.float32, device=dev) if (has_pt and need[5]) else None
             p = K._p
             status = lib.moss_skin_rasterize_backward(
-                torch.cuda.current_stream(dev).cuda_stream, C.byref(sc), C.byref(k), st.flags, p(radii),
+                _abi.stream_ptr(dev), C.byref(sc), C.byref(k), st.flags, p(radii),
                 g_color.data_ptr(), p(g_depth), p(g_alpha), p(d_means2D), p(d_conic), p(d_opacity), p(d_colors), p(d_sh),
                 p(d_xyz), p(d_scaling), p(d_rotation), p(d_delta), p(d_A), p(d_po))
         _abi.check(status, "moss_skin_rasterize_backward")

@@ -64,3 +64,56 @@ class GraphedStep:
         if int(c[1]) != 0:
             raise RuntimeError(f"graphed step: binning capacity {int(c[2])} exceeded by num_rendered {int(c[0])}")
         return int(c[0])
+
+
+class GraphedIteration:
+    """A whole training iteration written against the PUBLIC API -- e.g. skinning.frame_tables -> skinning.nearest_vertex
+    -> fused.skin_and_rasterize (or GaussianRasterizer) -> losses.image_losses -> ``loss.backward()`` ->
+    add_densification_stats -- captured as ONE CUDA graph.  At ZJU size such an iteration is ~0.37 ms of kernels behind
+    ~0.8 ms of Python; replayed it costs one launch.
+
+    ``fn()`` runs the iteration over STATIC tensors (parameters, camera, pose, targets: copy new values into them between
+    replays, as with any CUDA graph) and returns what the caller wants to read afterwards (loss, image ...).  It is called
+    once synchronously (the library learns the instance count that sizes the binning workspace), twice on a side stream
+    and once under capture, the last three inside ``rasterizer.async_launch()``.  Gradients: call
+    ``optimizer.zero_grad(set_to_none=True)`` at the top of ``fn`` so that the ``.grad`` tensors are created inside the
+    graph's memory pool; an optimizer whose step count lives on the host (FusedAdamW, torch's non-capturable ones) steps
+    OUTSIDE the graph, after ``replay()``.  Keep no graph-attached tensor of an earlier eager iteration alive (store
+    ``loss.detach()``, not ``loss``): such a graph pins the parameters' AccumulateGrad nodes to the stream they were
+    created on -- the legacy default stream -- and the captured backward then fails with
+    ``cudaErrorStreamCaptureImplicit``.
+    ``check()`` raises if a replay needed more binning capacity than the capture reserved (1.25 x the instance count of
+    the synchronous call plus 4096: capture again after densification or a large change of pose or camera)."""
+
+    def __init__(self, fn, device=None):
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.device = dev
+        with torch.cuda.device(dev):
+            fn()
+            torch.cuda.synchronize(dev)
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side), R.async_launch():
+                for _ in range(2):
+                    fn()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            R.async_counters()                       # drop the warm-up runs' counters
+            self.graph = torch.cuda.CUDAGraph()
+            with R.async_launch(), torch.cuda.graph(self.graph):
+                self.out = fn()
+            self.counters = R.async_counters()       # written by every replay
+
+    def replay(self):
+        self.graph.replay()
+        return self.out
+
+    def check(self):
+        """-> instance counts of the last replay's forwards; raises if one exceeded its captured capacity."""
+        counts = []
+        for c in self.counters:
+            c = c.cpu()
+            if int(c[1]) != 0:
+                raise RuntimeError(f"graphed iteration: binning capacity {int(c[2])} exceeded by num_rendered {int(c[0])}; capture again")
+            counts.append(int(c[0]))
+        return counts

@@ -65,9 +65,9 @@ def mask_bounds(mask):
     H, W = m.shape[-2:]
     if m.numel() != H * W:
         raise RuntimeError("mask must be [H,W] or [1,H,W]")
-    with torch.cuda.device(m.device):
+    with _abi.on_device(m.device):
         out = torch.empty((8,), dtype=torch.int32, device=m.device)
-        st = lib.moss_mask_bounds(torch.cuda.current_stream(m.device).cuda_stream, W, H, _p(m), _p(out))
+        st = lib.moss_mask_bounds(_abi.stream_ptr(m.device), W, H, _p(m), _p(out))
     _abi.check(st, "moss_mask_bounds")
     return out
 
@@ -89,8 +89,8 @@ class _ImageLosses(torch.autograd.Function):
         w = [float(x) for x in weights]
         if w[1] != 0.0 and (alpha is None or bkgd_mask is None):
             raise RuntimeError("the mask loss needs alpha and bkgd_mask")
-        with torch.cuda.device(dev):
-            stream = torch.cuda.current_stream(dev).cuda_stream
+        with _abi.on_device(dev):
+            stream = _abi.stream_ptr(dev)
             scratch = _scratch_for(dev, stream, lib.moss_image_losses_scratch_bytes(W, H))
             out = torch.empty((8 + 4 * H * W,), dtype=torch.float32, device=dev)
             losses, d_image, d_alpha = out[:5], out[8:8 + 3 * H * W].view(3, H, W), out[8 + 3 * H * W:].view(1, H, W)
@@ -115,9 +115,9 @@ class _ImageLosses(torch.autograd.Function):
         d_image, d_alpha = ctx.saved_tensors
         dev = d_image.device
         g = _f32(g_total.reshape(1), "grad")
-        with torch.cuda.device(dev):
+        with _abi.on_device(dev):
             # in place on buffers this node owns; a no-op on the device when the upstream gradient is exactly 1
-            st = lib.moss_scale_gradients(torch.cuda.current_stream(dev).cuda_stream, _p(g), _p(d_image), d_image.numel(),
+            st = lib.moss_scale_gradients(_abi.stream_ptr(dev), _p(g), _p(d_image), d_image.numel(),
                                           _p(d_alpha) if ctx.has_alpha else None, d_alpha.numel() if ctx.has_alpha else 0)
         _abi.check(st, "moss_scale_gradients")
         return d_image, (d_alpha.view(ctx.alpha_shape) if ctx.has_alpha else None), None, None, None, None, None

@@ -58,8 +58,8 @@ class FusedAdamW(torch.optim.Optimizer):
                     a.param, a.grad = p.data_ptr(), g.data_ptr()
                     a.exp_avg, a.exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
                     a.numel, a.lr, a.step = p.numel(), lr, st["step"]
-                with torch.cuda.device(dev):
-                    status = lib.moss_adamw_step(torch.cuda.current_stream(dev).cuda_stream, len(part), arr, beta1, beta2,
+                with _abi.on_device(dev):
+                    status = lib.moss_adamw_step(_abi.stream_ptr(dev), len(part), arr, beta1, beta2,
                                                  eps, wd)
                 _abi.check(status, "moss_adamw_step")
         return loss

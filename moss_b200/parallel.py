@@ -150,11 +150,11 @@ class PeerGradBuffer:
     def allreduce(self, numel, offset=0):
         """Sum tensor[offset:offset+numel] over all ranks, in place, on the current stream (no host sync; the epoch
         lives on the device, so the call can be captured in a CUDA graph)."""
-        st = self._lib.moss_peer_allreduce(torch.cuda.current_stream(self.device).cuda_stream, self.rank, self.world,
+        from . import _abi
+        st = self._lib.moss_peer_allreduce(_abi.stream_ptr(self.device), self.rank, self.world,
                                            int(self.handle.buffer_ptrs_dev), int(self.handle.signal_pad_ptrs_dev),
                                            int(self.handle.signal_pad_size), int(offset), int(numel), 0,
                                            self.error.data_ptr(), self.multicast_ptr or None)
-        from . import _abi
         _abi.check(st, "moss_peer_allreduce")
         return self.tensor
 
@@ -164,7 +164,7 @@ class PeerGradBuffer:
         moss_push_allreduce).  Same result on every rank, summed in rank order."""
         import ctypes as C
         from . import _abi
-        st = self._lib.moss_push_allreduce(torch.cuda.current_stream(self.device).cuda_stream, C.byref(self.descriptor(int(numel))))
+        st = self._lib.moss_push_allreduce(_abi.stream_ptr(self.device), C.byref(self.descriptor(int(numel))))
         _abi.check(st, "moss_push_allreduce")
         return self.tensor
 

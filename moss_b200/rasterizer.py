@@ -12,6 +12,7 @@ Differences that are invisible through the API:
   * the three opaque state tensors are caller-owned workspaces (`geom+image` in one allocation, `binning`).
 """
 from typing import NamedTuple
+import contextlib
 import ctypes as C
 import os
 import sys
@@ -106,6 +107,37 @@ class RasterState:
         self.batched = False
 
 
+# ---- asynchronous launch mode of the PUBLIC API (CUDA-graph capture of a whole training iteration, graphs.py) -----------
+# Normally a forward waits for the instance count (like the reference, which copies num_rendered to the host in the middle
+# of the call) so that the binning workspace can grow.  Inside `with async_launch():` the public entry points
+# (GaussianRasterizer, rasterize_batch, fused.skin_and_rasterize) pass MOSS_FLAG_ASYNC instead: nothing waits, the binning
+# capacity is 1.25 x the count the last synchronous call of the same shape produced (call once outside the block first),
+# and an overflow only raises a flag on the device.  Every forward inside the block drops its int32[4] counters
+# (num_rendered, overflow flag, capacity, non-empty tiles) into `async_counters()` for a later check.
+_default_flags = 0
+_async_counters = []
+
+
+@contextlib.contextmanager
+def async_launch():
+    global _default_flags
+    prev, _default_flags = _default_flags, _default_flags | _abi.FLAG_ASYNC
+    try:
+        yield
+    finally:
+        _default_flags = prev
+
+
+def async_counters(clear=True):
+    """The counter tensors of the forwards run under ``async_launch()`` since the last call (device tensors: reading them
+    synchronises)."""
+    global _async_counters
+    out = _async_counters
+    if clear:
+        _async_counters = []
+    return out
+
+
 def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, settings_list, flags, batched,
              skin=None):
     """``skin``: (filled _abi.MossSkin, tensors to keep alive, means3D_out or None, transforms_out or None) -- the fused
@@ -139,7 +171,7 @@ def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_p
         flags |= _abi.FLAG_DEBUG
     export = 1 if (flags & _abi.FLAG_EXPORT_KEYS) else 0
 
-    with torch.cuda.device(dev):
+    with _abi.on_device(dev):
         # three independent output tensors, like the reference (DGR/rasterize_points.cu:68-71): callers edit renders
         # in place (render_ZJU.py), which autograd refuses on views of a shared multi-output buffer
         lead = (V,) if batched else ()
@@ -175,7 +207,7 @@ def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_p
             sc.tanfovx = float(rs.tanfovx); sc.tanfovy = float(rs.tanfovy)
         sc.geom_ws = ws.data_ptr(); sc.geom_bytes = gbytes
         sc.image_ws = ws.data_ptr() + gbytes; sc.image_bytes = ibytes
-        stream = torch.cuda.current_stream(dev).cuda_stream
+        stream = _abi.stream_ptr(dev)
         nr = C.c_int(0)
         call_flags = flags
         want_ckpt = _want_ckpt(W, H, V)
@@ -212,6 +244,8 @@ def _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_p
         st.keep = (means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp) + tuple(t for c in cams for t in c)
         if skin is not None:
             st.keep = st.keep + (skin[0],) + tuple(skin[1])
+    if (flags & _abi.FLAG_ASYNC) and (_default_flags & _abi.FLAG_ASYNC) and P > 0:
+        _async_counters.append(export_state(st, "counters"))
     return color, radii, depth, alpha, st
 
 
@@ -283,7 +317,7 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
     P, M, H, W, V = sc.P, sc.M, sc.H, sc.W, st.V
     dev = radii.device
     lead = (V,) if st.batched else ()
-    with torch.cuda.device(dev):
+    with _abi.on_device(dev):
         def _g(t, shape, required=False):
             if t is None:      # no gradient reaches this output: the ABI takes NULL for depth / alpha
                 return torch.zeros(shape, dtype=torch.float32, device=dev) if required else None
@@ -317,7 +351,7 @@ def backward_raw(st, radii, grad_color, grad_depth, grad_alpha, flags=0, out=Non
             # absent inputs: the reference hands back zero tensors (DGR/rasterize_points.cu:158-166).  Two fill kernels per
             # backward (7 us of a 156 us ZJU step) for tensors nobody reads: shared, read-only zeros instead
             dscales, drot = _shared_zeros((P, 3), dev), _shared_zeros((P, 4), dev)
-        stream = torch.cuda.current_stream(dev).cuda_stream
+        stream = _abi.stream_ptr(dev)
         outs = (_ptr(dmeans2D), _ptr(dconic), _ptr(dopacity), _ptr(dcolors), _ptr(dmeans3D), _ptr(dcov3D),
                 _ptr(dsh) if has_sh else None, _ptr(dscales) if has_sr else None, _ptr(drot) if has_sr else None)
         if push is not None:
@@ -379,7 +413,7 @@ def public_api_kind():
 
 
 def _rasterize(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, raster_settings, batched):
-    b = _load_binding()
+    b = _load_binding() if not (_default_flags & _abi.FLAG_ASYNC) else None
     if b is None:
         return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
                                          cov3Ds_precomp, list(raster_settings) if batched else raster_settings)
@@ -432,7 +466,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                 raster_settings):
         batched = isinstance(raster_settings, (list, tuple)) and not isinstance(raster_settings, GaussianRasterizationSettings)
         color, radii, depth, alpha, st = _forward(means3D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                                                  list(raster_settings) if batched else [raster_settings], 0, batched)
+                                                  list(raster_settings) if batched else [raster_settings], _default_flags, batched)
         ctx.raster_settings = raster_settings
         ctx.num_rendered = st.num_rendered
         ctx.mark_non_differentiable(radii)
@@ -491,8 +525,8 @@ class GaussianRasterizer(nn.Module):
             P = pos.shape[0]
             present = torch.empty((P,), dtype=torch.bool, device=pos.device)
             view = _f32c(rs.viewmatrix, "viewmatrix"); proj = _f32c(rs.projmatrix, "projmatrix")
-            with torch.cuda.device(pos.device):
-                status = lib.moss_mark_visible(torch.cuda.current_stream(pos.device).cuda_stream, P, _ptr(pos),
+            with _abi.on_device(pos.device):
+                status = lib.moss_mark_visible(_abi.stream_ptr(pos.device), P, _ptr(pos),
                                                _ptr(view), _ptr(proj), _ptr(present))
             _abi.check(status, "moss_mark_visible")
         return present
@@ -535,8 +569,8 @@ def export_state(st, name, view=None):
         "counters": (torch.int32, (4,)), "view_base": (torch.int32, (V + 1,)),
     }[name]
     out = torch.empty(spec[1], dtype=spec[0], device=dev)
-    with torch.cuda.device(dev):
-        n = lib.moss_export_state_batch(torch.cuda.current_stream(dev).cuda_stream, C.byref(sc), V, _abi.STATE[name],
+    with _abi.on_device(dev):
+        n = lib.moss_export_state_batch(_abi.stream_ptr(dev), C.byref(sc), V, _abi.STATE[name],
                                         out.data_ptr(), out.numel() * out.element_size())
     if n < 0:
         raise RuntimeError(f"moss_export_state({name}) failed: {lib.moss_error_string(int(-n)).decode()}")
@@ -587,7 +621,7 @@ def add_densification_stats(radii, viewspace_grad, xyz_gradient_accum=None, deno
         g = _f32c(viewspace_grad, "viewspace_grad")
         if g.shape != (P, 3) or g.device != radii.device:
             raise RuntimeError("viewspace_grad must be [P,3] on the device of radii")
-    with torch.cuda.device(radii.device):
-        status = lib.moss_densify_stats(torch.cuda.current_stream(radii.device).cuda_stream, P, _ptr(radii), _ptr(g),
+    with _abi.on_device(radii.device):
+        status = lib.moss_densify_stats(_abi.stream_ptr(radii.device), P, _ptr(radii), _ptr(g),
                                         _ptr(acc), _ptr(den), _ptr(mx))
     _abi.check(status, "moss_densify_stats")

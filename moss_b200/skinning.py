@@ -107,10 +107,10 @@ def joint_tables(smpl):
     if smpl.J_regressor.shape != (24, V) or smpl.shapedirs.shape[:2] != (V, 3):
         raise RuntimeError("SMPL table shapes do not match (v_template [V,3], shapedirs [V,3,S], J_regressor [24,V])")
     dev = smpl.v_template.device
-    with torch.cuda.device(dev):
+    with _abi.on_device(dev):
         jt = torch.empty((24, 3), dtype=torch.float32, device=dev)
         js = torch.empty((24, 3, S), dtype=torch.float32, device=dev)
-        st = _abi.load().moss_smpl_joint_tables(torch.cuda.current_stream(dev).cuda_stream, V, S, _p(smpl.v_template),
+        st = _abi.load().moss_smpl_joint_tables(_abi.stream_ptr(dev), V, S, _p(smpl.v_template),
                                                 _p(smpl.shapedirs), _p(smpl.J_regressor), _p(jt), _p(js))
     _abi.check(st, "moss_smpl_joint_tables")
     torch.cuda.current_stream(dev).synchronize()      # once per model: later frames may run on any stream
@@ -156,8 +156,8 @@ class _SmplFrame(torch.autograd.Function):
         if shapes.numel() > smpl.shapedirs.shape[-1] or smpl.posedirs.numel() != V * 3 * 207:
             raise RuntimeError("SMPL table shapes do not match (shapedirs [V,3,S] with S >= len(shapes), posedirs [V,3,207])")
         parents = _parents32(smpl.parents)
-        with torch.cuda.device(dev):
-            stream = torch.cuda.current_stream(dev).cuda_stream
+        with _abi.on_device(dev):
+            stream = _abi.stream_ptr(dev)
             out = torch.empty((24 * 16 + 24 * 3 + 6 * V,), dtype=torch.float32, device=dev)
             A, joints = out[:384].view(24, 4, 4), out[384:456]
             poseoff, shapeoff = out[456:456 + 3 * V].view(V, 3), out[456 + 3 * V:].view(V, 3)
@@ -180,8 +180,8 @@ class _SmplFrame(torch.autograd.Function):
         V = smpl.v_template.shape[0]
         d_A = _dev_f32(d_A, "grad A") if d_A is not None else None
         d_poseoff = _dev_f32(d_poseoff, "grad pose_offsets") if d_poseoff is not None else None
-        with torch.cuda.device(dev):
-            stream = torch.cuda.current_stream(dev).cuda_stream
+        with _abi.on_device(dev):
+            stream = _abi.stream_ptr(dev)
             scratch = _scratch_for(dev, stream, lib.moss_smpl_frame_scratch_bytes(V))
             d_poses = torch.empty((72,), dtype=torch.float32, device=dev)
             d_cr = torch.empty((23, 3, 3), dtype=torch.float32, device=dev) if (ctx.has_cr and ctx.needs_input_grad[1]) else None
@@ -269,7 +269,7 @@ class _SkinCovariance(torch.autograd.Function):
         vert_ids = vert_ids.reshape(-1).contiguous()
         if not vert_ids.is_cuda or vert_ids.shape[0] != P:
             raise RuntimeError("vert_ids must be a CUDA tensor with one entry per Gaussian")
-        with torch.cuda.device(dev):
+        with _abi.on_device(dev):
             means3D = torch.empty((P, 3), dtype=torch.float32, device=dev)
             has_cov = scaling is not None and rotation is not None
             cov3D = torch.empty((P, 6), dtype=torch.float32, device=dev) if has_cov else None
@@ -278,7 +278,7 @@ class _SkinCovariance(torch.autograd.Function):
             translation = torch.empty((P, 3), dtype=torch.float32, device=dev) if return_transl else None
             k = _fill_skin(xyz, vert_ids, weights, lbs_delta, A_big, A_tgt, poseoff_big, shapeoff, poseoff_tgt, R, Th,
                            scaling, rotation, scaling_modifier)
-            st = lib.moss_skin_forward(torch.cuda.current_stream(dev).cuda_stream, C.byref(k), _p(means3D), _p(cov3D),
+            st = lib.moss_skin_forward(_abi.stream_ptr(dev), C.byref(k), _p(means3D), _p(cov3D),
                                        _p(transforms), _p(bweights), _p(translation))
         _abi.check(st, "moss_skin_forward")
         ctx.mod = float(scaling_modifier)
@@ -315,7 +315,7 @@ class _SkinCovariance(torch.autograd.Function):
         dev = xyz.device
         P, V = xyz.shape[0], weights.shape[0]
         need = ctx.needs_input_grad        # xyz, scaling, rotation, lbs_delta, A_tgt, poseoff_tgt
-        with torch.cuda.device(dev):
+        with _abi.on_device(dev):
             g_means3D = (torch.zeros((P, 3), dtype=torch.float32, device=dev) if g_means3D is None
                          else _dev_f32(g_means3D, "grad means3D"))
             g_cov3D = _dev_f32(g_cov3D, "grad cov3D") if (has_cov and g_cov3D is not None and g_cov3D.numel()) else None
@@ -327,7 +327,7 @@ class _SkinCovariance(torch.autograd.Function):
             d_po = torch.empty((V, 3), dtype=torch.float32, device=dev) if (has_pt and need[5]) else None
             k = _fill_skin(xyz, vert_ids, weights, lbs_delta, A_big, A_tgt, po_big, so, po_tgt, R, Th, scaling, rotation,
                            ctx.mod)
-            st = lib.moss_skin_backward(torch.cuda.current_stream(dev).cuda_stream, C.byref(k), _p(g_means3D), _p(g_cov3D),
+            st = lib.moss_skin_backward(_abi.stream_ptr(dev), C.byref(k), _p(g_means3D), _p(g_cov3D),
                                         _p(d_xyz), _p(d_scaling), _p(d_rotation), _p(d_delta), _p(d_A), _p(d_po))
         _abi.check(st, "moss_skin_backward")
         return (d_xyz, d_scaling, d_rotation, d_delta, d_A, d_po) + (None,) * 9
@@ -358,9 +358,9 @@ class VertexGrid:
             raise RuntimeError("t_vertices is empty")
         self.V, self.device = v.shape[0], v.device
         nbytes = lib.moss_vertex_grid_bytes(self.V)
-        with torch.cuda.device(v.device):
+        with _abi.on_device(v.device):
             self.buf = torch.empty((nbytes,), dtype=torch.uint8, device=v.device)
-            st = lib.moss_vertex_grid_build(torch.cuda.current_stream(v.device).cuda_stream, self.V, _p(v), _p(self.buf), nbytes)
+            st = lib.moss_vertex_grid_build(_abi.stream_ptr(v.device), self.V, _p(v), _p(self.buf), nbytes)
         _abi.check(st, "moss_vertex_grid_build")
         self.src = t_vertices            # keeps the identity the cache is keyed on alive
 
@@ -400,8 +400,8 @@ def nearest_vertex(xyz, t_vertices, return_distance=False, grid="auto"):
     dist = torch.empty((P,), dtype=torch.float32, device=q.device) if return_distance else None
     if isinstance(grid, str) and grid == "auto":
         grid = _grid_for(t_vertices) if V >= 64 else None
-    with torch.cuda.device(q.device):
-        stream = torch.cuda.current_stream(q.device).cuda_stream
+    with _abi.on_device(q.device):
+        stream = _abi.stream_ptr(q.device)
         if grid is not None:
             if grid.V != V or grid.device != q.device:
                 raise RuntimeError("the VertexGrid was built for another vertex set")
