@@ -631,8 +631,10 @@ def run_ours(args, rank, world, dev):
             "frac": round(achieved / hbm, 5), "traffic": None, "peak_source": peak_src,
             "kernel_us": round(dom_us, 2), "algorithmic_bytes": ab[dom],
             "kernels_us": {k: round(v, 2) for k, v in kern.items() if v > 0 and k != "other"},
-            "kernels_us_note": "event brackets around every launch of a stream-launched pass (carry ~2-3 us each); the ncu "
-                               "durations of the same launches are in profiles/",
+            "kernels_us_note": "event brackets around every launch of a stream-launched pass; the two timestamp operations "
+                               "of a bracket cost 2-10 us that the graph-replayed step does not pay (holding the stream until "
+                               "the whole step is enqueued changes nothing, so it is not launch gaps); the ncu durations of "
+                               "the same launches are in profiles/",
             "kernels_hbm_frac": {k: round(ab[k] / (kern[k] * 1e-6) / 1e9 / hbm, 4) for k in ab if kern.get(k, 0) > 0},
             "step_algorithmic_bytes": sum(ab.values()),
             "step_hbm_frac": round(sum(ab.values()) / (ms_step * 1e-3) / 1e9 / hbm, 5),

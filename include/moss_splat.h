@@ -292,13 +292,14 @@ int moss_image_losses(void* stream, const MossImageLoss* loss, float* losses, fl
  * buffer: loss->scratch and loss->scratch_bytes are IGNORED (may be NULL / 0), and the call performs no cudaMalloc,
  * cudaFree or any other allocating call.  Limit: at most MOSS_IMAGE_LOSSES_STATIC_MAX_TILES tiles of 32x32 pixels,
  * ceil(W/32) * ceil(H/32) <= 4096 (e.g. 2048 x 2048); a larger image returns MOSS_ERR_STATIC_SCRATCH_LIMIT and launches
- * nothing.  Every GPU that loads the library holds the array (MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES = 65 792 bytes)
+ * nothing.  Every GPU that loads the library holds the array (MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES = 131 360 bytes: the launch's tile grid is
+ * aligned to the crop, one extra tile column and row)
  * until the process exits.  All calls on one device share it: calls that may OVERLAP on the GPU (different streams
  * without an ordering between them) race on it and give undefined results -- serialise them or use moss_image_losses()
  * with one scratch buffer per stream.  The part that must start at zero (the ticket) is cleared on `stream` by every
  * call, so an aborted earlier call leaves nothing behind. */
 #define MOSS_IMAGE_LOSSES_STATIC_MAX_TILES 4096
-#define MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES (256 + 16 * MOSS_IMAGE_LOSSES_STATIC_MAX_TILES)
+#define MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES (256 + 16 * (2 * MOSS_IMAGE_LOSSES_STATIC_MAX_TILES + 2))
 int moss_image_losses_static(void* stream, const MossImageLoss* loss, float* losses, float* dL_dimage, float* dL_dalpha);
 /* out: DEVICE int[8]; out[0..4] = x, y, w, h of the bounding rectangle of the non-zero pixels of mask (as
  * cv2.boundingRect(mask.astype(np.uint8)), (0,0,0,0) if none) and the number of pixels equal to 1; out[5..7] scratch. */

@@ -33,8 +33,8 @@ constexpr int LOSS_R = 5;                        // window radius (window_size =
 constexpr int LOSS_WIN = 2 * LOSS_R + 1;
 constexpr int LOSS_IN = LOSS_T + 4 * LOSS_R;     // 52: input tile edge, two window passes deep
 constexpr int LOSS_MID = LOSS_T + 2 * LOSS_R;    // 42: where the statistics and the derivative maps live
-// threads per tile: a template parameter.  The passes are latency-bound, so with few tiles (ZJU: <= 2 per SM) 16 warps
-// per tile hide more of it (116 -> 74 us); with many tiles two resident 8-warp blocks per SM do better (1080p: 328 vs 381 us).
+// threads per block: a template parameter.  The passes are latency-bound, so with few tiles (ZJU) 16 warps per block hide
+// more of it (116 -> 74 us per tile block); with many tiles two resident 8-warp blocks per SM do better (1080p: 328 vs 381 us).
 constexpr int LOSS_S3_REP = 10;                  // repeat_time (loss_utils.py:16)
 constexpr int LOSS_S3_W = LOSS_T + 2;            // 34: S3IM map points per row (tile + 1 pixel each side)
 constexpr int LOSS_S3_VW = LOSS_T + 4;           // 36: columns of the vertical pass the S3IM maps read
@@ -82,10 +82,33 @@ __device__ __forceinline__ float ssim_point(float mu1, float mu2, float e11, flo
 	return map;
 }
 
-template <int LOSS_THREADS>
-__global__ void __launch_bounds__(LOSS_THREADS)
+// CSPLIT: one block per (tile, colour channel) instead of one per tile (grid.z = 3).  The three channels of a tile are
+// independent up to the sums, so with few tiles (ZJU: 96 tiles inside the crop, fewer than SMs) the split puts three
+// times as many blocks on the machine and every block runs a third of the barrier-separated passes; block z = 0 also
+// owns the alpha / mask term.  Partial sums stay per block and are added in block order: reproducible.
+// Measured on B200 (kernel us, old -> new): 256 x 256 71 -> 43, 512 x 512 (ZJU crop) 75 -> 65.  The gain is bounded by
+// quantisation: 288 equal blocks on 148 SMs x 2 resident blocks is one wave whose SMs run two blocks at ~60 % issue
+// rate; 64 registers (two resident 16-warp blocks) beat 100 registers (one) at ZJU size, 68 vs 73 us.
+// The launch bounds matter for the per-tile kernel too: (256, 1) let ptxas take 172 registers -> ONE resident block
+// and 1080p went from 327 to 505 us; (256, 2) gives 116 registers, no spills, two resident blocks.
+constexpr int LOSS_CSPLIT_MAX_TILES = 2 * 148;   // split when the launch has at most this many tiles (host side)
+#ifndef MOSS_LOSS_SPLIT_THREADS
+#define MOSS_LOSS_SPLIT_THREADS 512              // threads of a per-channel block
+#endif
+#ifndef MOSS_LOSS_SPLIT_MINBLOCKS
+#define MOSS_LOSS_SPLIT_MINBLOCKS 2              // resident per-channel blocks per SM the register budget allows
+#endif
+#ifndef MOSS_LOSS_NOSPLIT_MINBLOCKS
+#define MOSS_LOSS_NOSPLIT_MINBLOCKS 2            // per-tile blocks: two resident 8-warp blocks per SM
+#endif
+constexpr int LOSS_SPLIT_THREADS = MOSS_LOSS_SPLIT_THREADS;
+
+template <int LOSS_THREADS, bool CSPLIT>
+__global__ void __launch_bounds__(LOSS_THREADS, CSPLIT ? MOSS_LOSS_SPLIT_MINBLOCKS : MOSS_LOSS_NOSPLIT_MINBLOCKS)
 image_losses_kernel(const __grid_constant__ LossArgs a)
 {
+	constexpr int NCH = CSPLIT ? 1 : 3;                                                       // channels of this block
+	const int ch_first = CSPLIT ? (int)blockIdx.z : 0;
 	constexpr int LOSS_PIX = LOSS_T * LOSS_T / LOSS_THREADS;                                  // output pixels per thread
 	constexpr int LOSS_S3_PTS = (LOSS_MID * LOSS_S3_W + LOSS_THREADS - 1) / LOSS_THREADS;     // S3IM map points per thread
 	static_assert(LOSS_T * LOSS_T % LOSS_THREADS == 0 && (LOSS_THREADS / 4) % 32 == 0, "whole pixels per thread, whole warps per loss");
@@ -102,20 +125,27 @@ image_losses_kernel(const __grid_constant__ LossArgs a)
 	// the crop, clipped to the image (a rectangle from moss_mask_bounds always lies inside)
 	const int rx = max(a.rect[0], 0), ry = max(a.rect[1], 0);
 	const int rw = max(min(a.rect[0] + a.rect[2], W) - rx, 0), rh = max(min(a.rect[1] + a.rect[3], H) - ry, 0), count = a.rect[4];
-	const int tx0 = blockIdx.x * LOSS_T, ty0 = blockIdx.y * LOSS_T;
+	// The tile grid is aligned to the CROP's corner, not to the image's (the launch has one extra tile column and row for
+	// that): a 254 x 383 crop then meets 8 x 12 tiles instead of 8 x 13 with two partial rows -- at ZJU size the difference
+	// between one resident wave of per-channel blocks and a wave plus a tail.
+	const int tx0 = (int)blockIdx.x * LOSS_T - ((LOSS_T - (rw > 0 && rh > 0 ? rx : 0) % LOSS_T) % LOSS_T);
+	const int ty0 = (int)blockIdx.y * LOSS_T - ((LOSS_T - (rw > 0 && rh > 0 ? ry : 0) % LOSS_T) % LOSS_T);
 	const bool ssim_on = (a.w_ssim != 0.f || a.w_s3im != 0.f) && rw > 0 && rh > 0 &&
 		tx0 < rx + rw && tx0 + LOSS_T > rx && ty0 < ry + rh && ty0 + LOSS_T > ry;
 	auto in_rect = [&](int x, int y) { return x >= rx && x < rx + rw && y >= ry && y < ry + rh; };
 
-	float grad[LOSS_PIX][3];        // dL/dimage of this thread's pixels: pixel k is tile-local (tid + k*256)
+	float grad[LOSS_PIX][NCH];      // dL/dimage of this thread's pixels: pixel k is tile-local (tid + k*LOSS_THREADS)
 #pragma unroll
-	for (int k = 0; k < LOSS_PIX; k++) grad[k][0] = grad[k][1] = grad[k][2] = 0.f;
+	for (int k = 0; k < LOSS_PIX; k++)
+#pragma unroll
+		for (int c = 0; c < NCH; c++) grad[k][c] = 0.f;
 	float sum_l1 = 0.f, sum_l2 = 0.f, sum_ssim = 0.f, sum_s3 = 0.f;
 
 	if (ssim_on) {
 		const float k_ssim = -a.w_ssim / (3.f * (float)rw * (float)rh);                       // d/dmap of w (1 - mean(map))
 		const float k_s3 = -a.w_s3im / (3.f * (float)rw * (float)rh * (float)LOSS_S3_REP);
-		for (int ch = 0; ch < 3; ch++) {
+		for (int c = 0; c < NCH; c++) {
+			const int ch = ch_first + c;
 			const float* img = a.image + ch * N;
 			const float* gt = a.gt + ch * N;
 			// ---- A: tile + halo, zero outside the crop -------------------------------------------------------------------
@@ -187,7 +217,7 @@ image_losses_kernel(const __grid_constant__ LossArgs a)
 						for (int q = 0; q < 3; q++) o[q] = fmaf(w, s_h[q * LOSS_MID * LOSS_T + (py + t) * LOSS_T + px], o[q]);
 					}
 					const float u = s_in1[(py + 2 * LOSS_R) * LOSS_IN + px + 2 * LOSS_R], v = s_in2[(py + 2 * LOSS_R) * LOSS_IN + px + 2 * LOSS_R];
-					grad[k][ch] += k_ssim * (o[0] + 2.f * u * o[1] + v * o[2]);
+					grad[k][c] += k_ssim * (o[0] + 2.f * u * o[1] + v * o[2]);
 				}
 				__syncthreads();
 			}
@@ -267,7 +297,7 @@ image_losses_kernel(const __grid_constant__ LossArgs a)
 						}
 					}
 					const float u = s_in1[(py + 2 * LOSS_R) * LOSS_IN + px + 2 * LOSS_R], v = s_in2[(py + 2 * LOSS_R) * LOSS_IN + px + 2 * LOSS_R];
-					grad[k][ch] += k_s3 * (o[0] + 2.f * u * o[1] + v * o[2]);
+					grad[k][c] += k_s3 * (o[0] + 2.f * u * o[1] + v * o[2]);
 				}
 				__syncthreads();
 			}
@@ -279,18 +309,19 @@ image_losses_kernel(const __grid_constant__ LossArgs a)
 #pragma unroll
 	for (int k = 0; k < LOSS_PIX; k++) {
 		const int p = tid + k * LOSS_THREADS, x = tx0 + p % LOSS_T, y = ty0 + p / LOSS_T;
-		if (x >= W || y >= H) continue;
+		if (x < 0 || y < 0 || x >= W || y >= H) continue;
 		const size_t o = (size_t)y * W + x;
 		const bool bound = a.bound ? __ldg(a.bound + o) == 1.f : true;
 		float d_alpha = 0.f;
 		if (bound) {
 #pragma unroll
-			for (int ch = 0; ch < 3; ch++) {
+			for (int c = 0; c < NCH; c++) {
+				const int ch = ch_first + c;
 				const float d = __ldg(a.image + ch * N + o) - __ldg(a.gt + ch * N + o);
 				sum_l1 += fabsf(d);
-				grad[k][ch] += d > 0.f ? k_l1 : (d < 0.f ? -k_l1 : 0.f);
+				grad[k][c] += d > 0.f ? k_l1 : (d < 0.f ? -k_l1 : 0.f);
 			}
-			if (a.alpha && a.bkgd) {
+			if (ch_first == 0 && a.alpha && a.bkgd) {
 				const float d = __ldg(a.alpha + o) - __ldg(a.bkgd + o);
 				sum_l2 = fmaf(d, d, sum_l2);
 				d_alpha = k_l2 * d;
@@ -298,9 +329,9 @@ image_losses_kernel(const __grid_constant__ LossArgs a)
 		}
 		if (a.dL_dimage) {
 #pragma unroll
-			for (int ch = 0; ch < 3; ch++) a.dL_dimage[ch * N + o] = grad[k][ch];
+			for (int c = 0; c < NCH; c++) a.dL_dimage[(ch_first + c) * N + o] = grad[k][c];
 		}
-		if (a.dL_dalpha) a.dL_dalpha[o] = d_alpha;
+		if (ch_first == 0 && a.dL_dalpha) a.dL_dalpha[o] = d_alpha;
 	}
 
 	// ---- block sums, then the last block adds the per-block sums in block order ----------------------------------------------
@@ -312,7 +343,7 @@ image_losses_kernel(const __grid_constant__ LossArgs a)
 		if (lane == 0) s_red[warp][q] = v[q];
 	}
 	__syncthreads();
-	const int bid = blockIdx.y * gridDim.x + blockIdx.x, nblocks = gridDim.x * gridDim.y;
+	const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x, nblocks = gridDim.x * gridDim.y * gridDim.z;
 	if (tid < 4) {
 		float s = 0.f;
 #pragma unroll

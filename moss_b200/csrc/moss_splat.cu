@@ -918,7 +918,26 @@ int moss_smpl_frame_backward(void* stream_, const MossSmplFrame* f, const float*
 }
 
 // ---- image-space losses ------------------------------------------------------------------------------------------------
-static int loss_blocks(int W, int H) { return ((W + LOSS_T - 1) / LOSS_T) * ((H + LOSS_T - 1) / LOSS_T); }
+// blocks of the launch: the tile grid is aligned to the crop's corner (loss.cuh), hence one extra column and row
+static long long loss_tiles(int W, int H) { return (long long)((W + LOSS_T - 1) / LOSS_T + 1) * (long long)((H + LOSS_T - 1) / LOSS_T + 1); }
+// few tiles (<= two per SM): one block per (tile, colour channel), 16 warps each; many tiles: one 8-warp block per tile
+static bool loss_channel_split(int W, int H) { return loss_tiles(W, H) <= LOSS_CSPLIT_MAX_TILES; }
+static long long loss_blocks(int W, int H) { return loss_tiles(W, H) * (loss_channel_split(W, H) ? 3 : 1); }
+static cudaError_t loss_set_attributes()
+{
+	// > 48 KB of dynamic shared memory is opt-in; two resident blocks need 174 KB, so ask for the largest carve-out
+	cudaError_t e = cudaFuncSetAttribute(image_losses_kernel<256, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM);
+	if (e == cudaSuccess) e = cudaFuncSetAttribute(image_losses_kernel<256, false>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+	if (e == cudaSuccess) e = cudaFuncSetAttribute(image_losses_kernel<LOSS_SPLIT_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM);
+	if (e == cudaSuccess) e = cudaFuncSetAttribute(image_losses_kernel<LOSS_SPLIT_THREADS, true>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+	return e;
+}
+static void loss_launch(const LossArgs& a, cudaStream_t stream)
+{
+	const dim3 tiles((a.W + LOSS_T - 1) / LOSS_T + 1, (a.H + LOSS_T - 1) / LOSS_T + 1);
+	if (loss_channel_split(a.W, a.H)) image_losses_kernel<LOSS_SPLIT_THREADS, true><<<dim3(tiles.x, tiles.y, 3), LOSS_SPLIT_THREADS, LOSS_DYN_SMEM, stream>>>(a);
+	else image_losses_kernel<256, false><<<tiles, 256, LOSS_DYN_SMEM, stream>>>(a);
+}
 size_t moss_image_losses_scratch_bytes(int W, int H)
 {
 	if (W < 1 || H < 1) return 16;
@@ -952,8 +971,7 @@ int moss_image_losses(void* stream_, const MossImageLoss* k, float* losses, floa
 	int dev = 0;                            // opt in to > 48 KB of dynamic shared memory (the attribute is per device)
 	MOSS_CUDA_TRY(cudaGetDevice(&dev));
 	if (dev >= 0 && dev < MAX_DEVICES && !g_loss_attr_set[dev].load(std::memory_order_acquire)) {
-		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
-		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
+		MOSS_CUDA_TRY(loss_set_attributes());
 		g_loss_attr_set[dev].store(true, std::memory_order_release);
 	}
 	LossArgs a;
@@ -962,11 +980,8 @@ int moss_image_losses(void* stream_, const MossImageLoss* k, float* losses, floa
 	loss_window(a.g, a.s3);
 	a.dL_dimage = dL_dimage; a.dL_dalpha = dL_dalpha; a.losses = losses;
 	a.ticket = (unsigned*)k->scratch; a.partial = (float*)((char*)k->scratch + 16);
-	const dim3 grid((k->W + LOSS_T - 1) / LOSS_T, (k->H + LOSS_T - 1) / LOSS_T);
 	{ MOSS_STAGE(MOSS_STAGE_IMAGE_LOSSES, stream);
-		// few tiles (<= two per SM): 16 warps per tile; many tiles: two resident 8-warp blocks per SM
-		if (grid.x * grid.y <= 2 * 148) image_losses_kernel<512><<<grid, 512, LOSS_DYN_SMEM, stream>>>(a);
-		else image_losses_kernel<256><<<grid, 256, LOSS_DYN_SMEM, stream>>>(a); }
+		loss_launch(a, stream); }
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }
@@ -977,7 +992,9 @@ int moss_image_losses(void* stream_, const MossImageLoss* k, float* losses, floa
 // cudaGetSymbolAddress, once per device with that device current, and is what the kernel receives.
 static __device__ __align__(256) unsigned char g_loss_static_scratch[MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES];
 static std::atomic<void*> g_loss_static_ptr[MAX_DEVICES];
-static_assert(MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES >= 16 + 16 * MOSS_IMAGE_LOSSES_STATIC_MAX_TILES, "static scratch holds ticket + partial sums");
+// ceil(W/32) * ceil(H/32) <= MAX_TILES bounds the launch's (ceil(W/32) + 1) * (ceil(H/32) + 1) blocks by 2 * MAX_TILES + 2
+static_assert(MOSS_IMAGE_LOSSES_STATIC_SCRATCH_BYTES >= 16 + 16 * (2 * MOSS_IMAGE_LOSSES_STATIC_MAX_TILES + 2), "static scratch holds ticket + partial sums");
+static_assert(3 * LOSS_CSPLIT_MAX_TILES <= MOSS_IMAGE_LOSSES_STATIC_MAX_TILES, "the per-channel blocks of a small image fit the static scratch too");
 
 int moss_image_losses_static(void* stream_, const MossImageLoss* k, float* losses, float* dL_dimage, float* dL_dalpha)
 {
@@ -995,8 +1012,7 @@ int moss_image_losses_static(void* stream_, const MossImageLoss* k, float* losse
 		if (dev >= 0 && dev < MAX_DEVICES) g_loss_static_ptr[dev].store(scratch, std::memory_order_release);
 	}
 	if (dev >= 0 && dev < MAX_DEVICES && !g_loss_attr_set[dev].load(std::memory_order_acquire)) {
-		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
-		MOSS_CUDA_TRY(cudaFuncSetAttribute(image_losses_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LOSS_DYN_SMEM));
+		MOSS_CUDA_TRY(loss_set_attributes());
 		g_loss_attr_set[dev].store(true, std::memory_order_release);
 	}
 	LossArgs a;
@@ -1007,10 +1023,8 @@ int moss_image_losses_static(void* stream_, const MossImageLoss* k, float* losse
 	a.ticket = (unsigned*)scratch; a.partial = (float*)((char*)scratch + 16);
 	// the array keeps the last call's contents: the ticket must be zero on entry (the partial sums are fully rewritten)
 	MOSS_CUDA_TRY(cudaMemsetAsync(scratch, 0, 16, stream));
-	const dim3 grid((k->W + LOSS_T - 1) / LOSS_T, (k->H + LOSS_T - 1) / LOSS_T);
 	g_launches.fetch_add(1, std::memory_order_relaxed);          // no MOSS_STAGE here: the profiler creates events
-	if (grid.x * grid.y <= 2 * 148) image_losses_kernel<512><<<grid, 512, LOSS_DYN_SMEM, stream>>>(a);
-	else image_losses_kernel<256><<<grid, 256, LOSS_DYN_SMEM, stream>>>(a);
+	loss_launch(a, stream);
 	MOSS_CHECK_LAUNCH(stream, 0);
 	return MOSS_OK;
 }
