@@ -447,7 +447,11 @@ long long moss_export_state_batch(void* stream, const MossScene* scene, int V, i
 #define MOSS_STAGE_SMPL_FRAME_BWD  17
 #define MOSS_STAGE_IMAGE_LOSSES    18
 #define MOSS_STAGE_COUNT           19
+/*   moss_nvtx_enable(1) (or MOSS_NVTX=1 in the environment): one NVTX range per C-ABI call, named like the entry point, and
+ *   one per kernel launch inside it, named like moss_stage_name(); `ncu --nvtx --nvtx-include "moss_rasterize_backward/"`
+ *   or an nsys timeline then attribute every launch.  Off by default; a no-op without a tool. */
 unsigned long long moss_kernel_launches(void);
+int moss_nvtx_enable(int on);
 int moss_profile_enable(int on);
 int moss_profile_read(double* ms, unsigned long long* launches);
 const char* moss_stage_name(int stage);

@@ -36,7 +36,7 @@ SYMBOLS = [
     "moss_binning_workspace_bytes_ex", "moss_binning_capacity", "moss_ckpt_workspace_bytes", "moss_rasterize_forward",
     "moss_rasterize_backward", "moss_mark_visible", "moss_export_state", "moss_abi_version",
     "moss_error_string", "moss_last_cuda_error", "moss_sizeof_scene", "moss_kernel_launches",
-    "moss_profile_enable", "moss_profile_read", "moss_stage_name",
+    "moss_profile_enable", "moss_profile_read", "moss_stage_name", "moss_nvtx_enable",
     "moss_geom_workspace_bytes_batch", "moss_image_workspace_bytes_batch", "moss_ckpt_workspace_bytes_batch",
     "moss_batch_grad_workspace_bytes", "moss_rasterize_forward_batch", "moss_rasterize_backward_batch", "moss_sizeof_view",
     "moss_export_state_batch", "moss_push_slice_floats", "moss_sizeof_push", "moss_rasterize_backward_push", "moss_push_allreduce",
@@ -154,6 +154,8 @@ def load():
     lib.moss_kernel_launches.restype = C.c_ulonglong
     lib.moss_profile_enable.restype = C.c_int
     lib.moss_profile_enable.argtypes = [C.c_int]
+    lib.moss_nvtx_enable.restype = C.c_int
+    lib.moss_nvtx_enable.argtypes = [C.c_int]
     lib.moss_profile_read.restype = C.c_int
     lib.moss_profile_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_ulonglong)]
     lib.moss_stage_name.restype = C.c_char_p

@@ -7,7 +7,9 @@
 // In synchronous mode the host waits only for an event recorded right after K2 (so K3/K4 are already queued
 // behind it and the GPU never idles) to learn num_rendered and detect binning-buffer overflow.
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>      // header-only (v3): resolves the tool's injection library at the first call, a no-op without one
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <math.h>
 #include <mutex>
@@ -98,10 +100,43 @@ struct Profiler {
 	}
 };
 Profiler g_prof;
+
+// NVTX ranges: one range per C-ABI call ("moss_rasterize_forward", ...) and one per kernel launch
+// inside it, named like the profiler's stages, so `ncu --nvtx --nvtx-include "moss_rasterize_backward/"` (or an nsys
+// timeline) attributes every launch.  Off by default; MOSS_NVTX=1 in the environment or moss_nvtx_enable(1) turns it on.
+std::atomic<int> g_nvtx{-1};          // -1: not decided yet (read MOSS_NVTX once)
+inline bool nvtx_on()
+{
+	int v = g_nvtx.load(std::memory_order_relaxed);
+	if (v < 0) {
+		const char* e = getenv("MOSS_NVTX");
+		v = (e && *e && *e != '0') ? 1 : 0;
+		g_nvtx.store(v, std::memory_order_relaxed);
+	}
+	return v != 0;
+}
+const char* stage_name(int stage)
+{
+	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
+		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step", "sum_views", "push_gather", "smpl_frame_forward", "smpl_frame_backward", "image_losses"};
+	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
+}
+struct ApiRange {
+	bool on;
+	explicit ApiRange(const char* name) : on(nvtx_on()) { if (on) nvtxRangePushA(name); }
+	~ApiRange() { if (on) nvtxRangePop(); }
+};
+#define MOSS_API_RANGE(name) ApiRange api_range__(name)
+
 struct StageScope {
-	cudaStream_t s; bool on;
-	StageScope(int stage, cudaStream_t s_) : s(s_), on(g_prof.on) { g_launches.fetch_add(1, std::memory_order_relaxed); if (on) g_prof.begin(stage, s); }
-	~StageScope() { if (on) g_prof.end(s); }
+	cudaStream_t s; bool on, nvtx;
+	StageScope(int stage, cudaStream_t s_) : s(s_), on(g_prof.on), nvtx(nvtx_on())
+	{
+		g_launches.fetch_add(1, std::memory_order_relaxed);
+		if (nvtx) nvtxRangePushA(stage_name(stage));
+		if (on) g_prof.begin(stage, s);
+	}
+	~StageScope() { if (on) g_prof.end(s); if (nvtx) nvtxRangePop(); }
 };
 #define MOSS_STAGE(stage, stream) StageScope stage_scope__(stage, stream)
 
@@ -290,11 +325,11 @@ int moss_profile_read(double* ms, unsigned long long* launches)
 	}
 	return r;
 }
-const char* moss_stage_name(int stage)
+const char* moss_stage_name(int stage) { return stage_name(stage); }
+int moss_nvtx_enable(int on)
 {
-	static const char* names[MOSS_STAGE_COUNT] = {"preprocess_forward", "tile_scan", "scatter_keys", "blend_forward",
-		"blend_backward", "preprocess_backward", "other", "tile_sort", "skin_forward", "skin_backward", "peer_allreduce", "nearest_vertex", "densify_stats", "adamw_step", "sum_views", "push_gather", "smpl_frame_forward", "smpl_frame_backward", "image_losses"};
-	return (stage >= 0 && stage < MOSS_STAGE_COUNT) ? names[stage] : "?";
+	g_nvtx.store(on ? 1 : 0, std::memory_order_relaxed);
+	return MOSS_OK;
 }
 int moss_last_cuda_error(void) { return g_last_cuda_error; }
 
@@ -643,6 +678,7 @@ size_t moss_push_slice_floats(size_t numel, int world)
 }
 int moss_push_allreduce(void* stream_, const MossPush* push)
 {
+	MOSS_API_RANGE("moss_push_allreduce");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (!push) return MOSS_ERR_INVALID_ARGUMENT;
 	PushCfg pc; GatherArgs ga; unsigned blocks = 0;
@@ -660,6 +696,7 @@ int moss_rasterize_backward_push(void* stream, const MossScene* sc, int V, const
 	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* tmp_ws, size_t tmp_bytes,
 	const MossPush* push)
 {
+	MOSS_API_RANGE("moss_rasterize_backward_push");
 	if (!push || (!views && V != 1)) return MOSS_ERR_INVALID_ARGUMENT;
 	return backward_impl((cudaStream_t)stream, sc, V, views, flags, radii, dL_dpix, dL_ddepth, dL_dalpha, dL_dmean2D, dL_dconic,
 		dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, tmp_ws, tmp_bytes, push);
@@ -673,11 +710,13 @@ size_t moss_batch_grad_workspace_bytes(int P, int M, int V)
 int moss_rasterize_forward(void* stream, const MossScene* sc, unsigned flags,
 	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
 {
+	MOSS_API_RANGE("moss_rasterize_forward");
 	return forward_impl((cudaStream_t)stream, sc, 1, nullptr, flags, out_color, out_depth, out_alpha, radii, num_rendered);
 }
 int moss_skin_rasterize_forward(void* stream, const MossScene* sc, const MossSkin* skin, unsigned flags,
 	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered, float* means3D, float* transforms)
 {
+	MOSS_API_RANGE("moss_skin_rasterize_forward");
 	if (!skin) return MOSS_ERR_INVALID_ARGUMENT;
 	return forward_impl((cudaStream_t)stream, sc, 1, nullptr, flags, out_color, out_depth, out_alpha, radii, num_rendered, skin, means3D, transforms);
 }
@@ -686,6 +725,7 @@ int moss_skin_rasterize_backward(void* stream, const MossScene* sc, const MossSk
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_dsh,
 	float* d_xyz, float* d_scaling, float* d_rotation, float* d_lbs_delta, float* d_A_tgt, float* d_poseoff_tgt)
 {
+	MOSS_API_RANGE("moss_skin_rasterize_backward");
 	if (!skin) return MOSS_ERR_INVALID_ARGUMENT;
 	SkinGradOut sg;
 	sg.d_xyz = d_xyz; sg.d_scaling = d_scaling; sg.d_rotation = d_rotation; sg.d_lbs_delta = d_lbs_delta;
@@ -696,6 +736,7 @@ int moss_skin_rasterize_backward(void* stream, const MossScene* sc, const MossSk
 int moss_rasterize_forward_batch(void* stream, const MossScene* sc, int V, const MossView* views, unsigned flags,
 	float* out_color, float* out_depth, float* out_alpha, int* radii, int* num_rendered)
 {
+	MOSS_API_RANGE("moss_rasterize_forward_batch");
 	if (!views) return MOSS_ERR_INVALID_ARGUMENT;
 	return forward_impl((cudaStream_t)stream, sc, V, views, flags, out_color, out_depth, out_alpha, radii, num_rendered);
 }
@@ -704,6 +745,7 @@ int moss_rasterize_backward(void* stream, const MossScene* sc, unsigned flags, c
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
 	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot)
 {
+	MOSS_API_RANGE("moss_rasterize_backward");
 	if (!dL_dconic) return MOSS_ERR_INVALID_ARGUMENT;
 	return backward_impl((cudaStream_t)stream, sc, 1, nullptr, flags, radii, dL_dpix, dL_ddepth, dL_dalpha, dL_dmean2D, dL_dconic,
 		dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, 0);
@@ -713,6 +755,7 @@ int moss_rasterize_backward_batch(void* stream, const MossScene* sc, int V, cons
 	float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
 	float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, void* tmp_ws, size_t tmp_bytes)
 {
+	MOSS_API_RANGE("moss_rasterize_backward_batch");
 	if (!views) return MOSS_ERR_INVALID_ARGUMENT;
 	return backward_impl((cudaStream_t)stream, sc, V, views, flags, radii, dL_dpix, dL_ddepth, dL_dalpha, dL_dmean2D, dL_dconic,
 		dL_dopacity, dL_dcolor, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, tmp_ws, tmp_bytes);
@@ -721,6 +764,7 @@ int moss_rasterize_backward_batch(void* stream, const MossScene* sc, int V, cons
 int moss_mark_visible(void* stream_, int P, const float* means3D, const float* viewmatrix,
 	const float* projmatrix, uint8_t* present)
 {
+	MOSS_API_RANGE("moss_mark_visible");
 	(void)projmatrix;
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (P < 0) return MOSS_ERR_INVALID_ARGUMENT;
@@ -816,6 +860,7 @@ size_t moss_sizeof_skin(void) { return sizeof(MossSkin); }
 int moss_skin_forward(void* stream_, const MossSkin* k, float* means3D, float* cov3D, float* transforms,
 	float* bweights, float* translation)
 {
+	MOSS_API_RANGE("moss_skin_forward");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (!skin_valid(k)) return MOSS_ERR_INVALID_ARGUMENT;
 	if (k->P == 0) return MOSS_OK;
@@ -830,6 +875,7 @@ int moss_skin_forward(void* stream_, const MossSkin* k, float* means3D, float* c
 int moss_skin_backward(void* stream_, const MossSkin* k, const float* g_means3D, const float* g_cov3D,
 	float* d_xyz, float* d_scaling, float* d_rotation, float* d_lbs_delta, float* d_A_tgt, float* d_poseoff_tgt)
 {
+	MOSS_API_RANGE("moss_skin_backward");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (!skin_valid(k)) return MOSS_ERR_INVALID_ARGUMENT;
 	if (d_A_tgt) MOSS_CUDA_TRY(cudaMemsetAsync(d_A_tgt, 0, sizeof(float) * NJ * 16, stream));
@@ -866,6 +912,7 @@ static bool smpl_frame_valid(const MossSmplFrame* f)
 int moss_smpl_joint_tables(void* stream_, int V, int S, const float* v_template, const float* shapedirs,
 	const float* J_regressor, float* J_template, float* J_shapedirs)
 {
+	MOSS_API_RANGE("moss_smpl_joint_tables");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (V < 1 || S < 0 || !v_template || !J_regressor || !J_template || (S > 0 && (!shapedirs || !J_shapedirs)))
 		return MOSS_ERR_INVALID_ARGUMENT;
@@ -878,6 +925,7 @@ int moss_smpl_joint_tables(void* stream_, int V, int S, const float* v_template,
 int moss_smpl_frame_forward(void* stream_, const MossSmplFrame* f, float* A, float* rot_mats, float* joints,
 	float* poseoff, float* shapeoff)
 {
+	MOSS_API_RANGE("moss_smpl_frame_forward");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (!smpl_frame_valid(f) || !A || !f->J_template || (f->n_shapes > 0 && !f->J_shapedirs) || (poseoff && !f->posedirs) ||
 		(shapeoff && f->n_shapes > 0 && !f->shapedirs)) return MOSS_ERR_INVALID_ARGUMENT;
@@ -897,6 +945,7 @@ int moss_smpl_frame_forward(void* stream_, const MossSmplFrame* f, float* A, flo
 int moss_smpl_frame_backward(void* stream_, const MossSmplFrame* f, const float* A, const float* joints,
 	const float* d_A, const float* d_poseoff, float* d_poses, float* d_correct_Rs)
 {
+	MOSS_API_RANGE("moss_smpl_frame_backward");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (!smpl_frame_valid(f) || !A || !joints || !d_poses || (d_poseoff && !f->posedirs) || !f->scratch ||
 		f->scratch_bytes < moss_smpl_frame_scratch_bytes(f->V) || ((uintptr_t)f->scratch & 15)) return MOSS_ERR_INVALID_ARGUMENT;
@@ -964,6 +1013,7 @@ static void loss_window(float* g, float (*s3)[3])
 
 int moss_image_losses(void* stream_, const MossImageLoss* k, float* losses, float* dL_dimage, float* dL_dalpha)
 {
+	MOSS_API_RANGE("moss_image_losses");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (!k || k->W < 1 || k->H < 1 || !k->image || !k->gt_image || !k->rect || !losses || !k->scratch ||
 		k->scratch_bytes < moss_image_losses_scratch_bytes(k->W, k->H) || ((uintptr_t)k->scratch & 15)) return MOSS_ERR_INVALID_ARGUMENT;
@@ -998,6 +1048,7 @@ static_assert(3 * LOSS_CSPLIT_MAX_TILES <= MOSS_IMAGE_LOSSES_STATIC_MAX_TILES, "
 
 int moss_image_losses_static(void* stream_, const MossImageLoss* k, float* losses, float* dL_dimage, float* dL_dalpha)
 {
+	MOSS_API_RANGE("moss_image_losses_static");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (!k || k->W < 1 || k->H < 1 || !k->image || !k->gt_image || !k->rect || !losses) return MOSS_ERR_INVALID_ARGUMENT;
 	if (k->w_mask != 0.f && (!k->alpha || !k->bkgd_mask)) return MOSS_ERR_INVALID_ARGUMENT;
@@ -1031,6 +1082,7 @@ int moss_image_losses_static(void* stream_, const MossImageLoss* k, float* losse
 
 int moss_mask_bounds(void* stream_, int W, int H, const float* mask, int* out)
 {
+	MOSS_API_RANGE("moss_mask_bounds");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (W < 1 || H < 1 || !mask || !out) return MOSS_ERR_INVALID_ARGUMENT;
 	MOSS_CUDA_TRY(cudaMemsetAsync(out, 0x7f, 2 * sizeof(int), stream));
@@ -1058,6 +1110,7 @@ int moss_scale_gradients(void* stream_, const float* scale_dev, float* a, size_t
 
 int moss_nearest_vertex(void* stream_, int P, const float* xyz, int V, const float* verts, int* vert_ids, float* dist)
 {
+	MOSS_API_RANGE("moss_nearest_vertex");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (P < 0 || V < 1) return MOSS_ERR_INVALID_ARGUMENT;
 	if (P == 0) return MOSS_OK;
@@ -1072,6 +1125,7 @@ size_t moss_vertex_grid_bytes(int V) { return V < 1 ? 0 : vertex_grid_bytes(V); 
 
 int moss_vertex_grid_build(void* stream_, int V, const float* verts, void* grid, size_t grid_bytes)
 {
+	MOSS_API_RANGE("moss_vertex_grid_build");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (V < 1 || !verts || !grid || ((uintptr_t)grid & 15) || grid_bytes < vertex_grid_bytes(V)) return MOSS_ERR_INVALID_ARGUMENT;
 	{ MOSS_STAGE(MOSS_STAGE_OTHER, stream);
@@ -1083,6 +1137,7 @@ int moss_vertex_grid_build(void* stream_, int V, const float* verts, void* grid,
 int moss_nearest_vertex_grid(void* stream_, int P, const float* xyz, int V, const void* grid, size_t grid_bytes,
 	int* vert_ids, float* dist)
 {
+	MOSS_API_RANGE("moss_nearest_vertex_grid");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (P < 0 || V < 1 || !grid || ((uintptr_t)grid & 15) || grid_bytes < vertex_grid_bytes(V)) return MOSS_ERR_INVALID_ARGUMENT;
 	if (P == 0) return MOSS_OK;
@@ -1096,6 +1151,7 @@ int moss_nearest_vertex_grid(void* stream_, int P, const float* xyz, int V, cons
 int moss_densify_stats(void* stream_, int P, const int* radii, const float* dL_dmean2D, float* xyz_gradient_accum,
 	float* denom, float* max_radii2D)
 {
+	MOSS_API_RANGE("moss_densify_stats");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (P < 0) return MOSS_ERR_INVALID_ARGUMENT;
 	if (P == 0) return MOSS_OK;
@@ -1111,6 +1167,7 @@ size_t moss_sizeof_adam_group(void) { return sizeof(MossAdamGroup); }
 int moss_adamw_step(void* stream_, int n_groups, const MossAdamGroup* groups, double beta1, double beta2, double eps,
 	double weight_decay)
 {
+	MOSS_API_RANGE("moss_adamw_step");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (n_groups < 0 || n_groups > ADAM_MAX_GROUPS || (n_groups && !groups)) return MOSS_ERR_INVALID_ARGUMENT;
 	AdamGroups a;
@@ -1147,6 +1204,7 @@ int moss_peer_allreduce(void* stream_, int rank, int world, void* const* buffer_
 	size_t signal_pad_bytes, size_t offset_floats, size_t numel, unsigned epoch, unsigned* error_word_dev,
 	void* multicast_ptr)
 {
+	MOSS_API_RANGE("moss_peer_allreduce");
 	cudaStream_t stream = (cudaStream_t)stream_;
 	if (world < 1 || world > PEER_MAX_WORLD || rank < 0 || rank >= world || !buffer_ptrs_dev || !signal_ptrs_dev ||
 		!error_word_dev || (offset_floats & 3) || signal_pad_bytes < moss_peer_signal_bytes(world))
