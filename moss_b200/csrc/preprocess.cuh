@@ -352,6 +352,11 @@ preprocess_forward_kernel(const __grid_constant__ ViewBatch vb,
 		const float radius_f = ceilf(fmul(fsqrt(lmax), 3.f));
 		const float pix_x = ndc_to_pix(ndc_x, vb.W), pix_y = ndc_to_pix(ndc_y, vb.H);
 		const int ri = (int)radius_f;              // DGR auxiliary.h:46 (float -> int max_radius)
+		// The low-pass filter keeps every finite covariance at radius >= 2; 0 means a NaN covariance (float -> int of NaN).
+		// The reference still counts such a Gaussian in num_rendered but never emits its key (radii > 0 test in
+		// duplicateWithKeys, DGR rasterizer_impl.cu:82), so its sorted list holds an UNINITIALISED entry that the blend
+		// kernels then use as a Gaussian index.  Here it is culled like any other invisible Gaussian.
+		if (ri <= 0) break;
 		const float rf = (float)ri;
 		const uint32_t gx = vb.grid_x, gy = vb.grid_y;
 		const uint32_t rminx = min(gx, (uint32_t)max(0, (int)fmul(fsub(pix_x, rf), 0.0625f)));

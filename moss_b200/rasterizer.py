@@ -569,6 +569,8 @@ def export_state(st, name, view=None):
         "counters": (torch.int32, (4,)), "view_base": (torch.int32, (V + 1,)),
     }[name]
     out = torch.empty(spec[1], dtype=spec[0], device=dev)
+    if out.numel() == 0:                 # nothing rendered (or P == 0): an empty list, no call with a null destination
+        return out
     with _abi.on_device(dev):
         n = lib.moss_export_state_batch(_abi.stream_ptr(dev), C.byref(sc), V, _abi.STATE[name],
                                         out.data_ptr(), out.numel() * out.element_size())

@@ -26,7 +26,11 @@ def _cov_from_scale_rot_python(scales, rotations, mod=1.0, transforms=None):
 def make_scene(name):
     """-> dict(means3D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp, cam, bg, sh_degree,
     scale_modifier).  Exactly one of shs/colors_precomp and one of (scales,rotations)/cov3D_precomp is not None."""
-    spec = SCENES[name]
+    return make_scene_from_spec(SCENES[name])
+
+
+def make_scene_from_spec(spec):
+    """The scene an entry of SCENES describes (also used by the randomised specs of tests/test_fuzz_gpu.py)."""
     P, W, H = spec["P"], spec["W"], spec["H"]
     if spec.get("stress"):
         sc = synth.stress_scene(P, W, H)
@@ -54,10 +58,17 @@ def make_scene(name):
         d["cov3D_precomp"] = _cov_from_scale_rot_python(d["scales"], d["rotations"], d["scale_modifier"], T)
         d["scales"] = None
         d["rotations"] = None
-    if spec.get("behind"):          # push some Gaussians behind / onto the near plane
+    if spec.get("behind"):          # push some Gaussians behind / onto the near plane (behind = 1.0: all of them, R = 0)
         m = d["means3D"]
-        idx = torch.from_numpy(rng.integers(0, P, P // 10))
+        frac = 0.1 if spec["behind"] is True else float(spec["behind"])
+        idx = torch.arange(P) if frac >= 1.0 else torch.from_numpy(rng.integers(0, P, max(int(P * frac), 1)))
         m[idx] = m[idx] + cam.camera_center.clone()[None] * 1.2
+    if spec.get("sh_M") and d["shs"] is not None:      # stored SH coefficients per Gaussian (1, 4, 9 or 16)
+        d["shs"] = d["shs"][:, :spec["sh_M"]].contiguous()
+    if spec.get("opacity_edges"):   # exactly transparent and exactly opaque Gaussians
+        idx = torch.from_numpy(rng.integers(0, P, max(P // 8, 1)))
+        d["opacities"][idx[: len(idx) // 2]] = 0.0
+        d["opacities"][idx[len(idx) // 2:]] = 1.0
     return d
 
 

@@ -60,7 +60,12 @@ def run_batch(d, cams, flags=0, grads=None, bflags=0):
                                           ("small_color", 4, 5), ("big_splats", 6, 3), ("tiny", 1, 1)])
 def test_every_view_of_a_batch_is_bit_exact_vs_reference(name, V, step, ref_mod):
     d = S.make_scene(name)
-    cams = _cams(d, V, step)
+    check_batch_vs_reference(d, _cams(d, V, step), ref_mod)
+
+
+def check_batch_vs_reference(d, cams, ref_mod):
+    """Every view of one batched call against one reference call per view (also driven by tests/test_fuzz_gpu.py)."""
+    V = len(cams)
     W, H = cams[0].image_width, cams[0].image_height
     gc, gd, ga = _upstream(V, W, H)
     o = run_batch(d, cams, flags=_abi.FLAG_EXPORT_KEYS, grads=(gc, gd, ga))

@@ -1,0 +1,117 @@
+"""GPU: randomised scenes against the UNMODIFIED reference rasterizer (the reference has no tests,
+so the new code brings property tests over random and degenerate inputs).  hypothesis draws the scene description --
+Gaussian count, image size (any W, H: not multiples of 16), active SH degree and stored coefficient count, SH or precomputed
+colours, scale + rotation or precomputed covariance, splat size from sub-pixel to screen-filling, camera inside / near / far,
+Gaussians behind the camera (up to all of them: nothing rendered), exactly transparent and exactly opaque splats, background
+-- and every example must give the reference's bits for radii, tile counts, the sorted key and ID lists, tile ranges,
+n_contrib, final_T and the three images, and its gradients within 1e-3 relative.  derandomize=True: the same examples in
+every run, so a pass here is a pass at the end of the round."""
+import os
+
+import pytest
+import torch
+
+hypothesis = pytest.importorskip("hypothesis")
+from hypothesis import given, settings, strategies as st, HealthCheck  # noqa: E402
+
+import moss_b200 as M  # noqa: E402
+from tests import scenes as S  # noqa: E402
+from moss_b200 import synth  # noqa: E402
+from tests.test_parity_gpu import run_ours, rel_err, _bits, GRAD_TOL, ref_mod  # noqa: E402,F401
+from tests.test_batch_gpu import check_batch_vs_reference  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+@st.composite
+def scene_specs(draw):
+    D = draw(st.integers(0, 3))
+    M_store = draw(st.sampled_from([m for m in (1, 4, 9, 16) if m >= (D + 1) ** 2]))
+    spec = dict(
+        P=draw(st.integers(4, 1500)), W=draw(st.integers(16, 260)), H=draw(st.integers(16, 260)),
+        D=D, sh_M=M_store, seed=draw(st.integers(0, 5)), cam=draw(st.integers(0, 22)),
+        radius=draw(st.sampled_from([0.6, 1.5, 3.0, 8.0])), mod=draw(st.sampled_from([0.5, 1.0, 2.0])),
+        scale_mul=draw(st.sampled_from([0.02, 0.3, 1.0, 4.0, 25.0])),
+        precomp_color=draw(st.booleans()), precomp_cov=draw(st.booleans()), transforms=draw(st.booleans()),
+        raw_quat=draw(st.booleans()), behind=draw(st.sampled_from([0, 0.1, 0.5, 1.0])),
+        opacity_edges=draw(st.booleans()),
+        bg=[draw(st.sampled_from([0.0, 0.25, 1.0])) for _ in range(3)],
+    )
+    return spec
+
+
+# MOSS_FUZZ_EXAMPLES=n / MOSS_FUZZ_RANDOM=1: a longer or a freshly seeded search (developer runs; the defaults are what CI runs)
+@settings(max_examples=int(os.environ.get("MOSS_FUZZ_EXAMPLES", "60")), deadline=None,
+          derandomize=not os.environ.get("MOSS_FUZZ_RANDOM"), database=None, suppress_health_check=list(HealthCheck))
+@given(spec=scene_specs(), with_depth=st.booleans())
+def test_random_scenes_equal_the_reference(ref_mod, spec, with_depth):  # noqa: F811
+    d = S.make_scene_from_spec(spec)
+    assert all(torch.isfinite(t).all() for t in d.values() if torch.is_tensor(t))     # NaN inputs: see test_nan_covariance_is_culled
+    cam = d["cam"]
+    grads = S.upstream_grads(cam.image_width, cam.image_height, seed=11 + spec["P"], depth=with_depth)
+    ref = ref_mod.RefCall(d)
+    rc, rr, rd, ra = ref.forward()
+    o = run_ours(d, grads=grads)
+    st_ = o["st"]
+    what = f"spec {spec}"
+    assert torch.equal(o["radii"], rr), what
+    assert torch.equal(M.export_state(st_, "tiles_touched"), ref.state("tiles_touched")), what
+    assert o["R"] == ref.R, what
+    for nm in ("keys_sorted", "point_list", "ranges", "n_contrib"):
+        assert torch.equal(M.export_state(st_, nm), ref.state(nm)), (nm, what)
+    assert torch.equal(_bits(M.export_state(st_, "final_T")), _bits(ref.state("final_T"))), what
+    for nm, a, b in (("color", o["color"], rc), ("depth", o["depth"], rd), ("alpha", o["alpha"], ra)):
+        assert torch.equal(_bits(a), _bits(b)), (nm, float((a - b).abs().max()), what)
+    rg = ref.backward(*grads)
+    og = o["grads"]
+    checks = ["means2D", "opacity", "means3D", "cov3D"]
+    checks += ["sh"] if d["shs"] is not None else ["colors"]
+    checks += ["scales", "rotations"] if d["scales"] is not None else []
+    for nm in checks:
+        assert torch.isfinite(og[nm]).all() == torch.isfinite(rg[nm]).all(), (nm, what)
+        if torch.isfinite(rg[nm]).all():
+            # tiny gradients (a handful of faint pixels) are compared against the tensor's own rounding floor
+            e = rel_err(og[nm], rg[nm])
+            floor = 1e-12 / max(float(rg[nm].double().norm()), 1e-30)
+            assert e <= GRAD_TOL + floor, (nm, e, what)
+    inv = ~(o["radii"] > 0)
+    for nm in checks:
+        assert float(og[nm][inv].abs().sum()) == 0.0, (nm, what)
+
+
+@settings(max_examples=int(os.environ.get("MOSS_FUZZ_EXAMPLES", "25")), deadline=None,
+          derandomize=not os.environ.get("MOSS_FUZZ_RANDOM"), database=None, suppress_health_check=list(HealthCheck))
+@given(spec=scene_specs(), V=st.integers(2, 5), first=st.integers(0, 22), step=st.integers(1, 11))
+def test_random_batches_equal_the_reference_view_by_view(ref_mod, spec, V, first, step):  # noqa: F811
+    """The batched call (view index folded into tile and Gaussian indices) on random scenes and random camera subsets."""
+    d = S.make_scene_from_spec(spec)
+    ring = synth.ring_cameras(23, spec["W"], spec["H"], radius=spec["radius"])
+    cams = [ring[(first + k * step) % 23] for k in range(V)]
+    check_batch_vs_reference(d, cams, ref_mod)
+
+
+def test_nan_covariance_is_culled():
+    """A NaN covariance gives radius 0 (float -> int of NaN).  The reference still counts the Gaussian in num_rendered but
+    never emits its key (DGR rasterizer_impl.cu:82), so its sorted list keeps an uninitialised entry that the blend kernels
+    use as an index; this library culls it: nothing rendered for it, finite outputs, zero gradient rows."""
+    d = S.make_scene("small")
+    d["scales"][::7] = float("nan")
+    grads = S.upstream_grads(d["cam"].image_width, d["cam"].image_height)
+    o = run_ours(d, grads=grads)
+    bad = torch.zeros(d["means3D"].shape[0], dtype=torch.bool, device=o["radii"].device)
+    bad[::7] = True
+    assert int((o["radii"][bad] != 0).sum()) == 0
+    assert int(M.export_state(o["st"], "tiles_touched")[bad].sum()) == 0
+    assert int((M.export_state(o["st"], "point_list").long() % 7 == 0).sum()) == 0      # none of them in the sorted list
+    for nm in ("color", "depth", "alpha"):
+        assert torch.isfinite(o[nm]).all(), nm
+    for nm, g in o["grads"].items():
+        if g is not None and g.numel():
+            assert torch.isfinite(g).all(), nm
+            assert float(g[bad].abs().sum()) == 0.0, nm
+    clean = S.make_scene("small")
+    keep = ~bad.cpu()
+    for k in ("means3D", "shs", "opacities", "scales", "rotations"):
+        clean[k] = clean[k][keep].contiguous()
+    oc = run_ours(clean)
+    assert torch.equal(o["color"], oc["color"]) and torch.equal(o["alpha"], oc["alpha"])   # as if they were not there
