@@ -115,3 +115,56 @@ def test_nan_covariance_is_culled():
         clean[k] = clean[k][keep].contiguous()
     oc = run_ours(clean)
     assert torch.equal(o["color"], oc["color"]) and torch.equal(o["alpha"], oc["alpha"])   # as if they were not there
+
+
+@st.composite
+def loss_cases(draw):
+    W, H = draw(st.integers(13, 200)), draw(st.integers(13, 200))
+    x0, y0 = draw(st.integers(0, W - 2)), draw(st.integers(0, H - 2))
+    x1, y1 = draw(st.integers(x0 + 1, W - 1)), draw(st.integers(y0 + 1, H - 1))
+    weights = draw(st.sampled_from([(1.0, 0.5, 0.2, 0.3), (1.0, 0.5, 0.2, 0.3), (0.0, 0.0, 1.0, 0.0), (0.0, 0.0, 0.0, 1.0), (1.0, 0.0, 0.0, 0.0)]))
+    return W, H, (x0, y0, x1, y1), draw(st.integers(0, 1000)), weights
+
+
+@settings(max_examples=int(os.environ.get("MOSS_FUZZ_EXAMPLES", "40")), deadline=None,
+          derandomize=not os.environ.get("MOSS_FUZZ_RANDOM"), database=None, suppress_health_check=list(HealthCheck))
+@given(case=loss_cases())
+def test_random_images_and_crops_equal_the_loss_oracle(case):
+    """The fused image-loss kernel on random image sizes and crop rectangles (anywhere in the image, touching its borders,
+    narrower than the 11-tap window, not aligned to the kernel's 32-pixel tiles) against the CPU oracle, which is pinned to
+    the real utils/loss_utils.py by tests/golden/loss_*.npz."""
+    from moss_b200 import losses as ML
+    from oracle import loss_oracle as LO
+    from tests.golden.make_loss_golden import synth_case
+    W, H, box, seed, w = case
+    image, alpha, gt, bkgd, bound = (torch.from_numpy(a) for a in synth_case(W, H, seed, box))
+    ic, ac = image.clone().requires_grad_(True), alpha.clone().requires_grad_(True)
+    total, t = LO.image_losses(ic, ac, gt, bkgd, bound, weights=w)
+    gi, ga = torch.autograd.grad(total, [ic, ac], allow_unused=True)
+    dev = "cuda:0"
+    ig, ag = image.to(dev).requires_grad_(True), alpha.to(dev).requires_grad_(True)
+    b = ML.mask_bounds(bound.to(dev))
+    assert b[:4].tolist() == [box[0], box[1], box[2] - box[0] + 1, box[3] - box[1] + 1], (case, b.tolist())
+    loss, terms = ML.image_losses(ig, ag, gt.to(dev), bkgd.to(dev), bound.to(dev), b, w)
+    loss.backward()
+    assert abs(float(loss.detach()) - float(total.detach())) <= 1e-5 * max(1.0, abs(float(total.detach()))), case
+    for got, ref in ((ig.grad, gi), (ag.grad, ga)):
+        ref = torch.zeros_like(got.cpu()) if ref is None else ref
+        scale = max(float(ref.abs().max()), 1e-30)
+        err = float((got.cpu().double() - ref.double().reshape(got.shape)).abs().max())
+        # absolute floor: a crop inside the rows where image == gt has a zero gradient, and both sides hold 1e-8 .. 1e-7 of rounding
+        assert err <= 5e-4 * scale + 1e-6, (case, err, scale)
+
+
+@settings(max_examples=int(os.environ.get("MOSS_FUZZ_EXAMPLES", "12")), deadline=None,
+          derandomize=not os.environ.get("MOSS_FUZZ_RANDOM"), database=None, suppress_health_check=list(HealthCheck))
+@given(P=st.integers(50, 3000), W=st.integers(48, 300), aspect=st.sampled_from([0.7, 1.0, 1.3]), seed=st.integers(0, 40),
+       with_delta=st.booleans())
+def test_random_fused_skin_rasterize_calls(P, W, aspect, seed, with_delta):
+    """The fused skin + rasterize call on random sizes, poses and LBS offsets: the two-step parity of tests/test_fused_gpu.py
+    (registers == front-end kernel, images / radii / binning == the unmodified reference rasterizer, gradients == the
+    two-call form)."""
+    from tests import test_fused_gpu as TF
+    H = max(int(W * aspect), 32)
+    TF.test_forward_two_step_parity(P, W, H, seed, with_delta)
+    TF.test_backward_matches_two_call_form(P, W, H, seed, with_delta)
