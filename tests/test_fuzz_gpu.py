@@ -77,6 +77,29 @@ def test_random_scenes_equal_the_reference(ref_mod, spec, with_depth):  # noqa: 
     inv = ~(o["radii"] > 0)
     for nm in checks:
         assert float(og[nm][inv].abs().sum()) == 0.0, (nm, what)
+    # the same scene through the public drop-in API (compiled autograd binding): the raw calls' outputs, bit for bit
+    from tests.test_parity_gpu import _settings
+    leaf = lambda t: None if t is None else t.to("cuda").requires_grad_(True)  # noqa: E731
+    t = {k: leaf(d[k]) for k in ("means3D", "shs", "colors_precomp", "opacities", "scales", "rotations", "cov3D_precomp")}
+    m2d = torch.zeros_like(t["means3D"], requires_grad=True)
+    color, radii, depth, alpha = M.GaussianRasterizer(_settings(d, "cuda"))(
+        means3D=t["means3D"], means2D=m2d, shs=t["shs"], colors_precomp=t["colors_precomp"], opacities=t["opacities"],
+        scales=t["scales"], rotations=t["rotations"], cov3D_precomp=t["cov3D_precomp"])
+    assert torch.equal(radii, o["radii"]), what
+    for a, b in ((color, o["color"]), (depth, o["depth"]), (alpha, o["alpha"])):
+        assert torch.equal(a, b), what
+    torch.autograd.backward([color, depth, alpha], [g.to("cuda") for g in grads])
+    api = dict(means2D=m2d.grad, opacity=t["opacities"].grad, means3D=t["means3D"].grad,
+               cov3D=None if t["cov3D_precomp"] is None else t["cov3D_precomp"].grad,
+               sh=None if t["shs"] is None else t["shs"].grad,
+               colors=None if t["colors_precomp"] is None else t["colors_precomp"].grad,
+               scales=None if t["scales"] is None else t["scales"].grad,
+               rotations=None if t["rotations"] is None else t["rotations"].grad)
+    for nm, g in api.items():
+        if g is None or (nm == "cov3D" and d["cov3D_precomp"] is None):
+            continue
+        ref_g = og[nm].reshape(g.shape)
+        assert rel_err(g, ref_g) <= 1e-5 + 1e-12 / max(float(ref_g.double().norm()), 1e-30), (nm, what)
 
 
 @settings(max_examples=int(os.environ.get("MOSS_FUZZ_EXAMPLES", "25")), deadline=None,
