@@ -91,6 +91,16 @@ class RefCall:
         dev, P, M = self.dev, self.P, self.M
         z = lambda *s: torch.zeros(s, device=dev)  # noqa: E731
         gc, gd, ga = (t.to(dev, torch.float32).contiguous() for t in (gc, gd, ga))
+        # The reference reads dL_ddepths[pix_id] / dL_dalphas[pix_id] for threads OUTSIDE the image too (missing braces at
+        # DGR/cuda_rasterizer/backward.cu:460-464): up to 15 rows past the end when H or W is not a multiple of 16.  With a
+        # tensor at the end of an allocator segment that is an illegal address (tests/test_zy_fuzz_gpu.py met it), so the two
+        # arrays are handed over with that many floats of slack behind them.  The values read there are never used.
+        slack = self.W * (((self.H + 15) // 16) * 16) + 16
+        def padded(t):
+            buf = torch.zeros(slack, device=dev)
+            buf[: t.numel()] = t.reshape(-1)
+            return buf
+        gd, ga = padded(gd), padded(ga)
         g = dict(means2D=z(P, 3), conic=z(P, 2, 2), opacity=z(P, 1), colors=z(P, 3), means3D=z(P, 3), cov3D=z(P, 6),
                  sh=z(P, M, 3), scales=z(P, 3), rotations=z(P, 4))
         torch.cuda.synchronize()

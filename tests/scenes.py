@@ -30,7 +30,7 @@ def make_scene(name):
 
 
 def make_scene_from_spec(spec):
-    """The scene an entry of SCENES describes (also used by the randomised specs of tests/test_fuzz_gpu.py)."""
+    """The scene an entry of SCENES describes (also used by the randomised specs of tests/test_zy_fuzz_gpu.py)."""
     P, W, H = spec["P"], spec["W"], spec["H"]
     if spec.get("stress"):
         sc = synth.stress_scene(P, W, H)

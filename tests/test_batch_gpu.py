@@ -64,7 +64,7 @@ def test_every_view_of_a_batch_is_bit_exact_vs_reference(name, V, step, ref_mod)
 
 
 def check_batch_vs_reference(d, cams, ref_mod):
-    """Every view of one batched call against one reference call per view (also driven by tests/test_fuzz_gpu.py)."""
+    """Every view of one batched call against one reference call per view (also driven by tests/test_zy_fuzz_gpu.py)."""
     V = len(cams)
     W, H = cams[0].image_width, cams[0].image_height
     gc, gd, ga = _upstream(V, W, H)

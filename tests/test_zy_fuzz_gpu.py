@@ -5,7 +5,9 @@ colours, scale + rotation or precomputed covariance, splat size from sub-pixel t
 Gaussians behind the camera (up to all of them: nothing rendered), exactly transparent and exactly opaque splats, background
 -- and every example must give the reference's bits for radii, tile counts, the sorted key and ID lists, tile ranges,
 n_contrib, final_T and the three images, and its gradients within 1e-3 relative.  derandomize=True: the same examples in
-every run, so a pass here is a pass at the end of the round."""
+every run, so a pass here is a pass at the end of the round.  (Named test_zy_* so that it is collected behind the other
+suites: the reference is driven with inputs nobody ran it on before, and a fault inside it would poison the CUDA context for
+every test after it.)"""
 import os
 
 import pytest
