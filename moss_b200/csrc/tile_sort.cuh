@@ -87,6 +87,43 @@ __device__ __forceinline__ float blend_power(float dx, float dy, const float4& c
 //                        n/256 <= 16, observed maximum ~45).  The deepest ZJU tile (1704 keys) takes ~22k
 //                        cycles; the bitonic network took ~8x that, and it sits on the launch's critical path;
 //   n > SORT_CAP       : in-place bitonic network on the global segment (rare; correctness fallback).
+// Ranks of the 256 splitter samples (thread t holds the depth word of sample t; ties broken by t, so the ranks are a
+// permutation): samp[rank] = mine.  Every warp sorts its 32 (depth, index) pairs with a shuffle bitonic network, the
+// eight sorted runs go to shared memory (`runs`, 256 x 8 bytes of scratch), and a sample's rank is its position in its
+// own run plus, for each of the seven other runs, the number of smaller elements found by a 6-probe binary search:
+// ~350 instructions per thread.  The all-pairs count this replaces (each thread against all 256 samples, ~1600
+// instructions) was 40 % of the sort kernel's instructions at Stress size (ncu: 248 M warp instructions for 8160 tiles).
+// Contains one __syncthreads(); the caller synchronises before reading samp.
+__device__ __forceinline__ void rank_splitters(uint32_t mine, unsigned long long* runs, uint32_t* samp)
+{
+	const unsigned full = 0xffffffffu;
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	unsigned long long k = ((unsigned long long)mine << 8) | (unsigned)tid;
+#pragma unroll
+	for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+		for (int stride = size >> 1; stride > 0; stride >>= 1) {
+			const unsigned long long other = __shfl_xor_sync(full, k, stride);
+			const bool keep_min = ((lane & size) == 0) == ((lane & stride) == 0);   // ascending half keeps the minimum in its lower lane
+			const bool other_less = other < k;
+			k = (keep_min == other_less) ? other : k;
+		}
+	}
+	runs[warp * 32 + lane] = k;
+	__syncthreads();
+	int r = lane;
+#pragma unroll
+	for (int w = 0; w < TILE_PIX / 32; w++) {
+		const unsigned long long* a = runs + w * 32;
+		int lo = 0;
+#pragma unroll
+		for (int st = 16; st > 0; st >>= 1) lo += (lds_u64(a + lo + st - 1) < k) ? st : 0;
+		lo += (lds_u64(a + lo) < k) ? 1 : 0;
+		r += (w != warp) ? lo : 0;
+	}
+	samp[r] = (uint32_t)(k >> 8);
+}
+
 struct SortSmem {
 	unsigned long long keys[SORT_CAP];   // bucketed keys (sample sort) / the keys themselves (bitonic)
 	uint32_t samp[256];                  // sorted depth words of the splitters
@@ -117,15 +154,8 @@ __device__ __forceinline__ void tile_sort_large(SortSmem& sm, const BinWS& b, ui
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	// 1. splitters (sorted depth words of 255 evenly spaced keys), ranked exactly like the shared-memory version
 	const uint32_t mine = tid < 255 ? (uint32_t)(gk[(int)(((long long)(tid + 1) * n) >> 8)] >> 32) : 0xffffffffu;
-	sm.start[tid] = mine;                                              // scratch until step 3
 	sm.cur[tid] = 0u;
-	__syncthreads();
-	{
-		const unsigned long long me = ((unsigned long long)mine << 8) | (unsigned)tid;
-		int r = 0;
-		for (int q = 0; q < 256; q++) r += ((((unsigned long long)sm.start[q] << 8) | (unsigned)q) < me) ? 1 : 0;
-		sm.samp[r] = mine;
-	}
+	rank_splitters(mine, sm.keys, sm.samp);                            // sm.keys: scratch here, the bucket bytes from step 2 on
 	__syncthreads();
 	// 2. bucket of every key, bucket sizes
 	for (int i = tid; i < n; i += TILE_PIX) {
@@ -192,30 +222,13 @@ __device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 ra
 		return;
 	}
 	MOSS_TD(8);
-	// 1. splitters: the depth words of 255 evenly spaced keys, sorted by rank (every thread counts the samples
-	//    below its own: 255 broadcast reads, no barrier inside -- a 36-stage bitonic network costs ~5x more).
+	// 1. splitters: the depth words of 255 evenly spaced keys, sorted by rank (rank_splitters: warp-sorted runs merged
+	//    by binary searches; a 36-stage block-wide bitonic network costs ~5x the all-pairs count this replaced).
 	//    Buckets are defined on the depth word only: bucket(k) = #splitters < depth(k) is monotone in the full
 	//    key, which is all the counting sort needs; the ranking inside a bucket compares full keys.
 	const uint32_t mine = tid < 255 ? (uint32_t)(gk[(int)(((long long)(tid + 1) * n) >> 8)] >> 32) : 0xffffffffu;
-	uint32_t* scratch = reinterpret_cast<uint32_t*>(sm.keys);   // the bucketed keys are written only in step 4
-	scratch[tid] = mine;
 	sm.cur[tid] = 0u;
-	__syncthreads();
-	{
-		// (value, index) compared as one 64-bit number: ties broken by sample index, so ranks are a permutation;
-		// four independent counters keep the adds off one dependent chain
-		const unsigned long long me = ((unsigned long long)mine << 8) | (unsigned)tid;
-		int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
-#pragma unroll 16
-		for (int q = 0; q < 256; q += 4) {
-			const uint4 v = *reinterpret_cast<const uint4*>(scratch + q);
-			r0 += ((((unsigned long long)v.x << 8) | (unsigned)(q + 0)) < me) ? 1 : 0;
-			r1 += ((((unsigned long long)v.y << 8) | (unsigned)(q + 1)) < me) ? 1 : 0;
-			r2 += ((((unsigned long long)v.z << 8) | (unsigned)(q + 2)) < me) ? 1 : 0;
-			r3 += ((((unsigned long long)v.w << 8) | (unsigned)(q + 3)) < me) ? 1 : 0;
-		}
-		sm.samp[(r0 + r1) + (r2 + r3)] = mine;
-	}
+	rank_splitters(mine, sm.keys, sm.samp);                     // sm.keys is scratch here: the bucketed keys are written only in step 4
 	__syncthreads();
 	MOSS_TD(4);
 	// Steps 2, 4 and 5 handle SORT_ILP keys per thread at a time so their global loads, binary searches and
