@@ -203,37 +203,12 @@ __device__ __forceinline__ void tile_sort_large(SortSmem& sm, const BinWS& b, ui
 	}
 }
 
-__device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 range, int n, int tile)
+template <int SORT_ILP>
+__device__ __forceinline__ void sample_sort_tail(SortSmem& sm, const BinWS& b, uint2 range, int n, int tile, const unsigned long long* gk)
 {
-	unsigned long long* gk = b.keys + range.x;
-	const int tid = threadIdx.x;
-	if (n <= TILE_PIX) {
-		if (tid < n) sm.keys[tid] = gk[tid];
-		__syncthreads();
-		block_bitonic_sort(sm.keys, n);
-		if (tid < n) emit_sorted(b, range.x + tid, tile, sm.keys[tid]);
-		return;
-	}
-	if (n > SORT_CAP) {
-		if (n <= LARGE_SORT_CAP && b.keys_tmp) { tile_sort_large(sm, b, range, n, tile); return; }
-		__syncthreads();
-		block_bitonic_sort(gk, n);
-		for (int i = tid; i < n; i += TILE_PIX) emit_sorted(b, range.x + i, tile, gk[i]);
-		return;
-	}
-	MOSS_TD(8);
-	// 1. splitters: the depth words of 255 evenly spaced keys, sorted by rank (rank_splitters: warp-sorted runs merged
-	//    by binary searches; a 36-stage block-wide bitonic network costs ~5x the all-pairs count this replaced).
-	//    Buckets are defined on the depth word only: bucket(k) = #splitters < depth(k) is monotone in the full
-	//    key, which is all the counting sort needs; the ranking inside a bucket compares full keys.
-	const uint32_t mine = tid < 255 ? (uint32_t)(gk[(int)(((long long)(tid + 1) * n) >> 8)] >> 32) : 0xffffffffu;
-	sm.cur[tid] = 0u;
-	rank_splitters(mine, sm.keys, sm.samp);                     // sm.keys is scratch here: the bucketed keys are written only in step 4
-	__syncthreads();
-	MOSS_TD(4);
 	// Steps 2, 4 and 5 handle SORT_ILP keys per thread at a time so their global loads, binary searches and
 	// bucket scans overlap (each step is a chain of dependent shared-memory reads per key).
-	constexpr int SORT_ILP = 8;
+	const int tid = threadIdx.x;
 	// 2. bucket = number of splitters below the key (0..255); bucket sizes
 	for (int c0 = 0; c0 < n; c0 += SORT_ILP * TILE_PIX) {
 		unsigned long long key[SORT_ILP];
@@ -328,6 +303,41 @@ __device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 ra
 			if (p < n) emit_sorted(b, range.x + st[u] + r[u], tile, key[u]);
 		}
 	}
+}
+
+__device__ __forceinline__ void tile_sort(SortSmem& sm, const BinWS& b, uint2 range, int n, int tile)
+{
+	unsigned long long* gk = b.keys + range.x;
+	const int tid = threadIdx.x;
+	if (n <= TILE_PIX) {
+		if (tid < n) sm.keys[tid] = gk[tid];
+		__syncthreads();
+		block_bitonic_sort(sm.keys, n);
+		if (tid < n) emit_sorted(b, range.x + tid, tile, sm.keys[tid]);
+		return;
+	}
+	if (n > SORT_CAP) {
+		if (n <= LARGE_SORT_CAP && b.keys_tmp) { tile_sort_large(sm, b, range, n, tile); return; }
+		__syncthreads();
+		block_bitonic_sort(gk, n);
+		for (int i = tid; i < n; i += TILE_PIX) emit_sorted(b, range.x + i, tile, gk[i]);
+		return;
+	}
+	MOSS_TD(8);
+	// 1. splitters: the depth words of 255 evenly spaced keys, sorted by rank (rank_splitters: warp-sorted runs merged
+	//    by binary searches; a 36-stage block-wide bitonic network costs ~5x the all-pairs count this replaced).
+	//    Buckets are defined on the depth word only: bucket(k) = #splitters < depth(k) is monotone in the full
+	//    key, which is all the counting sort needs; the ranking inside a bucket compares full keys.
+	const uint32_t mine = tid < 255 ? (uint32_t)(gk[(int)(((long long)(tid + 1) * n) >> 8)] >> 32) : 0xffffffffu;
+	sm.cur[tid] = 0u;
+	rank_splitters(mine, sm.keys, sm.samp);                     // sm.keys is scratch here: the bucketed keys are written only in step 4
+	__syncthreads();
+	MOSS_TD(4);
+	// Steps 2-5 with as many keys per thread in flight as the tile needs: a chunk is SORT_ILP x 256 slots, and a 900-key
+	// tile walked in chunks of 2048 spends half of its binary searches and bucket scans on slots that hold nothing.
+	if (n <= 2 * TILE_PIX) sample_sort_tail<2>(sm, b, range, n, tile, gk);
+	else if (n <= 4 * TILE_PIX) sample_sort_tail<4>(sm, b, range, n, tile, gk);
+	else sample_sort_tail<8>(sm, b, range, n, tile, gk);
 	MOSS_TD(9);
 }
 

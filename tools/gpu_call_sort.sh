@@ -4,5 +4,5 @@ mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_parity_gpu.py tests/test_batch_gpu.py tests/test_zy_fuzz_gpu.py tests/test_graph_gpu.py -x -q -m gpu > gpurun_out/sort_pytest.log 2>&1
 echo "pytest exit $?" >> gpurun_out/sort_pytest.log
 tail -3 gpurun_out/sort_pytest.log
-bash tools/ab_libs.sh ab_libs/libmoss_prev.so default > gpurun_out/sort_ab.txt 2> gpurun_out/sort_ab.err
+bash tools/ab_libs.sh default > gpurun_out/sort_ab.txt 2> gpurun_out/sort_ab.err
 cat gpurun_out/sort_ab.txt
