@@ -479,8 +479,15 @@ blend_backward_kernel(const __grid_constant__ ViewBatch vb, GeomWS g, ImageWS im
 	if (sub == 0) MOSS_TT(4);
 #endif
 
-	float accum_rec[3] = {0.f, 0.f, 0.f}, last_color[3] = {0.f, 0.f, 0.f};
-	float accum_depth_rec = 0.f, last_depth = 0.f, accum_alpha_rec = 0.f, last_alpha = 0.f;
+	// State of the back-to-front walk.  The reference keeps, per channel, (accum_rec, last_alpha, last_color) and forms
+	// arc = last_alpha * last_color + (1 - last_alpha) * accum_rec at the NEXT contributing instance (DGR backward.cu:
+	// 531-551).  Here the walk carries that combination itself -- accum_rec[] below IS the arc the next contributor will
+	// use -- updated as alpha * c + (1 - alpha) * arc: the same operands and the same expression, one value per channel
+	// instead of two.  An instance that does not contribute runs the same update with alpha = 0 (0 * c + 1 * arc = arc,
+	// T / (1 - 0) = T, exactly), so the recurrences need no selects; its gradient terms vanish because they all carry
+	// the masked alpha or the masked Gaussian weight as a factor.  (Per hit: 20 selects -> 2, 5 registers of state less.)
+	float accum_rec[3] = {0.f, 0.f, 0.f};
+	float accum_depth_rec = 0.f, accum_alpha_rec = 0.f;
 	if (ck.rec && n_contrib > seg_hi) {
 		// the pixel kept blending behind this segment: start from the forward's state in front of position seg_hi.
 		// With P = that prefix state and F the final sums, the reference's running "what lies behind" values are
@@ -570,10 +577,13 @@ blend_backward_kernel(const __grid_constant__ ViewBatch vb, GeomWS g, ImageWS im
 				dx[k] = xy.x - pxf; dy[k] = xy.y - pyf;
 				const float power = blend_power(dx[k], dy[k], co);
 				Gs[k] = expf(power);
-				al[k] = fminf(fmul(co.w, Gs[k]), 0.99f);
-				ra[k] = __fdividef(1.0f, 1.0f - al[k]);
+				const float a_raw = fminf(fmul(co.w, Gs[k]), 0.99f);
 				const uint32_t contributor = block_last - 1u - (uint32_t)(base + j);
-				valid[k] = (h + k < nh) && contributor < last_contributor && !(power > 0.0f) && !(al[k] < 1.0f / 255.0f);
+				valid[k] = (h + k < nh) && contributor < last_contributor && !(power > 0.0f) && !(a_raw < 1.0f / 255.0f);
+				// masked: a skipped instance has alpha 0 and weight 0 (exp(power) may be inf for power > 0: never multiplied in)
+				al[k] = valid[k] ? a_raw : 0.f;
+				Gs[k] = valid[k] ? Gs[k] : 0.f;
+				ra[k] = __fdividef(1.0f, 1.0f - al[k]);
 			}
 			bool any_valid = false;
 #pragma unroll
@@ -584,45 +594,38 @@ blend_backward_kernel(const __grid_constant__ ViewBatch vb, GeomWS g, ImageWS im
 			float v[BWD_GROUP * 8], v_opa[BWD_GROUP];
 #pragma unroll
 			for (int k = 0; k < BWD_GROUP; k++) {
-				const bool ok = valid[k];
-				const float alpha = al[k];
+				const float alpha = al[k];                        // 0 for an instance that does not contribute
 				const float4 f = fs[k];
 				const float4 co = cos_[k];
 				const float Tn = T * ra[k];                       // T / (1 - alpha), DGR backward.cu:520
-				const float omla = 1.f - last_alpha;
+				const float oma = 1.f - alpha;
 				const float dchannel_dcolor = alpha * Tn;
 				const float c[3] = {f.x, f.y, f.z};
 				float dL_dopa = 0.0f;
 #pragma unroll
 				for (int ch = 0; ch < 3; ch++) {
-					const float arc = last_alpha * last_color[ch] + omla * accum_rec[ch];
-					dL_dopa += (c[ch] - arc) * dpix[ch];
-					v[k * 8 + ch] = ok ? dchannel_dcolor * dpix[ch] : 0.f;
-					accum_rec[ch] = ok ? arc : accum_rec[ch];
-					last_color[ch] = ok ? c[ch] : last_color[ch];
+					dL_dopa += (c[ch] - accum_rec[ch]) * dpix[ch];
+					v[k * 8 + ch] = dchannel_dcolor * dpix[ch];
+					accum_rec[ch] = alpha * c[ch] + oma * accum_rec[ch];
 				}
-				const float adr = last_alpha * last_depth + omla * accum_depth_rec;
-				dL_dopa += (f.w - adr) * ddepth;
-				const float aar = last_alpha + omla * accum_alpha_rec;
-				dL_dopa += (1.f - aar) * dalpha;
+				dL_dopa += (f.w - accum_depth_rec) * ddepth;
+				dL_dopa += (1.f - accum_alpha_rec) * dalpha;
 				dL_dopa *= Tn;
 				dL_dopa += (-T_final * ra[k]) * bg_dot_dpixel;
-				accum_depth_rec = ok ? adr : accum_depth_rec;
-				last_depth = ok ? f.w : last_depth;
-				accum_alpha_rec = ok ? aar : accum_alpha_rec;
-				last_alpha = ok ? alpha : last_alpha;
-				T = ok ? Tn : T;
+				accum_depth_rec = alpha * f.w + oma * accum_depth_rec;
+				accum_alpha_rec = alpha + oma * accum_alpha_rec;
+				T = Tn;
 
 				const float dL_dG = co.w * dL_dopa;
-				const float gdx = Gs[k] * dx[k], gdy = Gs[k] * dy[k];
+				const float gdx = Gs[k] * dx[k], gdy = Gs[k] * dy[k];   // Gs is 0 for a skipped instance
 				const float dG_ddelx = -gdx * co.x - gdy * co.y;
 				const float dG_ddely = -gdy * co.z - gdx * co.y;
-				v[k * 8 + 3] = ok ? dL_dG * dG_ddelx * ddelx_dx : 0.f;
-				v[k * 8 + 4] = ok ? dL_dG * dG_ddely * ddely_dy : 0.f;
-				v[k * 8 + 5] = ok ? -0.5f * gdx * dx[k] * dL_dG : 0.f;
-				v[k * 8 + 6] = ok ? -0.5f * gdx * dy[k] * dL_dG : 0.f;
-				v[k * 8 + 7] = ok ? -0.5f * gdy * dy[k] * dL_dG : 0.f;
-				v_opa[k] = ok ? Gs[k] * dL_dopa : 0.f;
+				v[k * 8 + 3] = dL_dG * dG_ddelx * ddelx_dx;
+				v[k * 8 + 4] = dL_dG * dG_ddely * ddely_dy;
+				v[k * 8 + 5] = -0.5f * gdx * dx[k] * dL_dG;
+				v[k * 8 + 6] = -0.5f * gdx * dy[k] * dL_dG;
+				v[k * 8 + 7] = -0.5f * gdy * dy[k] * dL_dG;
+				v_opa[k] = Gs[k] * dL_dopa;
 			}
 			// ---- warp reduction, one row per (warp, slot): lane l ends with component l&7 of hit l>>3 ------------
 			static_assert(BWD_GROUP == 4, "the transpose-reduce below is laid out for 4 hits x 8 components");
