@@ -146,6 +146,19 @@ def test_skinning_refuses_cpu_compute_and_frame_abi_validates():
     assert lib.moss_smpl_joint_tables(None, 0, 10, None, None, None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
 
 
+def test_image_loss_scratch_and_tracing_switch_without_a_gpu(lib):
+    """Scratch sizes of the image-loss launch (tile grid aligned to the crop: one extra tile column and row; images of up to
+    296 tiles launch one block per tile and colour channel) and the NVTX switch, none of which touches the GPU."""
+    tiles = lambda W, H: ((W + 31) // 32 + 1) * ((H + 31) // 32 + 1)      # noqa: E731
+    assert lib.moss_image_losses_scratch_bytes(512, 512) == 16 + 16 * 3 * tiles(512, 512)       # 289 tiles: per-channel blocks
+    assert lib.moss_image_losses_scratch_bytes(1920, 1080) == 16 + 16 * tiles(1920, 1080)       # 2135 tiles: one block per tile
+    assert lib.moss_image_losses_scratch_bytes(0, 7) == 16
+    k = _abi.MossImageLoss()
+    assert lib.moss_image_losses(None, C.byref(k), None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    assert lib.moss_image_losses_static(None, C.byref(k), None, None, None) == _abi.MOSS_ERR_INVALID_ARGUMENT
+    assert lib.moss_nvtx_enable(1) == 0 and lib.moss_nvtx_enable(0) == 0
+
+
 def test_api_validation_and_no_cpu_fallback():
     import moss_b200 as M
     rs = M.GaussianRasterizationSettings(image_height=16, image_width=16, tanfovx=1.0, tanfovy=1.0, bg=torch.zeros(3),
