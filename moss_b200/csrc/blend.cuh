@@ -486,6 +486,8 @@ blend_backward_kernel(const __grid_constant__ ViewBatch vb, GeomWS g, ImageWS im
 	// instead of two.  An instance that does not contribute runs the same update with alpha = 0 (0 * c + 1 * arc = arc,
 	// T / (1 - 0) = T, exactly), so the recurrences need no selects; its gradient terms vanish because they all carry
 	// the masked alpha or the masked Gaussian weight as a factor.  (Per hit: 20 selects -> 2, 5 registers of state less.)
+	// Assumes finite colours and depths: 0 * c of a skipped instance with a NaN / Inf colour reaches the pixel's running
+	// sums here, where a select kept it out (such a Gaussian already puts NaN into every pixel it does contribute to).
 	float accum_rec[3] = {0.f, 0.f, 0.f};
 	float accum_depth_rec = 0.f, accum_alpha_rec = 0.f;
 	if (ck.rec && n_contrib > seg_hi) {
