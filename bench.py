@@ -21,6 +21,8 @@ library's own exchange kernels over NVLink peer memory (weak scaling: views/step
                      reads image + gradients back.  `e2e.value` blocks the host on every call (forward outputs are read
                      back on a side stream during the backward); `e2e.pipelined` keeps two calls in flight.  Both arms
                      run the same two loops (e2e_step / e2e_pipelined).
+  config / run     : `config` names the workload and is the SAME dict in both arms (workload, gaussians, image, views, L2
+                     protocol, parallelism); what is specific to an arm's run (instances, launch mode, collective) is in `run`.
   roofline / cpu_baseline / clocks / gpu_launches / extra_workloads / front_end / exchange_check: see DESIGN.md "Measurement".
 
 --impl reference : the UNMODIFIED reference CUDA rasterizer (oracle/_ref/diff_gaussian_rasterization, rebuilt for
@@ -680,11 +682,13 @@ def run_ours(args, rank, world, dev):
         "ms_per_view": round(ms_step / V, 5),
         "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "gaussians": P, "visible": Vis, "instances": R,
-                   "image": [W, H], "views_per_step": world * V, "views_per_gpu_per_step": V,
+        # `config` names the workload and is the same dict in both arms; what is specific to this arm's run sits in `run`
+        "config": {"workload": desc, "gaussians": P, "image": [W, H], "views_per_step": world * V, "views_per_gpu_per_step": V,
                    "l2": "flushed between steps (256 MiB fill, outside the timed events)",
-                   "launch": "one CUDA graph per step (fwd+bwd+exchange captured once, MOSS_FLAG_ASYNC)" if use_graph else "stream launches",
-                   "parallelism": f"dp{world} (views sharded, packed parameter gradient summed over ranks: {h.collective_kind})" if world > 1 else "single GPU"},
+                   "parallelism": f"dp{world}" if world > 1 else "single GPU"},
+        "run": {"visible": Vis, "instances": R,
+                "launch": "one CUDA graph per step (fwd+bwd+exchange captured once, MOSS_FLAG_ASYNC)" if use_graph else "stream launches",
+                "collective": f"views sharded, packed parameter gradient summed over ranks: {h.collective_kind}" if world > 1 else "none"},
         "value_stream": {"value": round(mpix / (ss["mean"] * 1e-3), 2), "ms_per_step": round(ss["mean"], 5),
                          "note": "the same raw C-ABI calls as stream launches (no CUDA graph)"},
         "value_public_api": {"value": round(mpix / (sa["mean"] * 1e-3), 2), "ms_per_step": round(sa["mean"], 5),
@@ -1072,9 +1076,11 @@ def run_reference(args, rank, world, dev):
             "ms_median": round(sd["median"], 5), "ms_p10": round(sd["p10"], 5), "ms_p90": round(sd["p90"], 5),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "gaussians": P, "image": [W, H], "views_per_step": world * V, "views_per_gpu_per_step": V,
-                       "reference": "unmodified DGR CUDA rasterizer rebuilt for sm_100 (the reference has no CPU path)",
                        "l2": "flushed between steps (256 MiB fill, outside the timed events)",
-                       "parallelism": f"dp{world} (one NCCL all_reduce per gradient tensor: the reference has no packed gradient)" if world > 1 else "single GPU"},
+                       "parallelism": f"dp{world}" if world > 1 else "single GPU"},
+            "run": {"reference": "unmodified DGR CUDA rasterizer rebuilt for sm_100 (the reference has no CPU path)",
+                    "launch": "stream launches through the reference's Python API",
+                    "collective": "one NCCL all_reduce per gradient tensor: the reference has no packed gradient" if world > 1 else "none"},
             "e2e": e2e_object(mpix, pipe_ms_step, se, h2d, d2h, e2e_steps)}
     if raw is not None:
         if "error" in raw:
